@@ -1,0 +1,64 @@
+// Internal launch interfaces between the planner (api.cu) and the kernel files.
+#pragma once
+#include "common.cuh"
+
+namespace db200 {
+
+// out[row] = fold(in[row*row_stride : +n]) with ctas_per_row CTAs per row.
+struct SplitArgs {
+    const void* in; void* out;
+    size_t n; size_t rows; size_t row_stride; ptrdiff_t out_stride;
+    unsigned ctas_per_row; unsigned cluster;
+    const void* identity;
+};
+cudaError_t launch_split(int red, int dtin, int dtout, const SplitArgs& a, const Launch& l);
+
+// Segmented (row) reduction, one sub-warp / warp / CTA per row.
+struct RowsArgs {
+    const void* in; void* out;
+    size_t rows; size_t n; size_t row_stride; ptrdiff_t out_stride;
+    const void* identity;
+};
+cudaError_t launch_rows(int red, int dtin, int dtout, const RowsArgs& a, const Launch& l);
+
+// Fused row max + row sum in one pass (fp32 accumulate/outputs).
+struct RowsMaxSumArgs {
+    const void* in; float* out_max; float* out_sum;
+    size_t rows; size_t n; size_t row_stride;
+};
+cudaError_t launch_rows_max_sum(int dtin, const RowsMaxSumArgs& a, const Launch& l);
+
+// Column reduction: in[o][r][i] (i contiguous) -> out[o][i].
+struct ColsArgs {
+    const void* in; void* out;
+    size_t outer, reduced, inner;
+    size_t in_stride_o, in_stride_r;       // elements
+    ptrdiff_t out_stride_o, out_stride_i;  // elements
+    const void* identity;
+};
+cudaError_t launch_cols(int red, int dtin, int dtout, const ColsArgs& a, const Launch& l);
+
+// Arbitrary strided N-D reduction (collapsed dims, <= kMaxDims each side).
+constexpr int kMaxDims = 6;
+struct GenericArgs {
+    const void* in; void* out;
+    int nk, nr;
+    long long kshape[kMaxDims], kin[kMaxDims], kout[kMaxDims];
+    long long rshape[kMaxDims], rin[kMaxDims];
+    const void* identity;
+    int warp_per_output;
+};
+cudaError_t launch_generic(int red, int dtin, int dtout, const GenericArgs& a, const Launch& l);
+
+// out[j] = identity for all outputs (empty reduction range).
+cudaError_t launch_fill(int dtout, void* out, int nk, const long long* kshape, const long long* kout,
+                        const void* identity, const Launch& l);
+
+// WCR scatter: bins[idx[i]] = op(bins[idx[i]], values ? values[i] : *const_value).
+struct ScatterArgs {
+    const void* idx; const void* values; const void* const_value;
+    size_t n; void* bins; size_t nbins;
+};
+cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l);
+
+}  // namespace db200

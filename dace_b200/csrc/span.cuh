@@ -1,0 +1,64 @@
+// Contiguous-span accumulation used by the row kernels: a group of `nthr`
+// threads (a sub-warp, a warp or a CTA) folds `n` contiguous elements.
+// The span may start at any element-aligned address (memlet offsets land the
+// `_in` pointer anywhere, reference dace/libraries/standard/nodes/reduce.py:599-602):
+// a scalar head brings the pointer to vector alignment, the body issues U
+// independent 16/32-byte streaming loads per thread, a scalar tail finishes.
+#pragma once
+#include "common.cuh"
+
+namespace db200 {
+
+template <class L, int VB> struct VecInfo {
+    static constexpr int N = VB / int(sizeof(L));      // elements per vector
+    static constexpr int NA = N < 8 ? N : 8;           // independent accumulators per thread
+};
+
+template <class L, class A, class Op, int VB>
+__device__ __forceinline__ void fold_vec(A (&acc)[VecInfo<L, VB>::NA], const Words<VB>& w) {
+    constexpr int N = VecInfo<L, VB>::N;
+    constexpr int NA = VecInfo<L, VB>::NA;
+#pragma unroll
+    for (int j = 0; j < N; ++j) acc[j % NA] = Op::apply(acc[j % NA], vec_elem<L, A, VB>(w, j));
+}
+
+template <class A, class Op, int NA>
+__device__ __forceinline__ A fold_acc(const A (&acc)[NA]) {
+    A v = acc[0];
+#pragma unroll
+    for (int j = 1; j < NA; ++j) v = Op::apply(v, acc[j]);
+    return v;
+}
+
+template <class L, class A, class Op, int VB, int U>
+__device__ __forceinline__ A span_accumulate(const L* __restrict__ p, size_t n, unsigned tid, unsigned nthr) {
+    constexpr int N = VecInfo<L, VB>::N;
+    constexpr int NA = VecInfo<L, VB>::NA;
+    A acc[NA];
+#pragma unroll
+    for (int j = 0; j < NA; ++j) acc[j] = Op::neutral();
+
+    const size_t addr = reinterpret_cast<size_t>(p);
+    size_t h = ((size_t(VB) - (addr & size_t(VB - 1))) & size_t(VB - 1)) / sizeof(L);
+    if (h > n) h = n;
+    for (size_t i = tid; i < h; i += nthr) acc[0] = Op::apply(acc[0], to_acc<A, L>(ldg_scalar(p + i)));
+
+    const char* pv = reinterpret_cast<const char*>(p + h);
+    const size_t nvec = (n - h) / N;
+    size_t v = tid;
+    for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
+        Words<VB> w[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
+#pragma unroll
+        for (int u = 0; u < U; ++u) fold_vec<L, A, Op, VB>(acc, w[u]);
+    }
+    for (; v < nvec; v += nthr) {
+        Words<VB> w = ldg_stream<VB>(pv + v * VB);
+        fold_vec<L, A, Op, VB>(acc, w);
+    }
+    for (size_t i = h + nvec * N + tid; i < n; i += nthr) acc[0] = Op::apply(acc[0], to_acc<A, L>(ldg_scalar(p + i)));
+    return fold_acc<A, Op, NA>(acc);
+}
+
+}  // namespace db200
