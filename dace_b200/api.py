@@ -1,0 +1,220 @@
+"""Host-side mirror of the reference's Reduce operator on the B200 C ABI.
+
+``reduce`` has the argument meaning of ``dace.reduce(op, in_array, out_array,
+axis, identity)`` (reference dace/frontend/operations.py:240-258) and of the
+``Reduce`` library node's properties ``wcr`` / ``axes`` / ``identity``
+(reference dace/libraries/standard/nodes/reduce.py:1346-1411):
+
+* ``identity=None`` folds into the values already in ``out_array``;
+* ``axis=None`` reduces all axes; negative axes count from the end;
+* views with arbitrary strides are accepted on both sides (memlet subsets);
+* the output dtype is the input dtype unless ``out_array`` says otherwise
+  (bf16/f16 inputs may write fp32; accumulation is fp32 either way).
+
+torch is used only to own device memory and streams.  Every call goes through
+``libdace_b200_reduce.so``; nothing here computes on the CPU.
+"""
+import ctypes
+from typing import Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+from .redtypes import ReductionType, resolve
+
+F32, F64, I32, I64, U32, U64, BF16, F16, I8, U8, I16, U16 = range(12)
+
+_TORCH2DT = {
+    torch.float32: F32, torch.float64: F64, torch.int32: I32, torch.int64: I64,
+    torch.bfloat16: BF16, torch.float16: F16, torch.int8: I8, torch.uint8: U8, torch.int16: I16,
+    torch.bool: U8,
+}
+for _name, _dt in (('uint32', U32), ('uint64', U64), ('uint16', U16)):
+    if hasattr(torch, _name):
+        _TORCH2DT[getattr(torch, _name)] = _dt
+
+_NP_OF_DT = {F32: np.float32, F64: np.float64, I32: np.int32, I64: np.int64, U32: np.uint32, U64: np.uint64,
+             I8: np.int8, U8: np.uint8, I16: np.int16, U16: np.uint16}
+
+
+def dtype_code(t: torch.dtype) -> int:
+    try:
+        return _TORCH2DT[t]
+    except KeyError:
+        raise NotImplementedError('dtype %s has no sm_100a reduction kernel' % (t, ))
+
+
+def scalar_bytes(value, dt: int) -> bytes:
+    """Encode a Python/NumPy scalar as one element of C-ABI dtype ``dt``."""
+    if dt == BF16:
+        return torch.tensor(float(value), dtype=torch.bfloat16).view(torch.int16).numpy().tobytes()
+    if dt == F16:
+        return np.float16(value).tobytes()
+    npdt = _NP_OF_DT[dt]
+    if np.issubdtype(npdt, np.integer):
+        if isinstance(value, (bool, np.bool_)):
+            value = int(value)
+        return np.array(value).astype(npdt, casting='unsafe').tobytes()
+    return npdt(value).tobytes()
+
+
+def _stream_ptr(stream) -> int:
+    if stream is None:
+        return torch.cuda.current_stream().cuda_stream
+    if isinstance(stream, int):
+        return stream
+    return stream.cuda_stream
+
+
+class Workspace:
+    """Device workspace for cross-CTA combining: allocated once, reused
+    (the protocol of the reference's CUB temp storage,
+    reference dace/libraries/standard/nodes/reduce.py:550-570)."""
+
+    def __init__(self, device=None, stream=None):
+        lib = _lib.load()
+        self.nbytes = int(lib.dace_b200_workspace_bytes())
+        self.buffer = torch.empty(self.nbytes, dtype=torch.uint8, device=device or 'cuda')
+        _lib.check(lib.dace_b200_workspace_init(self.buffer.data_ptr(), self.nbytes, _stream_ptr(stream)),
+                   'dace_b200_workspace_init')
+
+    @property
+    def ptr(self) -> int:
+        return self.buffer.data_ptr()
+
+
+def _require_cuda(t: torch.Tensor, what: str):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        # Same rule as the reference's GPU expansions, which insist on GPU_Global /
+        # CPU_Pinned storage (reference reduce.py:499-507) - but no CPU fallback here.
+        raise ValueError('%s must be a CUDA tensor: the B200 backend has no CPU fallback' % what)
+
+
+def _normalize_axes(axis, ndim: int):
+    if axis is None:
+        return tuple(range(ndim))
+    if isinstance(axis, int):
+        axis = (axis, )
+    out = []
+    for a in axis:
+        a = int(a)
+        if a < -ndim or a >= ndim:
+            raise ValueError('axis %d out of range for %d dimensions' % (a, ndim))
+        out.append(a % ndim)
+    if len(set(out)) != len(out):
+        raise ValueError('duplicate reduction axis')
+    return tuple(sorted(out))
+
+
+def reduce(op, in_array: torch.Tensor, out_array: Optional[torch.Tensor] = None,
+           axis: Union[None, int, Sequence[int]] = None, identity=None, stream=None,
+           workspace: Optional[Workspace] = None) -> Optional[torch.Tensor]:
+    """``out_array[kept] = fold(op, identity, in_array[kept, reduced])`` on the GPU.
+
+    Returns the new tensor when ``out_array`` is None (then ``identity`` is
+    required), else None - the reference's convention."""
+    lib = _lib.load()
+    rt = resolve(op)
+    _require_cuda(in_array, 'in_array')
+    axes = _normalize_axes(axis, in_array.dim())
+    kept = [i for i in range(in_array.dim()) if i not in axes]
+    kept_shape = [in_array.shape[i] for i in kept]
+    created = out_array is None
+    if created:
+        if identity is None:
+            raise ValueError('identity is required when out_array is not given')
+        out_dtype = in_array.dtype
+        out_array = torch.empty(kept_shape, dtype=out_dtype, device=in_array.device)
+    _require_cuda(out_array, 'out_array')
+    if out_array.device != in_array.device:
+        raise ValueError('in_array and out_array live on different devices')
+    # The output may keep unit dims (e.g. C[0:N, 5, 5, 0:C]) - squeeze like the
+    # reference does (reference reduce.py:40-54) and match the kept extents.
+    out_sq_shape = [s for s in out_array.shape if s != 1]
+    kept_sq_shape = [s for s in kept_shape if s != 1]
+    if out_sq_shape != kept_sq_shape:
+        raise ValueError('out_array shape %s does not match the kept axes %s' %
+                         (tuple(out_array.shape), tuple(kept_shape)))
+    out_sq_strides = [st for s, st in zip(out_array.shape, out_array.stride()) if s != 1]
+    out_strides = []
+    it = iter(out_sq_strides)
+    for s in kept_shape:
+        out_strides.append(0 if s == 1 else next(it))
+
+    dt_in, dt_out = dtype_code(in_array.dtype), dtype_code(out_array.dtype)
+    nd = in_array.dim()
+    shape = (ctypes.c_int64 * max(nd, 1))(*in_array.shape)
+    istr = (ctypes.c_int64 * max(nd, 1))(*in_array.stride())
+    ostr = (ctypes.c_int64 * max(len(kept), 1))(*out_strides)
+    mask = 0
+    for a in axes:
+        mask |= 1 << a
+    ident_buf = None
+    if identity is not None:
+        ident_buf = ctypes.create_string_buffer(scalar_bytes(identity, dt_out), 8)
+    ws_ptr, ws_bytes = (workspace.ptr, workspace.nbytes) if workspace is not None else (None, 0)
+    with torch.cuda.device(in_array.device):
+        status = lib.dace_b200_reduce_nd(int(rt), dt_in, dt_out, in_array.data_ptr(), out_array.data_ptr(), nd,
+                                         shape, istr, ostr, mask, ident_buf, ws_ptr, ws_bytes, _stream_ptr(stream))
+    _lib.check(status, 'dace_b200_reduce_nd')
+    return out_array if created else None
+
+
+def rows_max_sum(in_array: torch.Tensor, out_max: Optional[torch.Tensor] = None,
+                 out_sum: Optional[torch.Tensor] = None, stream=None):
+    """Row-wise max and sum of a 2-D array in one pass (fp32 outputs)."""
+    lib = _lib.load()
+    _require_cuda(in_array, 'in_array')
+    if in_array.dim() != 2 or in_array.stride(1) != 1:
+        raise ValueError('rows_max_sum expects a 2-D array with contiguous rows')
+    rows, n = in_array.shape
+    if out_max is None:
+        out_max = torch.empty(rows, dtype=torch.float32, device=in_array.device)
+    if out_sum is None:
+        out_sum = torch.empty(rows, dtype=torch.float32, device=in_array.device)
+    for o in (out_max, out_sum):
+        _require_cuda(o, 'output')
+        if o.dtype != torch.float32 or not o.is_contiguous() or o.numel() != rows:
+            raise ValueError('outputs must be contiguous float32[rows]')
+    with torch.cuda.device(in_array.device):
+        status = lib.dace_b200_reduce_rows_max_sum(dtype_code(in_array.dtype), in_array.data_ptr(),
+                                                   out_max.data_ptr(), out_sum.data_ptr(), rows, n,
+                                                   in_array.stride(0), _stream_ptr(stream))
+    _lib.check(status, 'dace_b200_reduce_rows_max_sum')
+    return out_max, out_sum
+
+
+def wcr_scatter(op, bins: torch.Tensor, indices: torch.Tensor, values=None, stream=None) -> None:
+    """``bins[indices[i]] = op(bins[indices[i]], values[i])`` - the WCR map
+    ``out >> bins(1, wcr)[:]; out[idx] = v`` of reference
+    samples/explicit/histogram.py:13-26 and ``hist[bin] += w`` of reference
+    tests/npbench/misc/azimint_hist_test.py:39-59.  ``values`` may be a tensor,
+    a scalar (applied for every index) or None (== 1).  ``bins`` is updated in
+    place and must be initialised by the caller (WCR semantics)."""
+    lib = _lib.load()
+    rt = resolve(op)
+    _require_cuda(bins, 'bins')
+    _require_cuda(indices, 'indices')
+    if not bins.is_contiguous() or not indices.is_contiguous():
+        raise ValueError('bins and indices must be contiguous')
+    dt_val, dt_idx = dtype_code(bins.dtype), dtype_code(indices.dtype)
+    vptr, cbuf = None, None
+    if isinstance(values, torch.Tensor):
+        _require_cuda(values, 'values')
+        if values.dtype != bins.dtype or values.numel() != indices.numel() or not values.is_contiguous():
+            raise ValueError('values must be contiguous, of bins.dtype and as long as indices')
+        vptr = values.data_ptr()
+    elif values is not None:
+        cbuf = ctypes.create_string_buffer(scalar_bytes(values, dt_val), 8)
+    with torch.cuda.device(bins.device):
+        status = lib.dace_b200_wcr_scatter(int(rt), dt_idx, dt_val, indices.data_ptr(), vptr, cbuf,
+                                           indices.numel(), bins.data_ptr(), bins.numel(), _stream_ptr(stream))
+    _lib.check(status, 'dace_b200_wcr_scatter')
+
+
+def histogram(indices: torch.Tensor, nbins: int, dtype=torch.int32, stream=None) -> torch.Tensor:
+    """Counts per bin: zero-initialised bins + Sum WCR scatter of ones."""
+    bins = torch.zeros(nbins, dtype=dtype, device=indices.device)
+    wcr_scatter(ReductionType.Sum, bins, indices, None, stream=stream)
+    return bins

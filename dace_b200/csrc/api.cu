@@ -1,0 +1,271 @@
+// C ABI + host-side planner of the B200 reduction backend (see
+// include/dace_b200_reduce.h for the contract).
+//
+// The planner canonicalises an arbitrary memlet subset + axis set the way the
+// reference's reduction planner does - drop unit dims, merge contiguous dims of
+// the same kind (reference dace/libraries/standard/reduction_planner.py:44-118) -
+// and then picks one of the hand-written kernels instead of emitting a schedule.
+#include <cstring>
+#include <mutex>
+#include "../../include/dace_b200_reduce.h"
+#include "common.cuh"
+#include "kernels.h"
+
+namespace db200 {
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+static std::mutex g_ws_mutex;
+static void* g_default_ws[64] = {nullptr};
+
+static cudaError_t resolve_workspace(void* workspace, size_t bytes, Launch& l) {
+    if (workspace != nullptr) {
+        if (bytes < kWorkspaceBytes) return cudaErrorInvalidValue;
+    } else {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+        std::lock_guard<std::mutex> lock(g_ws_mutex);
+        if (g_default_ws[dev] == nullptr) {
+            void* p = nullptr;
+            e = cudaMalloc(&p, kWorkspaceBytes);
+            if (e != cudaSuccess) return e;
+            e = cudaMemset(p, 0, kCounterBytes);
+            if (e != cudaSuccess) { cudaFree(p); return e; }
+            g_default_ws[dev] = p;
+        }
+        workspace = g_default_ws[dev];
+    }
+    l.ws.counters = reinterpret_cast<unsigned*>(workspace);
+    l.ws.partials = reinterpret_cast<char*>(workspace) + kCounterBytes;
+    return cudaSuccess;
+}
+
+struct Dim {
+    long long shape, in_stride, out_stride;
+    bool reduced;
+};
+
+static inline size_t ceil_div(size_t a, size_t b) { return (a + b - 1) / b; }
+
+static bool supported_pair(int dtin, int dtout) {
+    return dispatch_types(dtin, dtout, [](auto) -> cudaError_t { return cudaSuccess; }) == cudaSuccess;
+}
+
+// Full reduction / few long rows through the split kernel.
+static cudaError_t plan_split(int red, int dtin, int dtout, const void* in, void* out, size_t rows, size_t n,
+                              size_t row_stride, ptrdiff_t out_stride, const void* identity, const Launch& l) {
+    const size_t row_bytes = n * dtype_size(dtin);
+    const size_t sms = sm_count();
+    size_t want = ceil_div(row_bytes, size_t(64) << 10);   // one 64 KiB tile per CTA at least
+    size_t cap = ceil_div(2 * sms, rows);
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    unsigned cluster = 1;
+    if (want >= 2) { cluster = 2; want = (want / 2) * 2; }
+    // Partials area: rows * clusters accumulators of <= 8 bytes.
+    while (want > cluster && rows * (want / cluster) * 8 > kPartialBytes) want -= cluster;
+    SplitArgs a{in, out, n, rows, row_stride, out_stride, (unsigned)want, cluster, identity};
+    return launch_split(red, dtin, dtout, a, l);
+}
+
+static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, void* out, int ndim,
+                                  const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,
+                                  uint32_t mask, const void* identity, void* workspace, size_t workspace_bytes,
+                                  cudaStream_t stream) {
+    if (ndim < 0 || ndim > DACE_B200_MAX_DIMS) return cudaErrorInvalidValue;
+    if (ndim > 0 && (!shape || !in_strides)) return cudaErrorInvalidValue;
+    if (!in || !out) return cudaErrorInvalidValue;
+    if (red < RT_Min || red > RT_BXor) return cudaErrorNotSupported;
+    if (!supported_pair(dtin, dtout)) return cudaErrorNotSupported;
+    Launch l;
+    l.stream = stream;
+    cudaError_t e = resolve_workspace(workspace, workspace_bytes, l);
+    if (e != cudaSuccess) return e;
+
+    // Gather dims; default output strides are C-contiguous over the kept axes.
+    Dim dims[DACE_B200_MAX_DIMS];
+    long long kstride[DACE_B200_MAX_DIMS];
+    {
+        long long s = 1;
+        for (int i = ndim - 1; i >= 0; --i) {
+            kstride[i] = 0;
+            if (!((mask >> i) & 1u)) { kstride[i] = s; s *= shape[i]; }
+        }
+    }
+    size_t nout = 1, nred = 1;
+    int kept_seen = 0;
+    for (int i = 0; i < ndim; ++i) {
+        if (shape[i] < 0) return cudaErrorInvalidValue;
+        dims[i].shape = shape[i];
+        dims[i].in_stride = in_strides[i];
+        dims[i].reduced = (mask >> i) & 1u;
+        if (dims[i].reduced) { dims[i].out_stride = 0; nred *= (size_t)shape[i]; }
+        else {
+            dims[i].out_stride = out_strides ? out_strides[kept_seen] : kstride[i];
+            ++kept_seen;
+            nout *= (size_t)shape[i];
+        }
+    }
+    if (nout == 0) return cudaSuccess;
+
+    // Canonicalise: drop unit dims, merge mergeable neighbours of the same kind.
+    Dim c[DACE_B200_MAX_DIMS];
+    int nc = 0;
+    for (int i = 0; i < ndim; ++i) {
+        if (dims[i].shape == 1) continue;
+        if (nc > 0 && c[nc - 1].reduced == dims[i].reduced &&
+            c[nc - 1].in_stride == dims[i].in_stride * dims[i].shape &&
+            (dims[i].reduced || c[nc - 1].out_stride == dims[i].out_stride * dims[i].shape)) {
+            c[nc - 1].shape *= dims[i].shape;
+            c[nc - 1].in_stride = dims[i].in_stride;
+            c[nc - 1].out_stride = dims[i].out_stride;
+        } else {
+            c[nc++] = dims[i];
+        }
+    }
+
+    if (nred == 0) {
+        // Empty range: outputs become the identity; without one they stay as they are.
+        if (!identity) return cudaSuccess;
+        long long ks[kMaxDims], ko[kMaxDims];
+        int nk = 0;
+        for (int i = 0; i < nc; ++i)
+            if (!c[i].reduced) { if (nk >= kMaxDims) return cudaErrorNotSupported; ks[nk] = c[i].shape; ko[nk] = c[i].out_stride; ++nk; }
+        return launch_fill(dtout, out, nk, ks, ko, identity, l);
+    }
+
+    int nk = 0, nr = 0;
+    for (int i = 0; i < nc; ++i) (c[i].reduced ? nr : nk)++;
+
+    const size_t esz = dtype_size(dtin);
+    if (nr > 0) {
+        // [R] contiguous -> full reduction.
+        if (nc == 1 && c[0].in_stride == 1)
+            return plan_split(red, dtin, dtout, in, out, 1, (size_t)c[0].shape, 0, 0, identity, l);
+        // [K, R] with contiguous R -> rows.
+        if (nc == 2 && !c[0].reduced && c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
+            const size_t rows = (size_t)c[0].shape, n = (size_t)c[1].shape;
+            const size_t row_bytes = n * esz;
+            if (rows < 2 * (size_t)sm_count() && row_bytes >= (size_t(128) << 10) && rows <= kCounters)
+                return plan_split(red, dtin, dtout, in, out, rows, n, (size_t)c[0].in_stride,
+                                  (ptrdiff_t)c[0].out_stride, identity, l);
+            RowsArgs a{in, out, rows, n, (size_t)c[0].in_stride, (ptrdiff_t)c[0].out_stride, identity};
+            return launch_rows(red, dtin, dtout, a, l);
+        }
+        // [R, K] / [K1, R, K2] with contiguous trailing K -> cols.
+        if (nc == 2 && c[0].reduced && !c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
+            ColsArgs a{in, out, 1, (size_t)c[0].shape, (size_t)c[1].shape, 0, (size_t)c[0].in_stride,
+                       0, (ptrdiff_t)c[1].out_stride, identity};
+            return launch_cols(red, dtin, dtout, a, l);
+        }
+        if (nc == 3 && !c[0].reduced && c[1].reduced && !c[2].reduced && c[2].in_stride == 1 &&
+            c[0].in_stride >= 0 && c[1].in_stride >= 0) {
+            ColsArgs a{in, out, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[2].shape,
+                       (size_t)c[0].in_stride, (size_t)c[1].in_stride,
+                       (ptrdiff_t)c[0].out_stride, (ptrdiff_t)c[2].out_stride, identity};
+            return launch_cols(red, dtin, dtout, a, l);
+        }
+    }
+    // Everything else: generic strided kernel.
+    if (nk > kMaxDims || nr > kMaxDims) return cudaErrorNotSupported;
+    GenericArgs g;
+    memset(&g, 0, sizeof(g));
+    g.in = in; g.out = out; g.identity = identity;
+    for (int i = 0; i < nc; ++i) {
+        if (c[i].reduced) { g.rshape[g.nr] = c[i].shape; g.rin[g.nr] = c[i].in_stride; ++g.nr; }
+        else { g.kshape[g.nk] = c[i].shape; g.kin[g.nk] = c[i].in_stride; g.kout[g.nk] = c[i].out_stride; ++g.nk; }
+    }
+    const bool last_reduced = nc > 0 && c[nc - 1].reduced;
+    g.warp_per_output = nr > 0 && (last_reduced || nout < (size_t)sm_count() * 256);
+    return launch_generic(red, dtin, dtout, g, l);
+}
+
+}  // namespace db200
+
+using namespace db200;
+
+extern "C" {
+
+int dace_b200_version(void) { return 1000; }
+
+const char* dace_b200_status_string(int status) { return cudaGetErrorString((cudaError_t)status); }
+
+size_t dace_b200_workspace_bytes(void) { return kWorkspaceBytes; }
+
+int dace_b200_workspace_init(void* workspace, size_t workspace_bytes, dace_b200_stream_t stream) {
+    if (!workspace || workspace_bytes < kWorkspaceBytes) return (int)cudaErrorInvalidValue;
+    return (int)cudaMemsetAsync(workspace, 0, kCounterBytes, (cudaStream_t)stream);
+}
+
+int dace_b200_reduce_nd(int redtype, int dtype_in, int dtype_out, const void* in, void* out, int ndim,
+                        const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,
+                        uint32_t reduce_mask, const void* identity, void* workspace, size_t workspace_bytes,
+                        dace_b200_stream_t stream) {
+    return (int)reduce_nd_impl(redtype, dtype_in, dtype_out, in, out, ndim, shape, in_strides, out_strides,
+                               reduce_mask, identity, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int dace_b200_reduce_full(int redtype, int dtype_in, int dtype_out, const void* in, void* out, size_t num_items,
+                          const void* identity, void* workspace, size_t workspace_bytes,
+                          dace_b200_stream_t stream) {
+    int64_t shape[1] = {(int64_t)num_items}, st[1] = {1};
+    return (int)reduce_nd_impl(redtype, dtype_in, dtype_out, in, out, 1, shape, st, nullptr, 1u, identity,
+                               workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int dace_b200_reduce_rows(int redtype, int dtype_in, int dtype_out, const void* in, void* out,
+                          size_t num_segments, size_t segment_size, size_t segment_stride, const void* identity,
+                          void* workspace, size_t workspace_bytes, dace_b200_stream_t stream) {
+    int64_t shape[2] = {(int64_t)num_segments, (int64_t)segment_size};
+    int64_t st[2] = {(int64_t)segment_stride, 1};
+    return (int)reduce_nd_impl(redtype, dtype_in, dtype_out, in, out, 2, shape, st, nullptr, 2u, identity,
+                               workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int dace_b200_reduce_cols(int redtype, int dtype_in, int dtype_out, const void* in, void* out, size_t outer,
+                          size_t reduced, size_t inner, const void* identity, void* workspace,
+                          size_t workspace_bytes, dace_b200_stream_t stream) {
+    int64_t shape[3] = {(int64_t)outer, (int64_t)reduced, (int64_t)inner};
+    int64_t st[3] = {(int64_t)(reduced * inner), (int64_t)inner, 1};
+    return (int)reduce_nd_impl(redtype, dtype_in, dtype_out, in, out, 3, shape, st, nullptr, 2u, identity,
+                               workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int dace_b200_reduce_rows_max_sum(int dtype_in, const void* in, float* out_max, float* out_sum,
+                                  size_t num_segments, size_t segment_size, size_t segment_stride,
+                                  dace_b200_stream_t stream) {
+    if (!in || !out_max || !out_sum) return (int)cudaErrorInvalidValue;
+    if (num_segments == 0) return (int)cudaSuccess;
+    Launch l;
+    l.stream = (cudaStream_t)stream;
+    l.ws.counters = nullptr; l.ws.partials = nullptr;
+    RowsMaxSumArgs a{in, out_max, out_sum, num_segments, segment_size, segment_stride};
+    return (int)launch_rows_max_sum(dtype_in, a, l);
+}
+
+int dace_b200_wcr_scatter(int redtype, int dtype_idx, int dtype_val, const void* idx, const void* values,
+                          const void* const_value, size_t n, void* bins, size_t nbins,
+                          dace_b200_stream_t stream) {
+    if (n > 0 && (!idx || !bins)) return (int)cudaErrorInvalidValue;
+    if (nbins == 0 || n == 0) return (int)cudaSuccess;
+    Launch l;
+    l.stream = (cudaStream_t)stream;
+    l.ws.counters = nullptr; l.ws.partials = nullptr;
+    ScatterArgs a{idx, values, const_value, n, bins, nbins};
+    return (int)launch_scatter(redtype, dtype_idx, dtype_val, a, l);
+}
+
+}  // extern "C"

@@ -146,7 +146,7 @@ template <int BYTES> struct Words { uint32_t w[BYTES / 4]; };
 
 __device__ __forceinline__ Words<16> ldg_stream16(const void* p) {
     Words<16> r;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.u32 {%0,%1,%2,%3}, [%4];"
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]) : "l"(p));
     return r;
 }
@@ -288,6 +288,10 @@ struct Finish {
 
 template <class Op, class A, class S>
 __device__ __forceinline__ void write_result(S* out, A r, const Finish<A>& fin) {
+    if (fin.has_identity == 2) {  // degenerate reduction: plain copy, identity ignored
+        *out = from_acc<S, A>(r);
+        return;
+    }
     A base = fin.has_identity ? fin.identity : to_acc<A, S>(*out);
     *out = from_acc<S, A>(Op::apply(base, r));
 }

@@ -1,0 +1,200 @@
+// Segmented (row) reductions for sm_100a: the reduced axes are the trailing,
+// contiguous ones, so every output owns one contiguous span of the input.
+//
+// Replaces cub::DeviceSegmentedReduce::Reduce with dace::stridedIterator offsets
+// (reference dace/libraries/standard/nodes/reduce.py:526-544,
+// reference dace/runtime/include/dace/reduction.h:594-622) and the GPUAuto
+// contiguous schedule, one 32-thread block per output
+// (reference dace/libraries/standard/nodes/reduce.py:984-1139).
+//
+// Work decomposition by row length:
+//   * G in {1,2,4,8,16,32} lanes per row (sub-warp groups, persistent grid of
+//     full CTAs: no 1-warp blocks) - each lane issues U independent 256-bit loads;
+//   * one CTA per row for rows of tens of KiB and up;
+//   * rows of MiB size and few of them go to the split kernel (reduce_full.cu).
+#include "common.cuh"
+#include "span.cuh"
+#include "kernels.h"
+
+namespace db200 {
+
+constexpr int kRowThreads = 256;
+
+// G lanes per row; 32/G rows per warp per step.  G is a run-time power of two.
+template <class L, class A, class S, class Op, int VB, int U>
+__global__ void __launch_bounds__(kRowThreads)
+rows_group_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, size_t n, size_t row_stride,
+                  ptrdiff_t out_stride, Finish<A> fin, int G) {
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned g = lane & (G - 1);            // lane within the row group
+    const unsigned sub = lane / G;                // row slot within the warp
+    const unsigned rows_per_warp = 32 / G;
+    const size_t warp = (size_t(blockIdx.x) * kRowThreads + threadIdx.x) >> 5;
+    const size_t nwarps = (size_t(gridDim.x) * kRowThreads) >> 5;
+
+    for (size_t rb = warp * rows_per_warp; rb < rows; rb += nwarps * rows_per_warp) {
+        const size_t r = rb + sub;
+        const bool active = r < rows;
+        A v = Op::neutral();
+        if (active) v = span_accumulate<L, A, Op, VB, U>(in + r * row_stride, n, g, G);
+        for (int m = G >> 1; m >= 1; m >>= 1) v = Op::apply(v, shfl_xor(v, m));
+        if (active && g == 0) write_result<Op, A, S>(out + ptrdiff_t(r) * out_stride, v, fin);
+    }
+}
+
+// One CTA per row (grid-stride over rows).
+template <class L, class A, class S, class Op, int VB, int U>
+__global__ void __launch_bounds__(kRowThreads)
+rows_block_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, size_t n, size_t row_stride,
+                  ptrdiff_t out_stride, Finish<A> fin) {
+    __shared__ A scratch[32];
+    for (size_t r = blockIdx.x; r < rows; r += gridDim.x) {
+        A v = span_accumulate<L, A, Op, VB, U>(in + r * row_stride, n, threadIdx.x, kRowThreads);
+        v = block_reduce<Op, A>(v, scratch);
+        if (threadIdx.x == 0) write_result<Op, A, S>(out + ptrdiff_t(r) * out_stride, v, fin);
+        __syncthreads();  // scratch is reused by the next row
+    }
+}
+
+static inline int pick_group(size_t row_bytes) {
+    // Aim for >= 64 bytes (two 256-bit vectors) per lane before widening the group.
+    int G = 1;
+    while (G < 32 && size_t(G) * 64 < row_bytes) G <<= 1;
+    return G;
+}
+
+template <class T, class Op>
+static cudaError_t launch_rows_t(const RowsArgs& a, const Launch& l) {
+    using L = typename T::L; using A = typename T::A; using S = typename T::S;
+    constexpr int VB = 32;
+    Finish<A> fin = make_finish<A, S>(a.identity);
+    const size_t row_bytes = a.n * sizeof(L);
+    const int sms = sm_count();
+    if (row_bytes >= (size_t(32) << 10)) {
+        size_t grid = a.rows < size_t(sms) * 8 ? a.rows : size_t(sms) * 8;
+        rows_block_kernel<L, A, S, Op, VB, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
+            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin);
+        return cudaGetLastError();
+    }
+    const int G = pick_group(row_bytes);
+    const size_t rows_per_cta = size_t(kRowThreads / 32) * (32 / G);
+    size_t grid = (a.rows + rows_per_cta - 1) / rows_per_cta;
+    const size_t cap = size_t(sms) * 8;  // 8 x 256 threads = 2048 resident threads per SM
+    if (grid > cap) grid = cap;
+    if (grid == 0) grid = 1;
+    rows_group_kernel<L, A, S, Op, VB, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
+        (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rows(int red, int dtin, int dtout, const RowsArgs& a, const Launch& l) {
+    return dispatch_types(dtin, dtout, [&](auto t) -> cudaError_t {
+        using T = decltype(t);
+        using A = typename T::A;
+        return dispatch_op<A>(red, [&](auto op) -> cudaError_t {
+            using Op = decltype(op);
+            return launch_rows_t<T, Op>(a, l);
+        });
+    });
+}
+
+// ---------------------------------------------------------------------------
+// Fused row max + row sum: one read of the input for both outputs (softmax-
+// style pair, reference tests/softmax_test.py:8-31 runs them as two Reduce
+// nodes, i.e. two full passes).  fp32 accumulation for every input type.
+// ---------------------------------------------------------------------------
+template <class L, int VB, int U>
+__device__ __forceinline__ void span_max_sum(const L* __restrict__ p, size_t n, unsigned tid, unsigned nthr,
+                                             float& mx, float& sm) {
+    constexpr int N = VecInfo<L, VB>::N;
+    constexpr int NA = 4;
+    float amax[NA], asum[NA];
+#pragma unroll
+    for (int j = 0; j < NA; ++j) { amax[j] = OpMax<float>::neutral(); asum[j] = 0.f; }
+    const size_t addr = reinterpret_cast<size_t>(p);
+    size_t h = ((size_t(VB) - (addr & size_t(VB - 1))) & size_t(VB - 1)) / sizeof(L);
+    if (h > n) h = n;
+    for (size_t i = tid; i < h; i += nthr) {
+        float x = to_acc<float, L>(ldg_scalar(p + i));
+        amax[0] = fmaxf(amax[0], x); asum[0] += x;
+    }
+    const char* pv = reinterpret_cast<const char*>(p + h);
+    const size_t nvec = (n - h) / N;
+    size_t v = tid;
+    for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
+        Words<VB> w[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int j = 0; j < N; ++j) {
+                float x = vec_elem<L, float, VB>(w[u], j);
+                amax[j % NA] = fmaxf(amax[j % NA], x);
+                asum[j % NA] += x;
+            }
+    }
+    for (; v < nvec; v += nthr) {
+        Words<VB> w = ldg_stream<VB>(pv + v * VB);
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            float x = vec_elem<L, float, VB>(w, j);
+            amax[j % NA] = fmaxf(amax[j % NA], x);
+            asum[j % NA] += x;
+        }
+    }
+    for (size_t i = h + nvec * N + tid; i < n; i += nthr) {
+        float x = to_acc<float, L>(ldg_scalar(p + i));
+        amax[0] = fmaxf(amax[0], x); asum[0] += x;
+    }
+    mx = fmaxf(fmaxf(amax[0], amax[1]), fmaxf(amax[2], amax[3]));
+    sm = (asum[0] + asum[1]) + (asum[2] + asum[3]);
+}
+
+template <class L, int VB, int U>
+__global__ void __launch_bounds__(kRowThreads)
+rows_max_sum_kernel(const L* __restrict__ in, float* __restrict__ out_max, float* __restrict__ out_sum,
+                    size_t rows, size_t n, size_t row_stride, int G) {
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned g = lane & (G - 1);
+    const unsigned sub = lane / G;
+    const unsigned rows_per_warp = 32 / G;
+    const size_t warp = (size_t(blockIdx.x) * kRowThreads + threadIdx.x) >> 5;
+    const size_t nwarps = (size_t(gridDim.x) * kRowThreads) >> 5;
+    for (size_t rb = warp * rows_per_warp; rb < rows; rb += nwarps * rows_per_warp) {
+        const size_t r = rb + sub;
+        const bool active = r < rows;
+        float mx = OpMax<float>::neutral(), sm = 0.f;
+        if (active) span_max_sum<L, VB, U>(in + r * row_stride, n, g, G, mx, sm);
+        for (int m = G >> 1; m >= 1; m >>= 1) {
+            mx = fmaxf(mx, __shfl_xor_sync(kFullMask, mx, m));
+            sm += __shfl_xor_sync(kFullMask, sm, m);
+        }
+        if (active && g == 0) { out_max[r] = mx; out_sum[r] = sm; }
+    }
+}
+
+template <class L>
+static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& l) {
+    const int sms = sm_count();
+    const int G = pick_group(a.n * sizeof(L));
+    const size_t rows_per_cta = size_t(kRowThreads / 32) * (32 / G);
+    size_t grid = (a.rows + rows_per_cta - 1) / rows_per_cta;
+    const size_t cap = size_t(sms) * 8;
+    if (grid > cap) grid = cap;
+    if (grid == 0) grid = 1;
+    rows_max_sum_kernel<L, 32, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
+        (const L*)a.in, a.out_max, a.out_sum, a.rows, a.n, a.row_stride, G);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rows_max_sum(int dtin, const RowsMaxSumArgs& a, const Launch& l) {
+    switch (dtin) {
+        case DT_F32: return launch_rows_max_sum_t<float>(a, l);
+        case DT_BF16: return launch_rows_max_sum_t<__nv_bfloat16>(a, l);
+        case DT_F16: return launch_rows_max_sum_t<__half>(a, l);
+        default: return cudaErrorNotSupported;
+    }
+}
+
+}  // namespace db200

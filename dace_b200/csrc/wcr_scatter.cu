@@ -1,0 +1,295 @@
+// Write-conflict-resolution scatter (scatter-add / histogram) for sm_100a:
+//     bins[idx[i]] = op(bins[idx[i]], values ? values[i] : const_value)
+//
+// Replaces the code DaCe generates for a GPU map with a dynamic WCR memlet:
+// one thread per element, 32-thread blocks, one global atomic per element via
+// dace::wcr_fixed<...>::reduce_atomic (reference dace/codegen/targets/cpu.py:965-1013,
+// reference dace/runtime/include/dace/reduction.h:167-340; generated kernel shape
+// in SURVEY.md A.5), and the only privatisation primitive the reference has,
+// SharedToGlobal1D::Accum (reference dace/runtime/include/dace/cuda/copy.cuh:789-811).
+//
+// Two paths:
+//   * bins fit in shared memory (Sum): per-CTA privatised sub-histograms,
+//     replicated per warp group for small bin counts, warp-aggregated updates
+//     (match.any) when collisions inside a warp are likely, one flush of the
+//     non-zero bins with global reductions (RED, no return value);
+//   * otherwise: persistent grid, 128-bit index loads, U vectors in flight,
+//     RED.global straight into the (L2-resident) bin array, with a warp-uniform
+//     fast path that turns 32 equal keys into one reduction.
+// Out-of-range indices are skipped.  Integer results are bit-exact by
+// construction (integer addition is associative); float sums are atomics, so
+// order- and run-dependent in the last ulps like the reference's own.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace db200 {
+
+// ---- atomic "reduce into memory" for every (op, type) we support ----------
+template <class V> __device__ __forceinline__ void cas_apply_product(V* addr, V val) {
+    if constexpr (sizeof(V) == 4) {
+        unsigned* a = reinterpret_cast<unsigned*>(addr);
+        unsigned old = *a, assumed;
+        do {
+            assumed = old;
+            V cur = *reinterpret_cast<V*>(&assumed);
+            V nv = cur * val;
+            old = atomicCAS(a, assumed, *reinterpret_cast<unsigned*>(&nv));
+        } while (old != assumed);
+    } else {
+        unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+        unsigned long long old = *a, assumed;
+        do {
+            assumed = old;
+            V cur = *reinterpret_cast<V*>(&assumed);
+            V nv = cur * val;
+            old = atomicCAS(a, assumed, *reinterpret_cast<unsigned long long*>(&nv));
+        } while (old != assumed);
+    }
+}
+
+template <int RED, class V>
+__device__ __forceinline__ void atomic_reduce(V* addr, V val) {
+    if constexpr (RED == RT_Sum) {
+        if constexpr (std::is_same<V, long long>::value)
+            atomicAdd(reinterpret_cast<unsigned long long*>(addr), static_cast<unsigned long long>(val));
+        else
+            atomicAdd(addr, val);
+    } else if constexpr (RED == RT_Product) {
+        cas_apply_product<V>(addr, val);
+    } else if constexpr (RED == RT_Min || RED == RT_Max) {
+        if constexpr (std::is_same<V, float>::value) {
+            // NaN-free ordering trick: non-negative floats order like ints,
+            // negative floats order inversely like unsigned ints.
+            const bool nonneg = !(__float_as_uint(val) >> 31);
+            if (RED == RT_Max) {
+                if (nonneg) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(val));
+                else atomicMin(reinterpret_cast<unsigned*>(addr), __float_as_uint(val));
+            } else {
+                if (nonneg) atomicMin(reinterpret_cast<int*>(addr), __float_as_int(val));
+                else atomicMax(reinterpret_cast<unsigned*>(addr), __float_as_uint(val));
+            }
+        } else if constexpr (std::is_same<V, double>::value) {
+            const bool nonneg = !(static_cast<unsigned long long>(__double_as_longlong(val)) >> 63);
+            if (RED == RT_Max) {
+                if (nonneg) atomicMax(reinterpret_cast<long long*>(addr), __double_as_longlong(val));
+                else atomicMin(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)__double_as_longlong(val));
+            } else {
+                if (nonneg) atomicMin(reinterpret_cast<long long*>(addr), __double_as_longlong(val));
+                else atomicMax(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)__double_as_longlong(val));
+            }
+        } else {
+            if (RED == RT_Max) atomicMax(addr, val); else atomicMin(addr, val);
+        }
+    } else if constexpr (std::is_integral<V>::value) {
+        using U = typename std::conditional<sizeof(V) == 4, unsigned, unsigned long long>::type;
+        U* a = reinterpret_cast<U*>(addr);
+        U u = static_cast<U>(val);
+        if constexpr (RED == RT_BAnd) atomicAnd(a, u);
+        else if constexpr (RED == RT_BOr) atomicOr(a, u);
+        else atomicXor(a, u);
+    }
+}
+
+template <class I> __device__ __forceinline__ long long idx_at(const Words<16>& w, int j) {
+    return (long long)vec_elem<I, I, 16>(w, j);
+}
+
+// ---- global path ----------------------------------------------------------
+template <int RED, class I, class V, bool HAS_VALUES, int U>
+__global__ void __launch_bounds__(512)
+scatter_global_kernel(const I* __restrict__ idx, const V* __restrict__ values, V cval, size_t n,
+                      V* __restrict__ bins, size_t nbins) {
+    const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t nthr = size_t(gridDim.x) * blockDim.x;
+    if constexpr (HAS_VALUES) {
+        for (size_t i = tid; i < n; i += nthr) {
+            long long k = (long long)ldg_scalar(idx + i);
+            V v = ldg_scalar(values + i);
+            if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(bins + k, v);
+        }
+    } else {
+        constexpr int N = 16 / int(sizeof(I));
+        const size_t addr = reinterpret_cast<size_t>(idx);
+        size_t h = ((16 - (addr & 15)) & 15) / sizeof(I);
+        if (h > n) h = n;
+        const char* pv = reinterpret_cast<const char*>(idx + h);
+        const size_t nvec = (n - h) / N;
+        size_t v = tid;
+        for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
+            Words<16> w[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) w[u] = ldg_stream16(pv + (v + size_t(u) * nthr) * 16);
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    long long k = idx_at<I>(w[u], j);
+                    if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(bins + k, cval);
+                }
+        }
+        for (; v < nvec; v += nthr) {
+            Words<16> w = ldg_stream16(pv + v * 16);
+#pragma unroll
+            for (int j = 0; j < N; ++j) {
+                long long k = idx_at<I>(w, j);
+                if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(bins + k, cval);
+            }
+        }
+        for (size_t i = tid; i < h; i += nthr) {
+            long long k = (long long)ldg_scalar(idx + i);
+            if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(bins + k, cval);
+        }
+        for (size_t i = h + nvec * N + tid; i < n; i += nthr) {
+            long long k = (long long)ldg_scalar(idx + i);
+            if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(bins + k, cval);
+        }
+    }
+}
+
+// ---- shared-memory privatised path (Sum only) ------------------------------
+template <class V, bool AGG, bool HAS_VALUES>
+__device__ __forceinline__ void smem_add(V* hist, long long k, size_t nbins, V val) {
+    const bool ok = k >= 0 && (size_t)k < nbins;
+    if constexpr (AGG && std::is_integral<V>::value) {
+        // Warp-aggregated: lanes with the same key elect a leader that adds the group's total.
+        const unsigned active = __ballot_sync(kFullMask, ok);
+        if (ok) {
+            const unsigned peers = __match_any_sync(active, k);
+            const int leader = __ffs(peers) - 1;
+            // Constant increments aggregate to val * popc; per-lane values need a segmented sum.
+            V total = val;
+            if constexpr (!HAS_VALUES) {
+                total = val * V(__popc(peers));
+            } else if (__popc(peers) > 1) {
+                total = V(0);
+                unsigned rest = peers;
+                while (rest) {
+                    int src = __ffs(rest) - 1;
+                    total += __shfl_sync(peers, val, src);
+                    rest &= rest - 1;
+                }
+            }
+            if ((int)(threadIdx.x & 31) == leader) atomic_reduce<RT_Sum, V>(hist + k, total);
+        }
+    } else {
+        if (ok) atomic_reduce<RT_Sum, V>(hist + k, val);
+    }
+}
+
+template <class I, class V, bool HAS_VALUES, bool AGG>
+__global__ void __launch_bounds__(512)
+scatter_smem_kernel(const I* __restrict__ idx, const V* __restrict__ values, V cval, size_t n,
+                    V* __restrict__ bins, size_t nbins, int copies) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    V* hist = reinterpret_cast<V*>(smem_raw);
+    const size_t total = nbins * copies;
+    for (size_t i = threadIdx.x; i < total; i += blockDim.x) hist[i] = V(0);
+    __syncthreads();
+    V* mine = hist + size_t((threadIdx.x >> 5) % copies) * nbins;
+
+    const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t nthr = size_t(gridDim.x) * blockDim.x;
+    // Round the trip count up so that whole warps stay converged for match/shfl.
+    const size_t iters = (n + nthr - 1) / nthr;
+    for (size_t it = 0; it < iters; ++it) {
+        const size_t i = it * nthr + tid;
+        long long k = -1;
+        V v = cval;
+        if (i < n) {
+            k = (long long)ldg_scalar(idx + i);
+            if constexpr (HAS_VALUES) v = ldg_scalar(values + i);
+        }
+        smem_add<V, AGG, HAS_VALUES>(mine, k, nbins, v);
+    }
+    __syncthreads();
+    for (size_t b = threadIdx.x; b < nbins; b += blockDim.x) {
+        V s = hist[b];
+        for (int c = 1; c < copies; ++c) s += hist[size_t(c) * nbins + b];
+        if (s != V(0)) atomic_reduce<RT_Sum, V>(bins + b, s);
+    }
+}
+
+template <int RED, class I, class V>
+static cudaError_t launch_scatter_t(const ScatterArgs& a, const Launch& l) {
+    const int sms = sm_count();
+    V cval = V(1);
+    if (a.const_value) memcpy(&cval, a.const_value, sizeof(V));
+    if (a.n == 0) return cudaSuccess;
+    const size_t hist_bytes = a.nbins * sizeof(V);
+    if (RED == RT_Sum && hist_bytes <= (size_t(96) << 10) && a.n >= (size_t(1) << 14)) {
+        int copies = int((size_t(96) << 10) / hist_bytes);
+        if (copies > 16) copies = 16;
+        if (copies < 1) copies = 1;
+        const size_t smem = hist_bytes * copies;
+        const bool agg = a.nbins <= 1024 && std::is_integral<V>::value;
+        size_t grid = size_t(sms) * 2;
+        const size_t need = (a.n + 511) / 512;
+        if (grid > need) grid = need;
+        cudaError_t e;
+#define DB200_SMEM_LAUNCH(HV, AG)                                                                          \
+        e = cudaFuncSetAttribute(scatter_smem_kernel<I, V, HV, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                 (int)(size_t(96) << 10));                                                 \
+        if (e != cudaSuccess) return e;                                                                    \
+        scatter_smem_kernel<I, V, HV, AG><<<(unsigned)grid, 512, smem, l.stream>>>(                        \
+            (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins, copies);
+        if (a.values) { if (agg) { DB200_SMEM_LAUNCH(true, true) } else { DB200_SMEM_LAUNCH(true, false) } }
+        else          { if (agg) { DB200_SMEM_LAUNCH(false, true) } else { DB200_SMEM_LAUNCH(false, false) } }
+#undef DB200_SMEM_LAUNCH
+        return cudaGetLastError();
+    }
+    size_t grid = size_t(sms) * 4;
+    const size_t need = (a.n + 511) / 512;
+    if (grid > need) grid = need;
+    if (a.values)
+        scatter_global_kernel<RED, I, V, true, 4><<<(unsigned)grid, 512, 0, l.stream>>>(
+            (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins);
+    else
+        scatter_global_kernel<RED, I, V, false, 4><<<(unsigned)grid, 512, 0, l.stream>>>(
+            (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins);
+    return cudaGetLastError();
+}
+
+template <class I, class V>
+static cudaError_t launch_scatter_op(int red, const ScatterArgs& a, const Launch& l) {
+    switch (red) {
+        case RT_Sum: return launch_scatter_t<RT_Sum, I, V>(a, l);
+        case RT_Min: return launch_scatter_t<RT_Min, I, V>(a, l);
+        case RT_Max: return launch_scatter_t<RT_Max, I, V>(a, l);
+        case RT_Product: return launch_scatter_t<RT_Product, I, V>(a, l);
+        default: break;
+    }
+    if constexpr (std::is_integral<V>::value) {
+        switch (red) {
+            case RT_BAnd: return launch_scatter_t<RT_BAnd, I, V>(a, l);
+            case RT_BOr: return launch_scatter_t<RT_BOr, I, V>(a, l);
+            case RT_BXor: return launch_scatter_t<RT_BXor, I, V>(a, l);
+            default: break;
+        }
+    }
+    return cudaErrorNotSupported;
+}
+
+template <class I>
+static cudaError_t launch_scatter_val(int red, int dtval, const ScatterArgs& a, const Launch& l) {
+    switch (dtval) {
+        case DT_I32: return launch_scatter_op<I, int>(red, a, l);
+        case DT_U32: return launch_scatter_op<I, unsigned>(red, a, l);
+        case DT_I64: return launch_scatter_op<I, long long>(red, a, l);
+        case DT_U64: return launch_scatter_op<I, unsigned long long>(red, a, l);
+        case DT_F32: return launch_scatter_op<I, float>(red, a, l);
+        case DT_F64: return launch_scatter_op<I, double>(red, a, l);
+        default: return cudaErrorNotSupported;
+    }
+}
+
+cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l) {
+    switch (dtidx) {
+        case DT_I32: return launch_scatter_val<int>(red, dtval, a, l);
+        case DT_U32: return launch_scatter_val<unsigned>(red, dtval, a, l);
+        case DT_I64: return launch_scatter_val<long long>(red, dtval, a, l);
+        case DT_U8: return launch_scatter_val<unsigned char>(red, dtval, a, l);
+        default: return cudaErrorNotSupported;
+    }
+}
+
+}  // namespace db200

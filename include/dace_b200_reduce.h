@@ -1,0 +1,167 @@
+/* dace_b200_reduce.h - C ABI of the B200 (sm_100a) reduction backend for DaCe.
+ *
+ * This is the drop-in boundary: the functions below are what a DaCe-generated
+ * program (host C++ tasklet inside __program_<sdfg>, reference
+ * dace/codegen/compiled_sdfg.py:549-592) calls instead of the per-node helper the
+ * reference's `CUDA (device)` expansion generates,
+ *
+ *     cudaError_t __dace_reduce_<sdfg>_<state>_<node>(T_in *input, T_out *output,
+ *                                                     size_t num_items | size_t num_segments,
+ *                                                     size_t segment_size, cudaStream_t stream);
+ *                     (reference dace/libraries/standard/nodes/reduce.py:574-588)
+ *
+ * and instead of the generated GPU map kernels that resolve write conflicts
+ * with one global atomic per element (reference dace/codegen/targets/cpu.py:965-1013).
+ *
+ * Conventions (same as the reference's, reference dace/runtime/include/dace/cuda/cudacommon.cuh:28-83):
+ *   - every entry point returns a cudaError_t value as int (0 = cudaSuccess), so
+ *     the call site can stay wrapped in DACE_GPU_CHECK(...);
+ *   - work is enqueued on `stream` and never synchronises the stream or device;
+ *   - `in`, `out`, `bins`... are device (or pinned, device-mapped) pointers owned
+ *     by the caller, already offset to the memlet start; nothing is retained;
+ *   - unsupported (op, dtype) combinations return cudaErrorNotSupported (801),
+ *     malformed arguments cudaErrorInvalidValue (1); nothing throws or exits;
+ *   - there is no CPU fallback anywhere behind this interface.
+ *
+ * Plain C, no torch / DaCe types in any signature.
+ */
+#ifndef DACE_B200_REDUCE_H
+#define DACE_B200_REDUCE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define DACE_B200_API __declspec(dllexport)
+#else
+#define DACE_B200_API __attribute__((visibility("default")))
+#endif
+
+/* Same handle type as cudaStream_t (struct CUstream_st *). */
+typedef struct CUstream_st* dace_b200_stream_t;
+
+/* Reduction operator; numeric values mirror dace::ReductionType
+ * (reference dace/runtime/include/dace/types.h:301-317, dace/dtypes.py:93-113). */
+enum dace_b200_redtype {
+    DACE_B200_CUSTOM = 0, /* not supported by the precompiled library */
+    DACE_B200_MIN = 1,
+    DACE_B200_MAX = 2,
+    DACE_B200_SUM = 3,
+    DACE_B200_PRODUCT = 4,
+    DACE_B200_LOGICAL_AND = 5,
+    DACE_B200_BITWISE_AND = 6,
+    DACE_B200_LOGICAL_OR = 7,
+    DACE_B200_BITWISE_OR = 8,
+    DACE_B200_LOGICAL_XOR = 9,
+    DACE_B200_BITWISE_XOR = 10
+};
+
+/* Element types. Supported (in -> out) pairs: T -> T for every type below, plus
+ * bf16 -> f32 and f16 -> f32 (fp32 accumulation in all four 16-bit cases). */
+enum dace_b200_dtype {
+    DACE_B200_F32 = 0,
+    DACE_B200_F64 = 1,
+    DACE_B200_I32 = 2,
+    DACE_B200_I64 = 3,
+    DACE_B200_U32 = 4,
+    DACE_B200_U64 = 5,
+    DACE_B200_BF16 = 6,
+    DACE_B200_F16 = 7,
+    DACE_B200_I8 = 8,
+    DACE_B200_U8 = 9,
+    DACE_B200_I16 = 10,
+    DACE_B200_U16 = 11
+};
+
+#define DACE_B200_MAX_DIMS 12
+
+/* Library/ABI version (major * 1000 + minor). */
+DACE_B200_API int dace_b200_version(void);
+
+/* Human-readable name of a returned status (cudaGetErrorString). */
+DACE_B200_API const char* dace_b200_status_string(int status);
+
+/* ---- Workspace ---------------------------------------------------------
+ * Cross-CTA combining uses a small device workspace (ticket counters +
+ * partials).  Mirrors the reference's CUB temp-storage protocol: query the size,
+ * cudaMalloc once in __dace_init_cuda, cudaFree in __dace_exit_cuda
+ * (reference dace/libraries/standard/nodes/reduce.py:550-570).  The workspace
+ * must be zero-initialised once with dace_b200_workspace_init(); kernels leave
+ * it clean.  Passing workspace == NULL selects a per-device default workspace the
+ * library allocates on first use (not safe for concurrent use from several
+ * streams; generated code passes its own).  One workspace serves one stream at
+ * a time. */
+DACE_B200_API size_t dace_b200_workspace_bytes(void);
+DACE_B200_API int dace_b200_workspace_init(void* workspace, size_t workspace_bytes, dace_b200_stream_t stream);
+
+/* ---- Reduce library node -------------------------------------------------
+ * General N-D entry, the call the `B200` expansion of
+ * dace.libraries.standard.Reduce emits.  Semantics of the node
+ * (reference dace/libraries/standard/nodes/reduce.py:1346-1411):
+ *     out[kept...] = fold(op, identity, in[kept..., reduced...])
+ * `shape`/`in_strides` describe the input memlet subset (ndim entries, strides
+ * in elements, any order/steps).  Bit i of `reduce_mask` marks axis i as reduced
+ * (all axes: (1<<ndim)-1).  `out_strides` has one entry per KEPT axis in axis
+ * order (NULL = C-contiguous).  `identity` is a HOST pointer to one value of
+ * dtype_out, or NULL meaning "fold into the value already stored in out"
+ * (reference dace/frontend/operations.py:251).  With no reduced axis of extent
+ * > 1 the call is a strided copy, identity ignored (reference reduce.py:77-87).
+ * Replaces: reduce.py:574-588 (CUB), :984-1332 (GPUAuto kernels). */
+DACE_B200_API int dace_b200_reduce_nd(int redtype, int dtype_in, int dtype_out, const void* in, void* out, int ndim,
+                                      const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,
+                                      uint32_t reduce_mask, const void* identity, void* workspace,
+                                      size_t workspace_bytes, dace_b200_stream_t stream);
+
+/* All axes reduced, contiguous input: replaces
+ * cub::DeviceReduce::Reduce(storage, ssize, in, out, num_items, op, identity, stream)
+ * (reference reduce.py:520-525). */
+DACE_B200_API int dace_b200_reduce_full(int redtype, int dtype_in, int dtype_out, const void* in, void* out,
+                                        size_t num_items, const void* identity, void* workspace,
+                                        size_t workspace_bytes, dace_b200_stream_t stream);
+
+/* Trailing axes reduced: num_segments contiguous segments of segment_size
+ * elements, segment s starting at in + s*segment_stride (pass segment_size for a
+ * dense array).  Replaces cub::DeviceSegmentedReduce::Reduce with
+ * dace::stridedIterator offsets (reference reduce.py:526-544). */
+DACE_B200_API int dace_b200_reduce_rows(int redtype, int dtype_in, int dtype_out, const void* in, void* out,
+                                        size_t num_segments, size_t segment_size, size_t segment_stride,
+                                        const void* identity, void* workspace, size_t workspace_bytes,
+                                        dace_b200_stream_t stream);
+
+/* Middle/leading axis reduced: in[outer][reduced][inner] (dense, inner
+ * contiguous) -> out[outer][inner].  Replaces the GPUAuto strided schedule
+ * (reference reduce.py:1141-1332); the CUB expansion has no equivalent
+ * (reference reduce.py:493-496). */
+DACE_B200_API int dace_b200_reduce_cols(int redtype, int dtype_in, int dtype_out, const void* in, void* out,
+                                        size_t outer, size_t reduced, size_t inner, const void* identity,
+                                        void* workspace, size_t workspace_bytes, dace_b200_stream_t stream);
+
+/* Fused row max + row sum in a single pass over `in` (two Reduce nodes sharing
+ * an input, as in reference tests/softmax_test.py:8-31).  dtype_in: f32, bf16
+ * or f16; outputs fp32; identities -inf / 0. */
+DACE_B200_API int dace_b200_reduce_rows_max_sum(int dtype_in, const void* in, float* out_max, float* out_sum,
+                                                size_t num_segments, size_t segment_size, size_t segment_stride,
+                                                dace_b200_stream_t stream);
+
+/* ---- WCR map reductions (scatter-add / histogram) ---------------------------
+ *     bins[idx[i]] = op(bins[idx[i]], values ? values[i] : *const_value)   i in [0, n)
+ * Replaces the generated one-thread-per-element kernel whose body is
+ * dace::wcr_fixed<op, T>::reduce_atomic(bins + k, v)
+ * (reference dace/codegen/targets/cpu.py:965-1013,
+ *  reference dace/runtime/include/dace/reduction.h:167-340).  `bins` is updated in
+ * place (WCR semantics: it is the caller's job to initialise it).  dtype_idx:
+ * i32, u32, i64, u8; dtype_val (= bins type): i32, u32, i64, u64, f32, f64.
+ * `values` may be NULL, then `const_value` (HOST pointer, dtype_val; NULL = 1) is
+ * applied for every index.  Indices outside [0, nbins) are skipped. */
+DACE_B200_API int dace_b200_wcr_scatter(int redtype, int dtype_idx, int dtype_val, const void* idx,
+                                        const void* values, const void* const_value, size_t n, void* bins,
+                                        size_t nbins, dace_b200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DACE_B200_REDUCE_H */

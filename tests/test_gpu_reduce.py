@@ -1,0 +1,337 @@
+"""GPU parity: the sm_100a kernels (through the C ABI) against the CPU oracle.
+
+Cases follow the reference's own tests: the shape/axes list of reference
+tests/library/reduce_test.py:52-79, the dtypes/ops of reference
+tests/numpy/reductions_test.py, exact max with explicit identity
+(reference tests/wcr_cudatest.py:31-65), sub-range / offset memlets
+(reference tests/reduce_offsets_test.py:26-66, tests/library/reduce_test.py:31-49).
+Bar: bit-exact for integers, <= 1e-5 relative (fp32) against the fp64-accumulated
+oracle, exact for min/max.
+"""
+import numpy as np
+import pytest
+import torch
+
+import dace_b200 as db
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+RTOL_F32 = 1e-5   # north_star: fp32 <= 1e-5 against an fp64 host reference
+RTOL_F64 = 1e-12
+
+_OPS = {'sum': (O.SUM, 'lambda a, b: a + b', 0), 'prod': (O.PRODUCT, 'lambda a, b: a * b', 1),
+        'max': (O.MAX, 'lambda a, b: max(a, b)', None), 'min': (O.MIN, 'lambda a, b: min(a, b)', None),
+        'band': (O.BAND, 'lambda a, b: a & b', -1), 'bor': (O.BOR, 'lambda a, b: a | b', 0),
+        'bxor': (O.BXOR, 'lambda a, b: a ^ b', 0), 'land': (O.LAND, 'lambda a, b: a and b', 1),
+        'lor': (O.LOR, 'lambda a, b: a or b', 0), 'lxor': (O.LXOR, 'lambda a, b: a != b', 0)}
+
+
+def _identity(op, dtype):
+    ident = _OPS[op][2]
+    if ident is not None:
+        return ident
+    if np.issubdtype(dtype, np.floating):
+        info = np.finfo(dtype)
+    else:
+        info = np.iinfo(dtype)
+    return info.min if op == 'max' else info.max   # dace.dtypes.min_value/max_value (reference dtypes.py:426-449)
+
+
+def _data(rng, shape, dtype, op='sum'):
+    if np.issubdtype(dtype, np.floating):
+        if op == 'prod':
+            return rng.uniform(0.9, 1.1, shape).astype(dtype)
+        return rng.uniform(-10, 10, shape).astype(dtype)   # reference tests/numpy/common.py:16-120
+    if op == 'prod':
+        return rng.integers(-3, 4, shape).astype(dtype)
+    lo = 0 if np.issubdtype(dtype, np.unsignedinteger) else -10
+    return rng.integers(lo, 10, shape).astype(dtype)
+
+
+def _check(got, ref, dtype, a=None, axes=None, op='sum'):
+    if np.issubdtype(dtype, np.floating) and op in ('sum', 'prod'):
+        rtol = RTOL_F32 if dtype == np.float32 else RTOL_F64
+        if op == 'sum' and a is not None:
+            # relative to the magnitude of the summed data (cancellation-safe)
+            scale = np.abs(a.astype(np.float64)).sum(axis=axes)
+            assert np.all(np.abs(got.astype(np.float64) - ref.astype(np.float64)) <= rtol * np.maximum(scale, 1e-30))
+        else:
+            np.testing.assert_allclose(got, ref, rtol=rtol * 10)
+    else:
+        np.testing.assert_array_equal(got, ref)
+
+
+def _run(a, axes, op, cuda, identity='default', out_init=None):
+    red, lam, _ = _OPS[op]
+    ident = _identity(op, a.dtype) if identity == 'default' else identity
+    ta = torch.from_numpy(a).to(cuda)
+    if out_init is None:
+        got = db.reduce(lam, ta, axis=axes, identity=ident).cpu().numpy()
+        ref = O.reduce(red, a, axes, identity=ident, wide=True)
+    else:
+        to = torch.from_numpy(out_init.copy()).to(cuda)
+        db.reduce(lam, ta, to, axis=axes, identity=ident)
+        got = to.cpu().numpy()
+        ref = out_init.copy()
+        O.reduce(red, a, axes, identity=ident, out=ref, wide=True)
+    return got, ref
+
+
+# The parametrize list of reference tests/library/reduce_test.py:53-58 (sizes kept).
+REF_CASES = [
+    ([8, 512, 4096], (0, 1), np.float32), ([8, 512, 4096], (0, 1), np.float64),
+    ([1024, 8], (0, ), np.float32), ([1000000], (0, ), np.float64), ([1111111], (0, ), np.float64),
+    ([123, 21, 26, 8], (1, 2), np.float32), ([2, 512, 2], (0, 2), np.float32),
+    ([512, 555, 257], (0, 2), np.float64), ([17, 255, 12], (1, ), np.float32),
+    ([64, 1024], (1, ), np.float32), ([512, 1024], (1, ), np.float64),
+]
+
+
+@pytest.mark.parametrize('shape,axes,dtype', REF_CASES)
+def test_reference_case_list_sum(shape, axes, dtype, cuda):
+    rng = np.random.default_rng(42)
+    a = rng.random(shape).astype(dtype)   # reference reduce_test.py:64 uses np.random.rand
+    got, ref = _run(a, axes, 'sum', cuda)
+    _check(got, ref, dtype, a, axes)
+    np.testing.assert_allclose(got, np.sum(a, axis=axes), rtol=1e-5 if dtype == np.float32 else 1e-10)
+
+
+@pytest.mark.parametrize('dtype', [np.float32, np.float64, np.int32, np.int64, np.uint32, np.uint64, np.int8,
+                                   np.uint8, np.int16, np.uint16])
+@pytest.mark.parametrize('op', ['sum', 'prod', 'max', 'min'])
+@pytest.mark.parametrize('shape,axes', [([4097], None), ([33, 1000], (1, )), ([1000, 33], (0, )),
+                                        ([5, 300, 7], (1, )), ([6, 50, 9], (0, 2))])
+def test_ops_dtypes_layouts(dtype, op, shape, axes, cuda):
+    rng = np.random.default_rng(1)
+    a = _data(rng, shape, dtype, op)
+    got, ref = _run(a, axes, op, cuda)
+    _check(got, ref, dtype, a, axes, op)
+
+
+@pytest.mark.parametrize('dtype', [np.int32, np.int64, np.uint32, np.uint8])
+@pytest.mark.parametrize('op', ['band', 'bor', 'bxor', 'land', 'lor', 'lxor'])
+def test_bitwise_logical(dtype, op, cuda):
+    rng = np.random.default_rng(2)
+    for shape, axes in [([5000], None), ([37, 129], (1, )), ([129, 37], (0, ))]:
+        if op.startswith('l'):
+            a = rng.integers(0, 2, shape).astype(dtype)
+        else:
+            a = rng.integers(0, 127, shape).astype(dtype)
+        ident = _OPS[op][2]
+        if ident == -1:
+            ident = np.array(-1).astype(dtype, casting='unsafe').item() if np.issubdtype(dtype, np.signedinteger) \
+                else np.iinfo(dtype).max
+        got, ref = _run(a, axes, op, cuda, identity=ident)
+        np.testing.assert_array_equal(got, ref)
+
+
+@pytest.mark.parametrize('n', [0, 1, 2, 7, 8, 9, 31, 255, 256, 257, 4095, 65536 + 3, (1 << 20) + 5, (1 << 24) + 1])
+def test_full_sum_sizes_and_alignment(n, cuda):
+    """Ragged sizes and every start alignment (memlet offsets move `_in` anywhere)."""
+    rng = np.random.default_rng(3)
+    base = rng.uniform(-1, 1, n + 16).astype(np.float32)
+    tb = torch.from_numpy(base).to(cuda)
+    for off in (0, 1, 3, 5, 8):
+        a = base[off:off + n]
+        got = db.reduce('lambda a, b: a + b', tb[off:off + n], axis=None, identity=0).cpu().numpy()
+        ref = O.reduce(O.SUM, a, None, identity=0, wide=True)
+        _check(got, ref, np.float32, a, None)
+
+
+def test_full_int_exact_large(cuda):
+    rng = np.random.default_rng(4)
+    a = rng.integers(-1000, 1000, (1 << 24) + 77, dtype=np.int32)
+    got, ref = _run(a, None, 'sum', cuda)
+    np.testing.assert_array_equal(got, ref)
+    a64 = rng.integers(-10**12, 10**12, (1 << 22) + 3, dtype=np.int64)
+    for op in ('sum', 'max', 'min'):
+        got, ref = _run(a64, None, op, cuda)
+        np.testing.assert_array_equal(got, ref)
+
+
+def test_wcr_cudatest_exact_max(cuda):
+    """reference tests/wcr_cudatest.py:31-65: max with identity -999999, exact."""
+    a = np.random.default_rng(5).random(10).astype(np.float32)
+    got, ref = _run(a, None, 'max', cuda, identity=-999999)
+    assert got == ref == a.max()
+
+
+def test_identity_none_accumulates(cuda):
+    """identity=None folds into the existing output (reference operations.py:251)."""
+    rng = np.random.default_rng(6)
+    a = rng.integers(-10, 10, (40, 50)).astype(np.int64)
+    init = rng.integers(-5, 5, 40).astype(np.int64)
+    got, ref = _run(a, (1, ), 'sum', cuda, identity=None, out_init=init)
+    np.testing.assert_array_equal(got, ref)
+    np.testing.assert_array_equal(got, init + a.sum(1))
+    got, ref = _run(a, (0, ), 'max', cuda, identity=None, out_init=np.full(50, 3, np.int64))
+    np.testing.assert_array_equal(got, np.maximum(3, a.max(0)))
+    got, ref = _run(a.reshape(-1), None, 'sum', cuda, identity=None, out_init=np.array(7, np.int64))
+    assert got == 7 + a.sum()
+
+
+def test_nonneutral_identity(cuda):
+    a = np.arange(24, dtype=np.int32).reshape(4, 6)
+    got, ref = _run(a, (1, ), 'sum', cuda, identity=100)
+    np.testing.assert_array_equal(got, 100 + a.sum(1))
+    np.testing.assert_array_equal(got, ref)
+
+
+def test_offsets_and_subranges(cuda):
+    """reference tests/reduce_offsets_test.py:26-66: A[25:50, 13:20] -> B[4:11]."""
+    rng = np.random.default_rng(7)
+    A = rng.random((50, 50))
+    B = rng.random(25)
+    tA, tB = torch.from_numpy(A).to(cuda), torch.from_numpy(B.copy()).to(cuda)
+    db.reduce('lambda a, b: a + b', tA[25:50, 13:20], tB[4:11], axis=0, identity=0)
+    exp = B.copy()
+    exp[4:11] = A[25:50, 13:20].sum(0)
+    np.testing.assert_allclose(tB.cpu().numpy(), exp, rtol=1e-12)
+    ref = B.copy()
+    O.reduce(O.SUM, A[25:50, 13:20], (0, ), identity=0, out=ref[4:11], wide=True)
+    np.testing.assert_allclose(tB.cpu().numpy(), ref, rtol=1e-12)
+    # no-identity max into a sub-range
+    tB2 = torch.from_numpy(B.copy()).to(cuda)
+    db.reduce('lambda a, b: max(a, b)', tA[25:50, 13:20], tB2[4:11], axis=0, identity=None)
+    exp = B.copy()
+    exp[4:11] = np.maximum(B[4:11], A[25:50, 13:20].max(0))
+    np.testing.assert_array_equal(tB2.cpu().numpy(), exp)
+
+
+def test_strided_memlet_5d(cuda):
+    """reference tests/library/reduce_test.py:31-49: A[0:N,0,0,0:Cin,0:Cout] -> C[0:N,5,5,0:Cout]."""
+    rng = np.random.default_rng(8)
+    A = rng.random((3, 4, 4, 6, 5)).astype(np.float32)
+    C = np.zeros((3, 8, 8, 5), np.float32)
+    tA, tC = torch.from_numpy(A).to(cuda), torch.from_numpy(C).to(cuda)
+    db.reduce('lambda a, b: a + b', tA[:, 0, 0, :, :], tC[:, 5, 5, :], axis=1, identity=0)
+    exp = C.copy()
+    exp[:, 5, 5, :] = A[:, 0, 0].sum(1)
+    np.testing.assert_allclose(tC.cpu().numpy(), exp, rtol=1e-5)
+
+
+def test_transposed_and_stepped_views(cuda):
+    rng = np.random.default_rng(9)
+    A = rng.integers(-50, 50, (64, 48, 10)).astype(np.int32)
+    tA = torch.from_numpy(A).to(cuda)
+    for view_np, view_t, axes in [(A.transpose(2, 0, 1), tA.permute(2, 0, 1), (1, )),
+                                  (A[::2, ::3], tA[::2, ::3], (0, 1)),
+                                  (A[:, :, ::2], tA[:, :, ::2], (2, )),
+                                  (A.transpose(1, 0, 2), tA.permute(1, 0, 2), None)]:
+        got = db.reduce('lambda a, b: a + b', view_t, axis=axes, identity=0).cpu().numpy()
+        ref = O.reduce(O.SUM, view_np, axes, identity=0)
+        np.testing.assert_array_equal(got, ref)
+        np.testing.assert_array_equal(got, view_np.sum(axis=axes))
+
+
+def test_degenerate_and_empty(cuda):
+    a = np.arange(12, dtype=np.float32).reshape(3, 1, 4)
+    ta = torch.from_numpy(a).to(cuda)
+    got = db.reduce('lambda a, b: a + b', ta, axis=1, identity=5).cpu().numpy()   # copy, identity ignored
+    np.testing.assert_array_equal(got, a[:, 0, :])
+    np.testing.assert_array_equal(got, O.reduce(O.SUM, a, (1, ), identity=5))
+    e = torch.empty((4, 0), dtype=torch.float32, device=cuda)
+    got = db.reduce('lambda a, b: a + b', e, axis=1, identity=2.5).cpu().numpy()
+    np.testing.assert_array_equal(got, np.full(4, 2.5, np.float32))
+    e2 = torch.empty((0, 4), dtype=torch.float32, device=cuda)
+    assert db.reduce('lambda a, b: a + b', e2, axis=1, identity=0).numel() == 0
+
+
+@pytest.mark.parametrize('rows,n', [(1, 1 << 22), (3, (1 << 20) + 17), (70, 40000), (500, 9000), (4096, 4096),
+                                    (10000, 100), (100000, 8), (7, 3), (65536, 33)])
+def test_rows_all_decompositions(rows, n, cuda):
+    """Every row-kernel regime: sub-warp groups, warp, CTA per row, split rows."""
+    rng = np.random.default_rng(10)
+    a = rng.uniform(-1, 1, (rows, n)).astype(np.float32)
+    for op in ('sum', 'max'):
+        got, ref = _run(a, (1, ), op, cuda)
+        _check(got, ref, np.float32, a, (1, ), op)
+    ai = rng.integers(-100, 100, (rows, n)).astype(np.int32)
+    got, ref = _run(ai, (1, ), 'sum', cuda)
+    np.testing.assert_array_equal(got, ref)
+
+
+@pytest.mark.parametrize('outer,red,inner', [(1, 1 << 16, 4096), (1, 100000, 8), (1, 5000, 1), (3, 1000, 24),
+                                             (123, 546, 8), (1, 64, 100000), (2, 7, 5), (1, 33000, 257),
+                                             (9, 2000, 264), (5000, 16, 16)])
+def test_cols_all_decompositions(outer, red, inner, cuda):
+    rng = np.random.default_rng(11)
+    a = rng.uniform(-1, 1, (outer, red, inner)).astype(np.float32)
+    got, ref = _run(a, (1, ), 'sum', cuda)
+    _check(got, ref, np.float32, a, (1, ))
+    ai = rng.integers(-100, 100, (outer, red, inner)).astype(np.int64)
+    for op in ('sum', 'min'):
+        got, ref = _run(ai, (1, ), op, cuda)
+        np.testing.assert_array_equal(got, ref)
+
+
+def test_bf16_f16_fp32_accumulate(cuda):
+    """bf16/f16 inputs, fp32 accumulation and fp32 outputs; sum of 128 ones == 128
+    (reference tests/fp8_bf16_dtypes_test.py:130-150)."""
+    rng = np.random.default_rng(12)
+    ones = torch.ones(128, dtype=torch.bfloat16, device=cuda)
+    out = torch.zeros((), dtype=torch.float32, device=cuda)
+    db.reduce('lambda a, b: a + b', ones, out, axis=None, identity=0)
+    assert out.item() == 128.0
+    assert db.reduce('lambda a, b: a + b', ones, axis=None, identity=0).float().item() == 128.0
+    x = rng.standard_normal((300, 1000)).astype(np.float32)
+    bits = O.f32_to_bf16_bits(x)
+    tx = torch.from_numpy(bits.view(np.int16)).to(cuda).view(torch.bfloat16)
+    for axes, shape in (((1, ), 300), ((0, ), 1000), (None, ())):
+        for red, lam, ident in ((O.SUM, 'lambda a, b: a + b', 0), (O.MAX, 'lambda a, b: max(a, b)', -3e38)):
+            out = torch.empty(shape, dtype=torch.float32, device=cuda)
+            db.reduce(lam, tx, out, axis=axes, identity=ident)
+            ref = O.reduce(red, bits, axes, identity=ident, in_bf16=True, out_dtype=np.float32, wide=True)
+            if red == O.SUM:
+                scale = np.abs(O.bf16_bits_to_f32(bits).astype(np.float64)).sum(axis=axes)
+                assert np.all(np.abs(out.cpu().numpy().astype(np.float64) - ref) <= RTOL_F32 * scale)
+            else:
+                np.testing.assert_array_equal(out.cpu().numpy(), ref)
+    h = rng.standard_normal((64, 512)).astype(np.float16)
+    th = torch.from_numpy(h).to(cuda)
+    out = torch.empty(64, dtype=torch.float32, device=cuda)
+    db.reduce('lambda a, b: a + b', th, out, axis=1, identity=0)
+    np.testing.assert_allclose(out.cpu().numpy(), h.astype(np.float64).sum(1), rtol=1e-5, atol=1e-4)
+
+
+@pytest.mark.parametrize('rows,n,dtype', [(512, 8192, torch.bfloat16), (100, 1000, torch.float32),
+                                          (33, 77, torch.float16), (4096, 64, torch.bfloat16), (2, 100000, torch.float32)])
+def test_rows_max_sum_fused(rows, n, dtype, cuda):
+    g = torch.Generator(device='cpu').manual_seed(0)
+    x = torch.randn(rows, n, generator=g).to(dtype)
+    tx = x.to(cuda)
+    mx, sm = db.rows_max_sum(tx)
+    xd = x.double().numpy()
+    np.testing.assert_array_equal(mx.cpu().numpy(), xd.max(1).astype(np.float32))
+    scale = np.abs(xd).sum(1)
+    assert np.all(np.abs(sm.cpu().numpy().astype(np.float64) - xd.sum(1)) <= RTOL_F32 * scale)
+    # and identical to running the two Reduce nodes separately
+    o1 = torch.empty(rows, dtype=torch.float32, device=cuda)
+    if dtype != torch.float32:
+        db.reduce('lambda a, b: max(a, b)', tx, o1, axis=1, identity=-3e38)
+        np.testing.assert_array_equal(o1.cpu().numpy(), mx.cpu().numpy())
+
+
+def test_custom_minmax_lambda_and_errors(cuda):
+    a = torch.arange(100, dtype=torch.float64, device=cuda) - 50
+    got = db.reduce('lambda a, b: a if a < b else b', a, axis=None, identity=1e30)   # reference custom_reduce_test.py
+    assert got.item() == -50
+    with pytest.raises(NotImplementedError):
+        db.reduce('lambda a, b: a * a + b', a, axis=None, identity=0)
+    with pytest.raises(ValueError):
+        db.reduce('lambda a, b: a + b', a.cpu(), axis=None, identity=0)
+
+
+def test_deterministic_and_workspace(cuda):
+    """Fixed-order cross-CTA combine: bitwise repeatable float sums; explicit workspace."""
+    g = torch.Generator(device='cpu').manual_seed(1)
+    x = torch.rand(1 << 24, generator=g).to(cuda)
+    ws = db.Workspace(cuda)
+    r = [db.reduce('lambda a, b: a + b', x, axis=None, identity=0, workspace=ws).item() for _ in range(5)]
+    assert len(set(r)) == 1
+    r2 = db.reduce('lambda a, b: a + b', x, axis=None, identity=0).item()
+    assert r2 == r[0]
+    m = x.view(4096, 4096)
+    c = [db.reduce('lambda a, b: a + b', m, axis=0, identity=0, workspace=ws) for _ in range(3)]
+    assert torch.equal(c[0], c[1]) and torch.equal(c[1], c[2])

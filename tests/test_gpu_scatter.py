@@ -1,0 +1,144 @@
+"""GPU parity for WCR map reductions (scatter-add / histogram) against the oracle.
+
+Workloads follow reference samples/explicit/histogram.py:12-26 (-> uint32[256]),
+reference tests/mapreduce_test.py:274-291 (uint8 image -> uint32[256] histogram),
+reference tests/npbench/misc/azimint_hist_test.py:39-59 (hist[bin] += 1 / += w)
+and BASELINE config C4 (int32 keys -> 2^20 int32 bins, bit-exact).
+"""
+import numpy as np
+import pytest
+import torch
+
+import dace_b200 as db
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _hist(keys_np, nbins, cuda, bins_dtype=np.int32):
+    tk = torch.from_numpy(keys_np).to(cuda)
+    bins = torch.zeros(nbins, dtype=getattr(torch, np.dtype(bins_dtype).name), device=cuda)
+    db.wcr_scatter('lambda a, b: a + b', bins, tk)
+    return bins.cpu().numpy()
+
+
+@pytest.mark.parametrize('nbins', [1, 2, 7, 256, 1000, 4096, 20000, 24576, 24577, 100000, 1 << 20])
+@pytest.mark.parametrize('n', [1, 1000, (1 << 20) + 13])
+def test_histogram_int32_exact(nbins, n, cuda):
+    rng = np.random.default_rng(nbins * 7 + n)
+    keys = rng.integers(0, nbins, n).astype(np.int32)
+    got = _hist(keys, nbins, cuda)
+    ref = O.wcr_scatter(O.SUM, np.zeros(nbins, np.int32), keys)
+    np.testing.assert_array_equal(got, ref)
+    np.testing.assert_array_equal(got, np.bincount(keys, minlength=nbins).astype(np.int32))
+
+
+@pytest.mark.parametrize('dist', ['uniform', 'zipf', 'equal', 'sorted'])
+@pytest.mark.parametrize('nbins', [256, 1 << 20])
+def test_histogram_distributions(dist, nbins, cuda):
+    rng = np.random.default_rng(0)
+    n = (1 << 22) + 5
+    if dist == 'uniform':
+        keys = rng.integers(0, nbins, n)
+    elif dist == 'zipf':
+        keys = np.minimum(rng.zipf(1.1, n) - 1, nbins - 1)
+    elif dist == 'equal':
+        keys = np.full(n, nbins // 3)
+    else:
+        keys = np.sort(rng.integers(0, nbins, n))
+    keys = keys.astype(np.int32)
+    got = _hist(keys, nbins, cuda)
+    np.testing.assert_array_equal(got, np.bincount(keys, minlength=nbins).astype(np.int32))
+    assert int(got.astype(np.int64).sum()) == n   # checksum of the counts
+
+
+def test_uint8_image_histogram_uint32(cuda):
+    """reference tests/mapreduce_test.py:274-291."""
+    rng = np.random.default_rng(1)
+    img = rng.integers(0, 256, (480, 640)).astype(np.uint8)
+    got = _hist(img.reshape(-1), 256, cuda, np.uint32)
+    ref = O.wcr_scatter(O.SUM, np.zeros(256, np.uint32), img.reshape(-1))
+    np.testing.assert_array_equal(got, ref)
+    np.testing.assert_array_equal(got, np.histogram(img, bins=256, range=(0, 256))[0].astype(np.uint32))
+
+
+def test_accumulates_into_existing_bins_and_skips_oob(cuda):
+    rng = np.random.default_rng(2)
+    keys = rng.integers(-5, 105, 100000).astype(np.int64)
+    start = rng.integers(0, 9, 100).astype(np.int64)
+    bins = torch.from_numpy(start.copy()).to(cuda)
+    db.wcr_scatter('lambda a, b: a + b', bins, torch.from_numpy(keys).to(cuda), 3)
+    ref = O.wcr_scatter(O.SUM, start.copy(), keys, 3)
+    np.testing.assert_array_equal(bins.cpu().numpy(), ref)
+    ok = keys[(keys >= 0) & (keys < 100)]
+    np.testing.assert_array_equal(ref, start + 3 * np.bincount(ok, minlength=100))
+
+
+@pytest.mark.parametrize('nbins', [64, 5000, 300000])
+def test_weighted_scatter_add(nbins, cuda):
+    """hist[bin] += weights[i]: ints exact, floats to 1e-5 of the per-bin magnitude."""
+    rng = np.random.default_rng(3)
+    n = 500000
+    keys = rng.integers(0, nbins, n).astype(np.int32)
+    tk = torch.from_numpy(keys).to(cuda)
+    wi = rng.integers(-100, 100, n).astype(np.int64)
+    bins = torch.zeros(nbins, dtype=torch.int64, device=cuda)
+    db.wcr_scatter('lambda a, b: a + b', bins, tk, torch.from_numpy(wi).to(cuda))
+    np.testing.assert_array_equal(bins.cpu().numpy(), O.wcr_scatter(O.SUM, np.zeros(nbins, np.int64), keys, wi))
+    for dt, tdt, tol in ((np.float32, torch.float32, 1e-5), (np.float64, torch.float64, 1e-12)):
+        wf = rng.uniform(0, 1, n).astype(dt)
+        bins = torch.zeros(nbins, dtype=tdt, device=cuda)
+        db.wcr_scatter('lambda a, b: a + b', bins, tk, torch.from_numpy(wf).to(cuda))
+        ref = np.bincount(keys, weights=wf.astype(np.float64), minlength=nbins)
+        np.testing.assert_allclose(bins.cpu().numpy(), ref, rtol=tol * 10, atol=tol)
+
+
+@pytest.mark.parametrize('op,red', [('lambda a, b: max(a, b)', O.MAX), ('lambda a, b: min(a, b)', O.MIN)])
+@pytest.mark.parametrize('dt,tdt', [(np.int32, torch.int32), (np.int64, torch.int64), (np.float32, torch.float32),
+                                    (np.float64, torch.float64), (np.uint32, torch.uint32)])
+def test_scatter_min_max_exact(op, red, dt, tdt, cuda):
+    rng = np.random.default_rng(4)
+    n, nbins = 200000, 777
+    keys = rng.integers(0, nbins, n).astype(np.int32)
+    if np.issubdtype(dt, np.floating):
+        vals = rng.uniform(-100, 100, n).astype(dt)
+        start = np.zeros(nbins, dt)
+    elif np.issubdtype(dt, np.unsignedinteger):
+        vals = rng.integers(0, 1 << 31, n).astype(dt)
+        start = np.full(nbins, 1 << 20, dt)
+    else:
+        vals = rng.integers(-1 << 30, 1 << 30, n).astype(dt)
+        start = np.zeros(nbins, dt)
+    bins = torch.from_numpy(start.copy()).to(cuda)
+    db.wcr_scatter(op, bins, torch.from_numpy(keys).to(cuda), torch.from_numpy(vals).to(cuda))
+    ref = O.wcr_scatter(red, start.copy(), keys, vals)
+    np.testing.assert_array_equal(bins.cpu().numpy(), ref)
+
+
+def test_scatter_bitwise_and_product(cuda):
+    rng = np.random.default_rng(5)
+    n, nbins = 100000, 100
+    keys = rng.integers(0, nbins, n).astype(np.int32)
+    tk = torch.from_numpy(keys).to(cuda)
+    vals = rng.integers(0, 1 << 30, n).astype(np.int32)
+    for op, red, init in (('lambda a, b: a | b', O.BOR, 0), ('lambda a, b: a ^ b', O.BXOR, 0),
+                          ('lambda a, b: a & b', O.BAND, -1)):
+        start = np.full(nbins, init, np.int32)
+        bins = torch.from_numpy(start.copy()).to(cuda)
+        db.wcr_scatter(op, bins, tk, torch.from_numpy(vals).to(cuda))
+        np.testing.assert_array_equal(bins.cpu().numpy(), O.wcr_scatter(red, start.copy(), keys, vals))
+    pv = rng.choice(np.array([1, 1, 1, -1, 2], np.int64), 3000)
+    pk = rng.integers(0, nbins, 3000).astype(np.int32)
+    bins = torch.ones(nbins, dtype=torch.int64, device=cuda)
+    db.wcr_scatter('lambda a, b: a * b', bins, torch.from_numpy(pk).to(cuda), torch.from_numpy(pv).to(cuda))
+    np.testing.assert_array_equal(bins.cpu().numpy(), O.wcr_scatter(O.PRODUCT, np.ones(nbins, np.int64), pk, pv))
+
+
+def test_unaligned_index_pointer(cuda):
+    rng = np.random.default_rng(6)
+    keys = rng.integers(0, 1 << 17, 100003).astype(np.int32)
+    tk = torch.from_numpy(keys).to(cuda)
+    for off in (1, 2, 3):
+        bins = torch.zeros(1 << 17, dtype=torch.int32, device=cuda)
+        db.wcr_scatter('lambda a, b: a + b', bins, tk[off:])
+        np.testing.assert_array_equal(bins.cpu().numpy(), np.bincount(keys[off:], minlength=1 << 17))
