@@ -87,7 +87,6 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
                                   cudaStream_t stream) {
     if (ndim < 0 || ndim > DACE_B200_MAX_DIMS) return cudaErrorInvalidValue;
     if (ndim > 0 && (!shape || !in_strides)) return cudaErrorInvalidValue;
-    if (!in || !out) return cudaErrorInvalidValue;
     if (red < RT_Min || red > RT_BXor) return cudaErrorNotSupported;
     if (!supported_pair(dtin, dtout)) return cudaErrorNotSupported;
     Launch l;
@@ -120,6 +119,7 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
         }
     }
     if (nout == 0) return cudaSuccess;
+    if (!out || (nred != 0 && !in)) return cudaErrorInvalidValue;  // empty tensors may carry null pointers
 
     // Canonicalise: drop unit dims, merge mergeable neighbours of the same kind.
     Dim c[DACE_B200_MAX_DIMS];
@@ -189,6 +189,7 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
         else { g.kshape[g.nk] = c[i].shape; g.kin[g.nk] = c[i].in_stride; g.kout[g.nk] = c[i].out_stride; ++g.nk; }
     }
     const bool last_reduced = nc > 0 && c[nc - 1].reduced;
+    g.copy_only = (mask & ((ndim >= 32) ? 0xffffffffu : ((1u << ndim) - 1u))) == 0;
     g.warp_per_output = nr > 0 && (last_reduced || nout < (size_t)sm_count() * 256);
     return launch_generic(red, dtin, dtout, g, l);
 }

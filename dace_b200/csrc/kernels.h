@@ -47,6 +47,7 @@ struct GenericArgs {
     long long rshape[kMaxDims], rin[kMaxDims];
     const void* identity;
     int warp_per_output;
+    int copy_only;  // no reduced axis was requested at all: plain strided copy
 };
 cudaError_t launch_generic(int red, int dtin, int dtout, const GenericArgs& a, const Launch& l);
 

@@ -108,9 +108,10 @@ static cudaError_t launch_generic_t(const GenericArgs& a, const Launch& l) {
         nout *= d.kshape[k]; nred *= d.rshape[k];
     }
     Finish<A> fin = make_finish<A, S>(a.identity);
-    // No reduced axis left: the reference copies input to output and ignores the
+    if (d.nr == 0) { d.nr = 1; d.rshape[0] = 1; d.rin[0] = 0; }
+    // Empty axis list: the reference copies input to output and ignores the
     // identity (reference dace/libraries/standard/nodes/reduce.py:77-87).
-    if (d.nr == 0) { d.nr = 1; d.rshape[0] = 1; d.rin[0] = 0; fin.has_identity = 2; }
+    if (a.copy_only) fin.has_identity = 2;
     const long long cap = (long long)sm_count() * 8;
     if (a.warp_per_output) {
         long long grid = (nout + 7) / 8;

@@ -108,8 +108,10 @@ DACE_B200_API int dace_b200_workspace_init(void* workspace, size_t workspace_byt
  * (all axes: (1<<ndim)-1).  `out_strides` has one entry per KEPT axis in axis
  * order (NULL = C-contiguous).  `identity` is a HOST pointer to one value of
  * dtype_out, or NULL meaning "fold into the value already stored in out"
- * (reference dace/frontend/operations.py:251).  With no reduced axis of extent
- * > 1 the call is a strided copy, identity ignored (reference reduce.py:77-87).
+ * (reference dace/frontend/operations.py:251).  With reduce_mask == 0 (the
+ * expansion squeezed every reduced axis away at compile time) the call is a
+ * strided copy, identity ignored (reference reduce.py:77-87); a reduced axis of
+ * run-time extent 1 folds normally.
  * Replaces: reduce.py:574-588 (CUB), :984-1332 (GPUAuto kernels). */
 DACE_B200_API int dace_b200_reduce_nd(int redtype, int dtype_in, int dtype_out, const void* in, void* out, int ndim,
                                       const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,

@@ -1,0 +1,63 @@
+"""CPU checks of the drop-in boundary: the shared library builds/loads and
+exports exactly what include/dace_b200_reduce.h declares (no compute calls)."""
+import ctypes
+import os
+import re
+
+import dace_b200
+from dace_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, 'include', 'dace_b200_reduce.h')
+
+
+def _declared():
+    src = open(HEADER).read()
+    return sorted(set(re.findall(r'DACE_B200_API\s+[\w\s\*]+?\b(dace_b200_\w+)\s*\(', src)))
+
+
+def test_header_declares_what_python_binds():
+    assert _declared() == sorted(_lib.EXPORTED_SYMBOLS)
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    assert os.path.exists(_lib.LIB_PATH), 'run __graft_entry__.build() first'
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in _declared():
+        assert hasattr(lib, name), name
+    lib = dace_b200.load()
+    assert lib.dace_b200_version() == 1000
+    assert lib.dace_b200_workspace_bytes() == 8 << 20
+    assert lib.dace_b200_status_string(801).decode() == 'operation not supported'
+
+
+def test_enum_values_match_reference_reductiontype():
+    """dace::ReductionType numeric values (reference dace/runtime/include/dace/types.h:301-317)."""
+    src = open(HEADER).read()
+    want = {'CUSTOM': 0, 'MIN': 1, 'MAX': 2, 'SUM': 3, 'PRODUCT': 4, 'LOGICAL_AND': 5, 'BITWISE_AND': 6,
+            'LOGICAL_OR': 7, 'BITWISE_OR': 8, 'LOGICAL_XOR': 9, 'BITWISE_XOR': 10}
+    for k, v in want.items():
+        assert re.search(r'DACE_B200_%s = %d\b' % (k, v), src), k
+    from dace_b200 import ReductionType
+    assert [ReductionType[n].value for n in ('Min', 'Max', 'Sum', 'Product', 'Logical_And', 'Bitwise_And',
+                                             'Logical_Or', 'Bitwise_Or', 'Logical_Xor', 'Bitwise_Xor')] == list(range(1, 11))
+
+
+def test_no_product_code_touches_the_oracle():
+    """The oracle is test infrastructure: nothing under dace_b200/ may reference it."""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, 'dace_b200')):
+        for f in files:
+            if f.endswith(('.py', '.cu', '.cuh', '.h')):
+                text = open(os.path.join(dirpath, f), errors='ignore').read()
+                assert 'oracle' not in text.lower(), os.path.join(dirpath, f)
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    monkeypatch.setattr(_lib, '_lib', None)
+    monkeypatch.setattr(_lib, 'LIB_PATH', str(tmp_path / 'nope.so'))
+    try:
+        _lib.load()
+    except _lib.B200LibraryError as e:
+        assert 'no CPU fallback' in str(e)
+    else:
+        raise AssertionError('load() must raise when the CUDA library is missing')

@@ -228,9 +228,12 @@ def test_transposed_and_stepped_views(cuda):
 def test_degenerate_and_empty(cuda):
     a = np.arange(12, dtype=np.float32).reshape(3, 1, 4)
     ta = torch.from_numpy(a).to(cuda)
-    got = db.reduce('lambda a, b: a + b', ta, axis=1, identity=5).cpu().numpy()   # copy, identity ignored
-    np.testing.assert_array_equal(got, a[:, 0, :])
+    got = db.reduce('lambda a, b: a + b', ta, axis=1, identity=5).cpu().numpy()   # run-time unit axis: normal fold
+    np.testing.assert_array_equal(got, 5 + a[:, 0, :])
     np.testing.assert_array_equal(got, O.reduce(O.SUM, a, (1, ), identity=5))
+    got = db.reduce('lambda a, b: a + b', ta[:, 0, :], axis=(), identity=5).cpu().numpy()   # no axis: copy
+    np.testing.assert_array_equal(got, a[:, 0, :])
+    np.testing.assert_array_equal(got, O.reduce(O.SUM, a[:, 0, :], (), identity=5))
     e = torch.empty((4, 0), dtype=torch.float32, device=cuda)
     got = db.reduce('lambda a, b: a + b', e, axis=1, identity=2.5).cpu().numpy()
     np.testing.assert_array_equal(got, np.full(4, 2.5, np.float32))
