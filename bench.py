@@ -1,0 +1,437 @@
+#!/usr/bin/env python
+"""Benchmark of the Reduce / WCR hot path on B200 (see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c3max|c4|c5|c1] [--impl reference]
+
+One "step" = one pass of the hot path over one batch of synthetic input already
+resident in HBM.  Default workload at every N is BASELINE config C2 (full sum of
+2^30 float32 to a scalar, per GPU); with N > 1 every rank reduces its own shard
+(outer-dimension sharding) and the per-GPU partials are combined by an NCCL
+allreduce on the same stream (weak scaling).  One JSON line is printed by rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = 'reduce_throughput'
+UNIT = 'GB/s'
+ADD = 'lambda a, b: a + b'
+MAX = 'lambda a, b: max(a, b)'
+
+# name -> description, algorithmic bytes per step per GPU (SURVEY.md 8(d) / DESIGN.md)
+WORKLOADS = {
+    'c2': ('C2 full sum of 2^30 float32 -> scalar', (1 << 30) * 4 + 4),
+    'c3': ('C3 fused row max+sum over [65536, 8192] bf16, fp32 accumulate', 65536 * 8192 * 2 + 2 * 65536 * 4),
+    'c3max': ('C3 row max over [65536, 8192] bf16 -> fp32 (single Reduce node)', 65536 * 8192 * 2 + 65536 * 4),
+    'c4': ('C4 WCR histogram: 2^28 int32 keys -> 2^20 int32 bins (uniform keys)', (1 << 28) * 4 + (1 << 20) * 4),
+    'c5': ('C5 column sum of a [2^19, 4096] float32 row shard per GPU', (1 << 19) * 4096 * 4 + 4096 * 4),
+    'c1': ('C1 np.sum(A, axis=1) on 4096x4096 float32', 4096 * 4096 * 4 + 4096 * 4),
+}
+
+
+def peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        with open(path) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md 6.65 TB/s)'
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index=0):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix='.csv')
+            os.close(fd)
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=open(self.path, 'w'), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+        except Exception:
+            pass
+        try:
+            rows = [r.strip().split(',') for r in open(self.path) if r.strip()]
+            os.unlink(self.path)
+            sm = sorted(float(r[0]) for r in rows if len(r) >= 6)
+            if sm:
+                out['sm_mhz'] = sm[len(sm) // 2]
+                out['sm_max_mhz'] = float(rows[0][1])
+                out['samples'] = len(sm)
+                names = ('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap')
+                for i, n in enumerate(names):
+                    if any(r[2 + i].strip().lower() == 'active' for r in rows if len(r) >= 6):
+                        out['reasons'].append(n)
+        except Exception:
+            pass
+        return out
+
+
+def make_workload(name, dev, rank, torch, db):
+    """Returns (step_fn(stream_sync=False) -> result tensor, host_step pieces, description)."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+    w = {}
+    if name == 'c2':
+        x = torch.rand(1 << 30, dtype=torch.float32, device=dev, generator=g)
+        out = torch.zeros((), dtype=torch.float32, device=dev)
+        w['inputs'] = [x]
+        w['step'] = lambda: db.reduce(ADD, x, out, axis=None, identity=0)
+        w['result'] = out
+        w['combine'] = 'sum'
+    elif name in ('c3', 'c3max'):
+        x = torch.randn(65536, 8192, dtype=torch.float32, device=dev, generator=g).to(torch.bfloat16)
+        mx = torch.empty(65536, dtype=torch.float32, device=dev)
+        sm = torch.empty(65536, dtype=torch.float32, device=dev)
+        w['inputs'] = [x]
+        if name == 'c3':
+            w['step'] = lambda: db.rows_max_sum(x, mx, sm)
+        else:
+            w['step'] = lambda: db.reduce(MAX, x, mx, axis=1, identity=-3.0e38)
+        w['result'] = mx
+        w['combine'] = None   # rows are sharded along the kept axis: no collective
+    elif name == 'c4':
+        keys = torch.randint(0, 1 << 20, (1 << 28, ), dtype=torch.int32, device=dev, generator=g)
+        bins = torch.zeros(1 << 20, dtype=torch.int32, device=dev)
+        w['inputs'] = [keys]
+
+        def step():
+            bins.zero_()          # part of the step: WCR accumulates into its output
+            db.wcr_scatter(ADD, bins, keys)
+        w['step'] = step
+        w['result'] = bins
+        w['combine'] = 'sum'
+    elif name == 'c5':
+        x = torch.rand(1 << 19, 4096, dtype=torch.float32, device=dev, generator=g)
+        out = torch.zeros(4096, dtype=torch.float32, device=dev)
+        w['inputs'] = [x]
+        w['step'] = lambda: db.reduce(ADD, x, out, axis=0, identity=0)
+        w['result'] = out
+        w['combine'] = 'sum'
+    elif name == 'c1':
+        x = torch.rand(4096, 4096, dtype=torch.float32, device=dev, generator=g)
+        out = torch.zeros(4096, dtype=torch.float32, device=dev)
+        w['inputs'] = [x]
+        w['step'] = lambda: db.reduce(ADD, x, out, axis=1, identity=0)
+        w['result'] = out
+        w['combine'] = None
+    else:
+        raise SystemExit('unknown workload %r' % name)
+    return w
+
+
+# ---------------------------------------------------------------------------
+# CPU side: the reference's own CPU expansion (oracle/_ref, built from the
+# reference by oracle/build_ref.py) on a bounded sample; the C oracle port if
+# the reference could not be compiled.  Checker/baseline only.
+# ---------------------------------------------------------------------------
+def cpu_reference_run(workload, budget_s=12.0, max_reps=5):
+    import numpy as np
+    from oracle import ref_loader
+    cores = os.cpu_count() or 1
+    os.environ.setdefault('OMP_NUM_THREADS', str(cores))
+    rng = np.random.default_rng(0)
+    if workload == 'c2':
+        n = 1 << 28
+        sample = 'first 2^28 of the 2^30 float32 (1 GiB), reference OpenMP expansion'
+        data = {'A': rng.random(n, dtype=np.float32), 'B': np.zeros(1, np.float32), 'D0': n}
+        prog, nbytes = 'full_sum_f32_omp', n * 4
+    elif workload in ('c3', 'c3max'):
+        rows, cols = 8192, 8192
+        sample = '[8192, 8192] bf16 slice (128 MiB), reference pure expansion (max, then sum for c3)'
+        bits = (rng.standard_normal((rows, cols), dtype=np.float32).view(np.uint32) >> 16).astype(np.uint16)
+        data = {'A': bits, 'B': np.zeros(rows, np.float32), 'D0': rows, 'D1': cols}
+        prog, nbytes = 'row_max_bf16_f32_pure', rows * cols * 2
+    elif workload == 'c4':
+        n = 1 << 26
+        sample = '2^26 of the 2^28 int32 keys -> 2^20 bins, reference WCR map (omp atomic)'
+        data = {'keys': rng.integers(0, 1 << 20, n, dtype=np.int32), 'bins': np.zeros(1 << 20, np.int32), 'N': n}
+        prog, nbytes = 'c4_hist_i32', n * 4
+    elif workload == 'c5':
+        rows, cols = 1 << 16, 4096
+        sample = '[2^16, 4096] float32 slice (1 GiB), reference OpenMP expansion'
+        data = {'A': rng.random((rows, cols), dtype=np.float32), 'B': np.zeros(cols, np.float32), 'D0': rows, 'D1': cols}
+        prog, nbytes = 'col_sum_f32_omp', rows * cols * 4
+    else:
+        rows, cols = 4096, 4096
+        sample = 'full 4096x4096 float32, reference @dace.program np.sum(A, axis=1), OpenMP expansion'
+        data = {'A': rng.random((rows, cols), dtype=np.float32), 'B': np.zeros(rows, np.float32), 'N': rows, 'M': cols}
+        prog, nbytes = 'c1_npsum_axis1_f32_omp', rows * cols * 4
+
+    if ref_loader.available():
+        kind = 'reference'
+        p = ref_loader.RefProgram(prog)
+        extra = ref_loader.RefProgram('row_sum_bf16_f32_pure') if workload == 'c3' else None
+
+        def run():
+            p(**data)
+            if extra is not None:
+                extra(**data)
+    else:
+        kind, cores = 'port', 1
+        from oracle import oracle as O
+        sample += ' [oracle/_ref missing: single-threaded C port]'
+
+        def run():
+            if workload == 'c4':
+                O.wcr_scatter(O.SUM, data['bins'], data['keys'])
+            elif workload in ('c3', 'c3max'):
+                O.reduce(O.MAX, data['A'], (1, ), identity=-3e38, in_bf16=True, out_dtype=np.float32)
+            elif workload == 'c5':
+                O.reduce(O.SUM, data['A'], (0, ), identity=0)
+            elif workload == 'c2':
+                O.reduce(O.SUM, data['A'], None, identity=0)
+            else:
+                O.reduce(O.SUM, data['A'], (1, ), identity=0)
+
+    run()  # warm-up (page faults, OpenMP pool)
+    times = []
+    t_start = time.perf_counter()
+    while len(times) < max_reps and (time.perf_counter() - t_start < budget_s or not times):
+        t0 = time.perf_counter()
+        run()
+        times.append(time.perf_counter() - t0)
+    best = min(times)
+    return {'value': nbytes / best / 1e9, 'unit': UNIT, 'cores': cores, 'kind': kind, 'sample': sample,
+            'best_s': best, 'reps': len(times), 'nbytes': nbytes}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's own CPU expansion of the path on the host cores."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return 0
+    desc, _ = WORKLOADS[args.workload]
+    res = []
+    for _ in range(max(1, args.warmup)):
+        cpu_reference_run(args.workload, budget_s=0.0, max_reps=1)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res.append(cpu_reference_run(args.workload, budget_s=0.0, max_reps=1))
+        if time.perf_counter() - t0 > 150:
+            break
+    mean_s = sum(r['best_s'] for r in res) / len(res)
+    best = res[0]['nbytes'] / mean_s / 1e9     # throughput over exactly the timed steps
+    base = dict(res[0])
+    base['value'] = best
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': best, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': len(res),
+        'warmup': max(1, args.warmup), 'ms_per_step': mean_s * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': dtype_of(args.workload), 'data': 'synthetic',
+        'config': {'workload': desc, 'sample': base['sample']},
+        'cpu_baseline': {k: base[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
+        'e2e': {'value': best, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def dtype_of(workload):
+    return {'c2': 'f32', 'c3': 'bf16->f32', 'c3max': 'bf16->f32', 'c4': 'i32', 'c5': 'f32', 'c1': 'f32'}[workload]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--e2e-steps', type=int, default=3)
+    ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--extras', action='store_true', help='also time the other configs (device-only) into "others"')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
+    if args.impl == 'reference':
+        return run_reference_arm(args)
+
+    import torch
+    import dace_b200 as db
+    db.load()   # fails loudly if the CUDA library is missing: no fallback
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device; the B200 backend has no CPU fallback')
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        os.environ.setdefault('MASTER_PORT', '29531')
+        dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
+
+    desc, bytes_per_gpu = WORKLOADS[args.workload]
+    w = make_workload(args.workload, dev, rank, torch, db)
+    step, result, combine = w['step'], w['result'], w['combine']
+    input_bytes = sum(t.numel() * t.element_size() for t in w['inputs'])
+    needs_flush = input_bytes < (256 << 20)       # inputs smaller than ~2x L2: flush between iterations
+    flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device=dev) if needs_flush else None
+
+    def full_step():
+        step()
+        if dist is not None and combine is not None:
+            dist.all_reduce(result, op=dist.ReduceOp.SUM)   # NCCL over NVLink, same stream as the kernel
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        """Average device time per call (ms) over k calls, CUDA events on the launching stream."""
+        if not needs_flush:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(k):
+                fn()
+            e1.record()
+            e1.synchronize()
+            return e0.elapsed_time(e1) / k
+        tot = 0.0
+        for _ in range(k):
+            flush_buf.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            e1.synchronize()
+            tot += e0.elapsed_time(e1)
+        return tot / k
+
+    for _ in range(args.warmup):
+        full_step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    ms = timed(full_step, args.steps)
+    barrier()
+    # kernel-only (no collective) timing for the roofline of the dominant kernel
+    kernel_ms = timed(step, args.steps)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([ms, kernel_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, kernel_ms = t.tolist()
+    value = world * bytes_per_gpu / (ms * 1e-3) / 1e9
+
+    # ---- end to end: host buffers, H2D + kernel + D2H of the result inside the timed region ----
+    e2e = None
+    if args.e2e_steps > 0:
+        hosts = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in w['inputs']]
+        for h, t in zip(hosts, w['inputs']):
+            h.copy_(t)
+        host_out = torch.empty(result.shape, dtype=result.dtype, pin_memory=True)
+
+        def e2e_step():
+            for h, t in zip(hosts, w['inputs']):
+                t.copy_(h, non_blocking=True)
+            full_step()
+            host_out.copy_(result, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            e2e_step()
+        barrier()
+        e2e_s = (time.perf_counter() - t0) / args.e2e_steps
+        if dist is not None:
+            t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_s = t.item()
+        e2e = {'value': world * bytes_per_gpu / e2e_s / 1e9, 'unit': UNIT, 'h2d_bytes_per_step': input_bytes,
+               'd2h_bytes_per_step': result.numel() * result.element_size(), 'ms_per_step': e2e_s * 1e3,
+               'steps': args.e2e_steps}
+        del hosts
+
+    others = None
+    if args.extras and world == 1:
+        others = {}
+        del w, step
+        torch.cuda.empty_cache()
+        for name in ('c1', 'c3', 'c3max', 'c4', 'c5'):
+            if name == args.workload:
+                continue
+            ww = make_workload(name, dev, rank, torch, db)
+            ib = sum(t.numel() * t.element_size() for t in ww['inputs'])
+            needs_flush = ib < (256 << 20)
+            if needs_flush and flush_buf is None:
+                flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+            for _ in range(3):
+                ww['step']()
+            torch.cuda.synchronize()
+            t_ms = timed(ww['step'], args.steps)
+            others[name] = {'GB/s': WORKLOADS[name][1] / (t_ms * 1e-3) / 1e9, 'ms': t_ms,
+                            'frac_of_hbm_peak': WORKLOADS[name][1] / (t_ms * 1e-3) / 1e9 / peaks()[0]}
+            del ww
+            torch.cuda.empty_cache()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        try:
+            cpu = cpu_reference_run(args.workload)
+            cpu = {k: cpu[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
+        except Exception as ex:   # baseline only; never blocks the GPU line
+            cpu = {'value': None, 'unit': UNIT, 'cores': 0, 'kind': 'unavailable', 'sample': str(ex)}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        achieved = bytes_per_gpu / (kernel_ms * 1e-3) / 1e9
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': dtype_of(args.workload), 'data': 'synthetic',
+            'config': {'workload': desc, 'bytes_per_step_per_gpu': bytes_per_gpu,
+                       'sharding': 'outer dimension, one shard per GPU' if world > 1 else 'single GPU',
+                       'combine': ('NCCL allreduce of the per-GPU partials' if (world > 1 and combine) else 'none'),
+                       'l2': 'L2 flushed (512 MiB write) between timed iterations' if needs_flush and others is None
+                             else 'inputs (>= 1 GiB) far larger than the 126 MB L2'},
+            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': UNIT, 'frac': achieved / peak,
+                         'traffic': None, 'peak_source': peak_src, 'kernel_ms': kernel_ms,
+                         'frac_of_8TBs_nominal': achieved / 8000.0},
+            'cpu_baseline': cpu, 'e2e': e2e, 'gpu_launches': args.steps, 'clocks': clocks,
+        }
+        if others is not None:
+            line['others'] = others
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == '__main__':
+    sys.exit(main())
