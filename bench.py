@@ -48,49 +48,48 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
-    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
-         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+    """SM clock and throttle reasons sampled DURING the timed region (NVML poll
+    thread every 5 ms; the launch loop releases the GIL inside ctypes calls)."""
 
     def __init__(self, index=0):
         self.index = index
-        self.proc = None
-        self.path = None
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+
+    def _poll(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            bits = {'hw_slowdown': nv.nvmlClocksEventReasonHwSlowdown,
+                    'hw_thermal_slowdown': nv.nvmlClocksEventReasonHwThermalSlowdown,
+                    'sw_thermal_slowdown': nv.nvmlClocksEventReasonSwThermalSlowdown,
+                    'sw_power_cap': nv.nvmlClocksEventReasonSwPowerCap}
+            while not self._stop.is_set():
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                for name, bit in bits.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.005)
+        except Exception as ex:   # clocks are evidence, not a dependency
+            self.error = str(ex)
 
     def start(self):
-        try:
-            fd, self.path = tempfile.mkstemp(suffix='.csv')
-            os.close(fd)
-            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
-                                          '--format=csv,noheader,nounits', '-lms', '100'],
-                                         stdout=open(self.path, 'w'), stderr=subprocess.DEVNULL)
-        except Exception:
-            self.proc = None
+        self._thread = threading.Thread(target=self._poll, daemon=True)
+        self._thread.start()
 
     def stop(self):
-        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
-        if self.proc is None:
-            return out
-        try:
-            self.proc.terminate()
-            self.proc.wait(timeout=5)
-        except Exception:
-            pass
-        try:
-            rows = [r.strip().split(',') for r in open(self.path) if r.strip()]
-            os.unlink(self.path)
-            sm = sorted(float(r[0]) for r in rows if len(r) >= 6)
-            if sm:
-                out['sm_mhz'] = sm[len(sm) // 2]
-                out['sm_max_mhz'] = float(rows[0][1])
-                out['samples'] = len(sm)
-                names = ('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap')
-                for i, n in enumerate(names):
-                    if any(r[2 + i].strip().lower() == 'active' for r in rows if len(r) >= 6):
-                        out['reasons'].append(n)
-        except Exception:
-            pass
-        return out
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join(timeout=2)
+        sm = sorted(self.samples)
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': self.max_mhz,
+                'reasons': sorted(self.reasons), 'samples': len(sm)}
 
 
 def make_workload(name, dev, rank, torch, db):
@@ -259,7 +258,7 @@ def dtype_of(workload):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--steps', type=int, default=100)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
@@ -333,6 +332,7 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+        time.sleep(0.05)
     barrier()
     ms = timed(full_step, args.steps)
     barrier()
