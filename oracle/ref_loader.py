@@ -20,25 +20,25 @@ _CT = {'int64_t': ctypes.c_int64, 'int': ctypes.c_int, 'int32_t': ctypes.c_int32
        'unsigned int': ctypes.c_uint, 'uint64_t': ctypes.c_uint64}
 
 
-def available() -> bool:
-    return os.path.exists(MANIFEST)
+def available(ref_dir: str = REF_DIR) -> bool:
+    return os.path.exists(os.path.join(ref_dir, 'manifest.json'))
 
 
-def manifest() -> dict:
-    with open(MANIFEST) as f:
+def manifest(ref_dir: str = REF_DIR) -> dict:
+    with open(os.path.join(ref_dir, 'manifest.json')) as f:
         return json.load(f)
 
 
 class RefProgram:
     """One compiled reference SDFG.  Call with arrays (NumPy, C-contiguous) and symbols by name."""
 
-    def __init__(self, name: str):
-        m = manifest()
+    def __init__(self, name: str, ref_dir: str = REF_DIR):
+        m = manifest(ref_dir)
         if name not in m['programs']:
             raise KeyError('no reference program %r in oracle/_ref (have: %s)' % (name, sorted(m['programs'])))
         self.name = name
         self.meta = m['programs'][name]
-        self.lib = ctypes.CDLL(os.path.join(REF_DIR, self.meta['lib']))
+        self.lib = ctypes.CDLL(os.path.join(ref_dir, self.meta['lib']))
         self._init = getattr(self.lib, '__dace_init_' + name)
         self._init.restype = ctypes.c_void_p
         self._init.argtypes = [_CT[s['ctype']] for s in self.meta['init_symbols']]

@@ -1,0 +1,152 @@
+"""Build DaCe programs whose Reduce nodes use the 'B200' expansion.
+
+Runs where /root/reference exists (this container): the UNMODIFIED reference
+frontend + codegen + CMake build produce ordinary DaCe shared objects whose host
+code calls ``dace_b200_reduce_nd`` (cross-compiled, no GPU needed).  Only the
+built .so files + a manifest land in tests/dace_e2e/_built/ (git-ignored, shipped
+to the GPU box), where tests/test_gpu_dace_e2e.py loads them with ctypes exactly
+like ``CompiledSDFG`` does (reference dace/codegen/compiled_sdfg.py:233-240) and
+checks the results against the oracle.  This is the drop-in proof: np.sum in a
+@dace.program -> Reduce library node -> 'B200' expansion -> C ABI -> sm_100a kernel.
+
+Usage:  PYTHONPATH=/root/repo python -m tests.dace_e2e.build_programs
+"""
+import json
+import os
+import shutil
+import sys
+import tempfile
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(HERE, '_built')
+VERSION = 2
+
+
+def up_to_date() -> bool:
+    try:
+        m = json.load(open(os.path.join(OUT, 'manifest.json')))
+        return m.get('version') == VERSION and all(os.path.exists(os.path.join(OUT, e['lib']))
+                                                   for e in m['programs'].values())
+    except Exception:
+        return False
+
+
+def _programs(dace):
+    import numpy as np
+    from dace_b200 import expansion as E
+    from oracle.build_ref import _reduce_sdfg
+    add, mx = 'lambda a, b: a + b', 'lambda a, b: max(a, b)'
+    progs = []
+    N, M = dace.symbol('N', dace.int64), dace.symbol('M', dace.int64)
+
+    # (1) Unmodified @dace.program; the backend is chosen only through the registry default.
+    E.Reduce.default_implementation = 'B200'
+    try:
+        @dace.program
+        def b200_c1_npsum_axis1(A: dace.float32[N, M], B: dace.float32[N]):
+            B[:] = np.sum(A, axis=1)
+
+        @dace.program
+        def b200_np_max_axis0_i64(A: dace.int64[N, M], B: dace.int64[M]):
+            B[:] = np.max(A, axis=0)
+
+        @dace.program
+        def b200_softmax_stats(A: dace.float32[N, M], mx_out: dace.float32[N], sm_out: dace.float32[N]):
+            mx_out[:] = np.max(A, axis=1)
+            sm_out[:] = np.sum(A, axis=1)
+
+        for p in (b200_c1_npsum_axis1, b200_np_max_axis0_i64, b200_softmax_stats):
+            sdfg = p.to_sdfg()
+            sdfg.apply_gpu_transformations()
+            E.use_b200_reductions(sdfg)
+            progs.append(sdfg)
+    finally:
+        E.Reduce.default_implementation = 'pure'
+
+    # (2) Hand-built Reduce nodes (reference tests/library/reduce_test.py:14-27), host arrays.
+    f32, f64, i32, bf16 = dace.float32, dace.float64, dace.int32, dace.bfloat16
+    fmax = float(np.finfo(np.float32).max)
+    for name, din, dout, nd, axes, wcr, ident in (
+        ('b200_full_sum_f32', f32, f32, 1, None, add, 0),
+        ('b200_col_sum_f32', f32, f32, 2, [0], add, 0),
+        ('b200_row_sum_i32', i32, i32, 2, [1], add, 0),
+        ('b200_mid2_sum_f32', f32, f32, 4, [1, 2], add, 0),
+        ('b200_outer_inner_sum_f64', f64, f64, 3, [0, 2], add, 0),
+        ('b200_row_max_bf16_f32', bf16, f32, 2, [1], mx, -fmax),
+        ('b200_noident_col_max_f64', f64, f64, 2, [0], mx, None),
+    ):
+        sdfg = _reduce_sdfg(dace, name, din, dout, nd, axes, wcr, ident, 'B200')
+        sdfg.apply_gpu_transformations()
+        E.use_b200_reductions(sdfg)
+        progs.append(sdfg)
+
+    # (3) Sub-range / offset memlets (reference tests/reduce_offsets_test.py:26-66).
+    sdfg = dace.SDFG('b200_offsets')
+    sdfg.add_array('A', [50, 50], f64)
+    sdfg.add_array('B', [25], f64)
+    st = sdfg.add_state()
+    r = st.add_reduce(add, [0], 0)
+    r.implementation = 'B200'
+    st.add_nedge(st.add_read('A'), r, dace.Memlet('A[25:50, 13:20]'))
+    st.add_nedge(r, st.add_write('B'), dace.Memlet('B[4:11]'))
+    sdfg.apply_gpu_transformations()
+    E.use_b200_reductions(sdfg)
+    progs.append(sdfg)
+
+    # (4) Device-resident arrays (GPU_Global): no copies in the generated program.
+    sdfg = dace.SDFG('b200_full_sum_f32_resident')
+    D0 = dace.symbol('D0', dace.int64)
+    sdfg.add_array('A', [D0], f32, storage=dace.StorageType.GPU_Global)
+    sdfg.add_array('B', [1], f32, storage=dace.StorageType.GPU_Global)
+    st = sdfg.add_state()
+    r = st.add_reduce(add, None, 0)
+    r.implementation = 'B200'
+    st.add_nedge(st.add_read('A'), r, dace.Memlet.from_array('A', sdfg.arrays['A']))
+    st.add_nedge(r, st.add_write('B'), dace.Memlet.from_array('B', sdfg.arrays['B']))
+    progs.append(sdfg)
+    return progs
+
+
+def build_all(verbose=True):
+    from oracle.refenv import import_reference
+    tmp = tempfile.mkdtemp(prefix='dace_b200_e2e_')
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    try:
+        dace = import_reference(os.path.join(tmp, '.dacecache'))
+        if dace is None:
+            raise RuntimeError('reference checkout not available')
+        os.makedirs(OUT, exist_ok=True)
+        manifest = {'version': VERSION, 'reference_version': dace.__version__, 'programs': {}}
+        for sdfg in _programs(dace):
+            name = sdfg.name
+            csdfg = sdfg.compile()
+            lib = 'lib%s.so' % name
+            shutil.copyfile(csdfg.filename, os.path.join(OUT, lib))
+            g = csdfg.sdfg
+            args = []
+            for aname in g.signature_arglist(with_types=False, for_call=True):
+                if aname in g.arrays:
+                    args.append({'name': aname, 'kind': 'array', 'dtype': g.arrays[aname].dtype.to_string(),
+                                 'storage': str(g.arrays[aname].storage)})
+                else:
+                    args.append({'name': aname, 'kind': 'symbol', 'ctype': g.symbols[aname].ctype})
+            init_names = [n.strip() for n in g.init_signature(for_call=True).split(',') if n.strip()]
+            src = open(os.path.join(os.path.dirname(os.path.dirname(csdfg.filename)), 'src', 'cpu', name + '.cpp')).read()
+            manifest['programs'][name] = {
+                'lib': lib, 'args': args,
+                'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
+                'b200_calls': src.count('dace_b200_reduce_nd('),
+            }
+            if verbose:
+                print('built', name, [a['name'] for a in args], 'b200 calls:', manifest['programs'][name]['b200_calls'],
+                      file=sys.stderr)
+        json.dump(manifest, open(os.path.join(OUT, 'manifest.json'), 'w'), indent=1)
+        return manifest
+    finally:
+        os.chdir(cwd)
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+if __name__ == '__main__':
+    build_all()

@@ -1,0 +1,129 @@
+"""GPU: DaCe-generated programs whose Reduce nodes were expanded with 'B200'.
+
+tests/dace_e2e/_built/*.so are ordinary DaCe build products (unmodified reference
+frontend + codegen + CMake, built in the container where /root/reference exists by
+tests/dace_e2e/build_programs.py).  They are loaded here the way
+``CompiledSDFG`` loads them (reference dace/codegen/compiled_sdfg.py:233-240):
+``__dace_init_<n>`` -> ``__program_<n>(state, arrays..., symbols...)`` ->
+``__dace_exit_<n>``; host NumPy arrays in, host arrays out - the generated code
+does the H2D/D2H copies and calls ``dace_b200_reduce_nd`` on its own stream.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from oracle import ref_loader
+
+pytestmark = pytest.mark.gpu
+
+BUILT = os.path.join(os.path.dirname(__file__), 'dace_e2e', '_built')
+if not ref_loader.available(BUILT):
+    pytest.skip('tests/dace_e2e/_built not present (built where /root/reference exists)', allow_module_level=True)
+
+
+def prog(name):
+    return ref_loader.RefProgram(name, BUILT)
+
+
+def close_f32(got, ref, a, axes):
+    scale = np.abs(a.astype(np.float64)).sum(axis=axes).reshape(np.shape(ref))
+    return np.all(np.abs(got.astype(np.float64) - ref.astype(np.float64)) <= 1e-5 * np.maximum(scale, 1e-30))
+
+
+def test_manifest_every_program_calls_the_c_abi(cuda):
+    m = ref_loader.manifest(BUILT)
+    assert len(m['programs']) >= 10
+    assert all(e['b200_calls'] >= 1 for e in m['programs'].values())
+
+
+def test_c1_np_sum_axis1_dace_program(cuda):
+    """BASELINE C1 shape: np.sum(A, axis=1) on 4096x4096 float32 in a @dace.program."""
+    a = np.random.default_rng(0).random((4096, 4096), dtype=np.float32)
+    b = np.zeros(4096, np.float32)
+    p = prog('b200_c1_npsum_axis1')
+    p(A=a, B=b, N=4096, M=4096)
+    ref = O.reduce(O.SUM, a, (1, ), identity=0, wide=True)
+    assert close_f32(b, ref, a, (1, ))
+    b2 = np.zeros(100, np.float32)
+    p(A=np.ascontiguousarray(a[:100, :77]), B=b2, N=100, M=77)   # symbolic sizes: same .so, new shape
+    assert close_f32(b2, a[:100, :77].astype(np.float64).sum(1), a[:100, :77], (1, ))
+
+
+def test_np_max_axis0_int64(cuda):
+    a = np.random.default_rng(1).integers(-10**12, 10**12, (777, 333))
+    b = np.zeros(333, np.int64)
+    prog('b200_np_max_axis0_i64')(A=a, B=b, N=777, M=333)
+    np.testing.assert_array_equal(b, a.max(0))
+    np.testing.assert_array_equal(b, O.reduce(O.MAX, a, (0, ), identity=np.iinfo(np.int64).min))
+
+
+def test_two_reduce_nodes_in_one_program(cuda):
+    a = np.random.default_rng(2).standard_normal((513, 2050)).astype(np.float32)
+    mx, sm = np.zeros(513, np.float32), np.zeros(513, np.float32)
+    prog('b200_softmax_stats')(A=a, mx_out=mx, sm_out=sm, N=513, M=2050)
+    np.testing.assert_array_equal(mx, a.max(1))
+    assert close_f32(sm, a.astype(np.float64).sum(1), a, (1, ))
+
+
+@pytest.mark.parametrize('name,shape,axes,dt,red', [
+    ('b200_full_sum_f32', (3000017, ), None, np.float32, O.SUM),
+    ('b200_col_sum_f32', (5000, 520), (0, ), np.float32, O.SUM),
+    ('b200_row_sum_i32', (999, 1001), (1, ), np.int32, O.SUM),
+    ('b200_mid2_sum_f32', (123, 21, 26, 8), (1, 2), np.float32, O.SUM),
+    ('b200_outer_inner_sum_f64', (64, 55, 33), (0, 2), np.float64, O.SUM),
+])
+def test_hand_built_reduce_nodes(name, shape, axes, dt, red, cuda):
+    rng = np.random.default_rng(3)
+    a = (rng.uniform(-10, 10, shape) if np.issubdtype(dt, np.floating) else rng.integers(-99, 99, shape)).astype(dt)
+    kept = [s for i, s in enumerate(shape) if axes is not None and i not in axes] or [1]
+    b = np.zeros(kept, dt)
+    prog(name)(A=a, B=b, **{'D%d' % i: s for i, s in enumerate(shape)})
+    ref = O.reduce(red, a, axes, identity=0, wide=True).reshape(b.shape)
+    if dt == np.float32:
+        assert close_f32(b, ref, a, axes)
+    elif dt == np.float64:
+        np.testing.assert_allclose(b, ref, rtol=1e-12, atol=1e-9)
+    else:
+        np.testing.assert_array_equal(b, ref)
+
+
+def test_bf16_rows_fp32_out(cuda):
+    rng = np.random.default_rng(4)
+    bits = O.f32_to_bf16_bits(rng.standard_normal((300, 4096)).astype(np.float32))
+    b = np.zeros(300, np.float32)
+    prog('b200_row_max_bf16_f32')(A=bits, B=b, D0=300, D1=4096)
+    np.testing.assert_array_equal(b, O.reduce(O.MAX, bits, (1, ), identity=-3.4028234663852886e38, in_bf16=True,
+                                              out_dtype=np.float32))
+
+
+def test_identity_none_folds_into_output(cuda):
+    a = np.random.default_rng(5).uniform(-1, 1, (400, 60))
+    b = np.full(60, 0.5)
+    prog('b200_noident_col_max_f64')(A=a, B=b, D0=400, D1=60)
+    np.testing.assert_array_equal(b, np.maximum(0.5, a.max(0)))
+
+
+def test_offset_subrange_memlets(cuda):
+    """reference tests/reduce_offsets_test.py:26-66."""
+    rng = np.random.default_rng(6)
+    a, b = rng.random((50, 50)), rng.random(25)
+    exp = b.copy()
+    exp[4:11] = a[25:50, 13:20].sum(0)
+    prog('b200_offsets')(A=a, B=b)
+    np.testing.assert_allclose(b, exp, rtol=1e-12)
+
+
+def test_device_resident_arrays(cuda):
+    """GPU_Global arrays: the program receives device pointers, nothing is copied."""
+    import ctypes
+    import torch
+    x = torch.rand(1 << 22, device=cuda)
+    out = torch.zeros(1, device=cuda)
+    p = prog('b200_full_sum_f32_resident')
+    state = p._init(x.numel())
+    p._prog(state, ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(out.data_ptr()), x.numel())
+    torch.cuda.synchronize()
+    p._exit(state)
+    assert abs(out.item() - x.double().sum().item()) <= 1e-5 * x.double().abs().sum().item()
