@@ -272,6 +272,7 @@ def main():
 
     import torch
     import dace_b200 as db
+    from dace_b200 import sharding
     db.load()   # fails loudly if the CUDA library is missing: no fallback
     if not torch.cuda.is_available():
         raise SystemExit('bench.py needs a CUDA device; the B200 backend has no CPU fallback')
@@ -298,7 +299,7 @@ def main():
     def full_step():
         step()
         if dist is not None and combine is not None:
-            dist.all_reduce(result, op=dist.ReduceOp.SUM)   # NCCL over NVLink, same stream as the kernel
+            sharding.combine(result, 'Sum')   # NCCL allreduce over NVLink, same stream as the kernel
 
     def barrier():
         if dist is not None:
