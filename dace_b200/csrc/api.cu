@@ -69,15 +69,18 @@ static cudaError_t plan_split(int red, int dtin, int dtout, const void* in, void
                               size_t row_stride, ptrdiff_t out_stride, const void* identity, const Launch& l) {
     const size_t row_bytes = n * dtype_size(dtin);
     const size_t sms = sm_count();
-    size_t want = ceil_div(row_bytes, size_t(64) << 10);   // one 64 KiB tile per CTA at least
-    size_t cap = ceil_div(2 * sms, rows);
+    // Large rows: 1 CTA of 1024 threads per SM, 256 KiB tiles; otherwise 2 x 512 threads, 64 KiB tiles.
+    const int big = row_bytes * rows >= (size_t(256) << 20) && row_bytes >= (size_t(8) << 20);
+    const size_t tile = big ? (size_t(256) << 10) : (size_t(64) << 10);
+    size_t want = ceil_div(row_bytes, tile);
+    size_t cap = ceil_div((big ? 1 : 2) * sms, rows);
     if (want > cap) want = cap;
     if (want < 1) want = 1;
     unsigned cluster = 1;
     if (want >= 2) { cluster = 2; want = (want / 2) * 2; }
     // Partials area: rows * clusters accumulators of <= 8 bytes.
     while (want > cluster && rows * (want / cluster) * 8 > kPartialBytes) want -= cluster;
-    SplitArgs a{in, out, n, rows, row_stride, out_stride, (unsigned)want, cluster, identity};
+    SplitArgs a{in, out, n, rows, row_stride, out_stride, (unsigned)want, cluster, identity, big};
     return launch_split(red, dtin, dtout, a, l);
 }
 

@@ -10,6 +10,7 @@ struct SplitArgs {
     size_t n; size_t rows; size_t row_stride; ptrdiff_t out_stride;
     unsigned ctas_per_row; unsigned cluster;
     const void* identity;
+    int big;  // 1: 1024-thread CTAs, 8 loads in flight (large inputs); 0: 512 threads, 4 loads
 };
 cudaError_t launch_split(int red, int dtin, int dtout, const SplitArgs& a, const Launch& l);
 

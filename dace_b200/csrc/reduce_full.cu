@@ -6,8 +6,8 @@
 // _out[0] (reference dace/libraries/standard/nodes/reduce.py:993-1004,1068-1076).
 //
 // One launch, no second pass:
-//   * persistent grid, a few CTAs per SM, each CTA walks 32/64 KiB tiles with
-//     U independent 256-bit streaming loads per thread (LDG.E.256, L1 no-allocate,
+//   * persistent grid, one or two CTAs per SM, each CTA walks 64/256 KiB tiles with
+//     U = 4/8 independent 256-bit streaming loads per thread (LDG.E.256, L1 no-allocate,
 //     L2 evict-first);
 //   * thread -> warp (shuffle / redux.sync) -> CTA (shared memory);
 //   * CTAs of a thread-block cluster combine through distributed shared memory;
@@ -148,6 +148,9 @@ cudaError_t launch_split(int red, int dtin, int dtout, const SplitArgs& a, const
         using A = typename T::A;
         return dispatch_op<A>(red, [&](auto op) -> cudaError_t {
             using Op = decltype(op);
+            // Geometry from the sweep in profiles/r1_ubench_split_sweep_and_atomics.txt: full occupancy
+            // (1024-thread CTAs) and 8 x 256-bit loads in flight per thread is worth +4 % on 4 GiB.
+            if (a.big) return launch_split_cfg<T, Op, 32, 8, 1024>(a, l);
             return launch_split_cfg<T, Op, 32, 4, 512>(a, l);
         });
     });
