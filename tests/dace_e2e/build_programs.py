@@ -9,7 +9,7 @@ like ``CompiledSDFG`` does (reference dace/codegen/compiled_sdfg.py:233-240) and
 checks the results against the oracle.  This is the drop-in proof: np.sum in a
 @dace.program -> Reduce library node -> 'B200' expansion -> C ABI -> sm_100a kernel.
 
-Usage:  PYTHONPATH=/root/repo python -m tests.dace_e2e.build_programs
+Usage:  PYTHONPATH=/root/repo python tests/dace_e2e/build_programs.py   (also run by __graft_entry__.build())
 """
 import json
 import os
