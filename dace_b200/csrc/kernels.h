@@ -62,5 +62,8 @@ struct ScatterArgs {
     size_t n; void* bins; size_t nbins;
 };
 cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l);
+// Partition + shared-memory histogram path for large bin arrays (wcr_partition.cu);
+// cudaErrorNotSupported = does not apply, use the global-atomic kernel.
+cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l);
 
 }  // namespace db200

@@ -13,12 +13,14 @@
 //     replicated per warp group for small bin counts, warp-aggregated updates
 //     (match.any) when collisions inside a warp are likely, one flush of the
 //     non-zero bins with global reductions (RED, no return value);
+//   * large bin arrays with constant increments: radix partition + shared-memory
+//     histogram in one cooperative kernel (wcr_partition.cu);
 //   * otherwise: persistent grid, 128-bit index loads, U vectors in flight,
-//     RED.global straight into the (L2-resident) bin array, with a warp-uniform
-//     fast path that turns 32 equal keys into one reduction.
+//     RED.global straight into the (L2-resident) bin array.
 // Out-of-range indices are skipped.  Integer results are bit-exact by
 // construction (integer addition is associative); float sums are atomics, so
 // order- and run-dependent in the last ulps like the reference's own.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -283,6 +285,10 @@ static cudaError_t launch_scatter_val(int red, int dtval, const ScatterArgs& a, 
 }
 
 cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l) {
+    if (red == RT_Sum && getenv("DACE_B200_NO_PARTITION") == nullptr) {
+        cudaError_t e = launch_scatter_partitioned(dtidx, dtval, a, l);
+        if (e != cudaErrorNotSupported) return e;
+    }
     switch (dtidx) {
         case DT_I32: return launch_scatter_val<int>(red, dtval, a, l);
         case DT_U32: return launch_scatter_val<unsigned>(red, dtval, a, l);

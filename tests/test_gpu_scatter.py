@@ -142,3 +142,59 @@ def test_unaligned_index_pointer(cuda):
         bins = torch.zeros(1 << 17, dtype=torch.int32, device=cuda)
         db.wcr_scatter('lambda a, b: a + b', bins, tk[off:])
         np.testing.assert_array_equal(bins.cpu().numpy(), np.bincount(keys[off:], minlength=1 << 17))
+
+
+@pytest.mark.parametrize('nbins', [24577, 100000, 1 << 20, (1 << 21) - 5])
+@pytest.mark.parametrize('dist', ['uniform', 'zipf', 'halfhot'])
+def test_partitioned_histogram_large_bins(nbins, dist, cuda):
+    """Radix-partition + shared-memory histogram path (wcr_partition.cu): several 2^23-key chunks,
+    partial tiles, skewed keys overflowing the bucket regions, out-of-range keys, existing contents."""
+    rng = np.random.default_rng(nbins % 1000)
+    n = (1 << 24) + (1 << 22) + 4321
+    if dist == 'uniform':
+        keys = rng.integers(-3, nbins + 3, n)           # a few keys out of range on both sides
+    elif dist == 'zipf':
+        keys = np.minimum(rng.zipf(1.2, n) - 1, nbins - 1)
+    else:
+        keys = rng.integers(0, nbins, n)
+        keys[::2] = nbins // 2                          # half of all keys hit one bin
+    keys = keys.astype(np.int32)
+    start = rng.integers(0, 5, nbins).astype(np.int32)
+    bins = torch.from_numpy(start.copy()).to(cuda)
+    db.wcr_scatter('lambda a, b: a + b', bins, torch.from_numpy(keys).to(cuda))
+    ok = keys[(keys >= 0) & (keys < nbins)]
+    np.testing.assert_array_equal(bins.cpu().numpy(), start + np.bincount(ok, minlength=nbins).astype(np.int32))
+
+
+def test_partitioned_histogram_variants(cuda):
+    rng = np.random.default_rng(9)
+    n, nbins = (1 << 23) + 999, 300000
+    keys = rng.integers(0, nbins, n).astype(np.int32)
+    tk = torch.from_numpy(keys).to(cuda)
+    ref = np.bincount(keys, minlength=nbins)
+    # unaligned key pointer
+    for off in (1, 2, 3):
+        bins = torch.zeros(nbins, dtype=torch.int32, device=cuda)
+        db.wcr_scatter('lambda a, b: a + b', bins, tk[off:])
+        np.testing.assert_array_equal(bins.cpu().numpy(), np.bincount(keys[off:], minlength=nbins))
+    # constant increment other than 1, uint32 and float32 bins, uint32 keys
+    bins = torch.zeros(nbins, dtype=torch.int32, device=cuda)
+    db.wcr_scatter('lambda a, b: a + b', bins, tk, 3)
+    np.testing.assert_array_equal(bins.cpu().numpy(), 3 * ref)
+    bu = torch.zeros(nbins, dtype=torch.uint32, device=cuda)
+    db.wcr_scatter('lambda a, b: a + b', bu, torch.from_numpy(keys.astype(np.uint32)).to(cuda))
+    np.testing.assert_array_equal(bu.cpu().numpy(), ref.astype(np.uint32))
+    bf = torch.zeros(nbins, dtype=torch.float32, device=cuda)
+    db.wcr_scatter('lambda a, b: a + b', bf, tk, 0.5)
+    np.testing.assert_array_equal(bf.cpu().numpy(), (0.5 * ref).astype(np.float32))   # small counts: exact in fp32
+    # repeated calls reuse the per-device scratch; two streams are ordered through it
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    b1 = torch.zeros(nbins, dtype=torch.int32, device=cuda)
+    b2 = torch.zeros(nbins, dtype=torch.int32, device=cuda)
+    torch.cuda.synchronize()
+    for _ in range(3):
+        db.wcr_scatter('lambda a, b: a + b', b1, tk, stream=s1)
+        db.wcr_scatter('lambda a, b: a + b', b2, tk, stream=s2)
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(b1.cpu().numpy(), 3 * ref)
+    np.testing.assert_array_equal(b2.cpu().numpy(), 3 * ref)
