@@ -10,17 +10,28 @@
 // then histogram each bucket in a 128 KiB shared-memory table.
 //
 // ONE persistent cooperative kernel, one 1024-thread CTA per SM, keys processed in
-// chunks of 2^23 so the partitioned copy (double-buffered, 2 x 48 MiB) stays in
-// the 126 MB L2 instead of round-tripping through HBM:
-//   phase A (all CTAs): 8192-key tiles; rank inside the tile by shared-memory
-//            atomics with return, bucket-sort the tile in shared memory, reserve space
-//            per bucket with one global atomic per (tile, bucket), coalesced copy-out;
+// chunks of ~2^24 (a whole number of tiles per group, so the grid barrier waits for nobody);
+// the partitioned copy is double-buffered and mostly lives in the 126 MB L2:
+//   phase A (4 independent 256-thread groups per CTA, named barriers), 2048-key tiles,
+//            register-prefetched one tile ahead: rank inside (tile, bucket) by shared-memory
+//            atomics with return, bucket-sort the tile in shared memory, reserve space per
+//            bucket with one global atomic per (tile, bucket) - its L2 round trip overlaps
+//            the sort - then a coalesced copy-out of ~256-byte runs;
 //   grid.sync();
 //   phase B (CTA = bucket x slice): stream the bucket slice with 128-bit L2 loads and
 //            atomically add into the CTA's persistent shared-memory table.
 // Tables are flushed once at the end with RED.global.  Keys that do not fit the
 // bucket's region (skewed distributions) take a warp-aggregated global atomic.
-// Integer results are bit-exact (integer addition is associative).
+// Integer results are bit-exact (integer addition is associative and commutative).
+//
+// Where the time goes (B200, C4, profiles/r1_c4_partition_notes.md): both phases are bound by
+// the shared-memory pipeline - random 4-byte accesses hit ~3.5-way bank conflicts, and a key
+// costs one ATOMS with return + one scattered STS in phase A and one ATOMS in phase B
+// (~18 cycles per 32 keys per SM, ~0.5 ms for 2^28 keys) - not by HBM (0.15 ms) or L2.
+// Tried and measured slower or equal: TMA bulk loads into an in-place ring, L2 prefetch,
+// fixed-slot staging with a warp-per-bucket copy-out, carrying phase-B loads through phase A.
+#include <algorithm>
+#include <cstdlib>
 #include <mutex>
 #include "common.cuh"
 #include "kernels.h"
@@ -28,16 +39,25 @@
 namespace db200 {
 
 constexpr int kPartThreads = 1024;
-constexpr int kTileKeys = 8192;                 // 8 keys per thread
-constexpr int kKeysPerThread = kTileKeys / kPartThreads;
+constexpr int kGroups = 4;                       // independent quarters of the CTA in phase A (named barriers)
+constexpr int kGroupThreads = kPartThreads / kGroups;
+constexpr int kKeysPerThread = 8;
+constexpr int kTileKeys = kGroupThreads * kKeysPerThread;   // 2048 keys per group tile
 constexpr int kBucketBits = 15;                 // 32768 bins per bucket = 128 KiB of 4-byte counters
 constexpr int kBucketBins = 1 << kBucketBits;
 constexpr int kMaxBuckets = 64;
-constexpr size_t kChunkKeys = size_t(1) << 23;  // 32 MiB of keys per chunk
+constexpr int kCntSlots = kMaxBuckets + 1;      // + the bucket that collects out-of-range keys
+constexpr size_t kChunkKeysDefault = size_t(1) << 24;  // ~64 MiB of keys per chunk (measured best of 2^22..2^26)
 constexpr size_t kMaxChunks = 4096;
+constexpr int kPhaseBUnroll = 8;              // 128-bit L2 loads in flight per thread in phase B
 
 template <class V>
 __device__ __forceinline__ void smem_add_v(V* p, V v) { atomicAdd(p, v); }
+
+// Barrier among the kGroupThreads threads of one group (ids 1..kGroups; 0 is __syncthreads / grid.sync).
+__device__ __forceinline__ void group_sync(unsigned g) {
+    asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kGroupThreads) : "memory");
+}
 
 template <class V>
 __global__ void __launch_bounds__(kPartThreads, 1)
@@ -45,14 +65,24 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
                          unsigned* buf, unsigned* gcur, size_t chunk, unsigned cap, int B, int S, int aligned) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     V* hist = reinterpret_cast<V*>(smem_raw);                                  // [kBucketBins]
-    unsigned* stage = reinterpret_cast<unsigned*>(smem_raw + size_t(kBucketBins) * sizeof(V));   // [kTileKeys]
-    __shared__ unsigned cnt[kMaxBuckets], off[kMaxBuckets], gbase[kMaxBuckets];
-    __shared__ unsigned tile_total;
+    unsigned* stage_all = reinterpret_cast<unsigned*>(smem_raw + size_t(kBucketBins) * sizeof(V));   // [kGroups][kTileKeys]
+    __shared__ unsigned s_cnt[kGroups][kCntSlots], s_off[kGroups][kCntSlots], s_delta[kGroups][kCntSlots],
+        s_gbase[kGroups][kCntSlots];
+    __shared__ unsigned s_ovf[kGroups];
 
     cg::grid_group grid = cg::this_grid();
     const unsigned tid = threadIdx.x;
     const unsigned lane = tid & 31;
+    const unsigned g = tid / kGroupThreads, gtid = tid % kGroupThreads;
+    unsigned* stage = stage_all + g * kTileKeys;
+    unsigned* cnt = s_cnt[g];
+    unsigned* off = s_off[g];
+    unsigned* delta = s_delta[g];
+    unsigned* gbase = s_gbase[g];
+    const unsigned uB = unsigned(B);
+
     for (unsigned i = tid; i < kBucketBins; i += kPartThreads) hist[i] = V(0);
+    if (gtid < kCntSlots) cnt[gtid] = 0;
     __syncthreads();
 
     const size_t nchunks = (n + chunk - 1) / chunk;
@@ -60,45 +90,50 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
         // ------------------------------ phase A: partition ------------------------------
         const size_t chunk_lo = c * chunk;
         const size_t chunk_n = (n - chunk_lo < chunk) ? (n - chunk_lo) : chunk;
-        const size_t ntiles = (chunk_n + kTileKeys - 1) / kTileKeys;
+        const unsigned ntiles = unsigned((chunk_n + kTileKeys - 1) / kTileKeys);
         unsigned* bufc = buf + size_t(c & 1) * size_t(B) * cap;
         unsigned* cur = gcur + c * size_t(B);
         const unsigned* ck = keys + chunk_lo;
 
         unsigned knext[kKeysPerThread];
-        auto load_tile = [&](size_t t, unsigned (&k)[kKeysPerThread]) {
-            const size_t base = t * kTileKeys;
+        auto load_tile = [&](unsigned t, unsigned (&k)[kKeysPerThread]) {
+            const size_t base = size_t(t) * kTileKeys;
             if (aligned && base + kTileKeys <= chunk_n) {
 #pragma unroll
                 for (int u = 0; u < kKeysPerThread / 4; ++u) {
-                    Words<16> w = ldg_stream16(ck + base + (size_t(tid) + size_t(u) * kPartThreads) * 4);
+                    Words<16> w = ldg_stream16(ck + base + (size_t(gtid) + size_t(u) * kGroupThreads) * 4);
 #pragma unroll
                     for (int j = 0; j < 4; ++j) k[u * 4 + j] = w.w[j];
                 }
             } else {
 #pragma unroll
                 for (int j = 0; j < kKeysPerThread; ++j) {
-                    const size_t i = base + tid + size_t(j) * kPartThreads;
+                    const size_t i = base + gtid + size_t(j) * kGroupThreads;
                     k[j] = i < chunk_n ? __ldg(ck + i) : 0xffffffffu;   // 0xffffffff is never a valid bin
                 }
             }
         };
-        size_t t = blockIdx.x;
+        const unsigned tstride = gridDim.x * kGroups;
+        unsigned t = blockIdx.x * kGroups + g;
         if (t < ntiles) load_tile(t, knext);
-        for (; t < ntiles; t += gridDim.x) {
+        for (; t < ntiles; t += tstride) {
             unsigned k[kKeysPerThread], rank[kKeysPerThread];
 #pragma unroll
             for (int j = 0; j < kKeysPerThread; ++j) k[j] = knext[j];
-            if (t + gridDim.x < ntiles) load_tile(t + gridDim.x, knext);   // software prefetch of the next tile
-            if (tid < kMaxBuckets) cnt[tid] = 0;
-            __syncthreads();
+            if (t + tstride < ntiles) load_tile(t + tstride, knext);   // software prefetch of the next tile
+            // rank inside (tile, bucket); keys >= nbins land in bucket index >= B and are dropped
 #pragma unroll
             for (int j = 0; j < kKeysPerThread; ++j)
-                rank[j] = k[j] < nbins ? atomicAdd(&cnt[k[j] >> kBucketBits], 1u) : 0u;
-            __syncthreads();
-            if (tid < 32) {
-                // exclusive scan over <= 64 buckets + one global reservation per non-empty bucket
-                const unsigned c0 = cnt[lane], c1 = cnt[lane + 32];
+                rank[j] = atomicAdd(&cnt[min(k[j] >> kBucketBits, uB)], 1u);
+            group_sync(g);
+            unsigned c0 = 0, c1 = 0, o0 = 0, o1 = 0, gb0 = 0, gb1 = 0;
+            if (gtid < 32) {
+                // exclusive scan over the 64 bucket counters, one global reservation per non-empty bucket
+                c0 = cnt[lane];
+                c1 = cnt[lane + 32];
+                cnt[lane] = 0;
+                cnt[lane + 32] = 0;
+                if (lane == 0) cnt[kMaxBuckets] = 0;
                 unsigned i0 = c0, i1 = c1;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
@@ -106,37 +141,68 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
                     if (lane >= (unsigned)d) { i0 += a0; i1 += a1; }
                 }
                 const unsigned tot0 = __shfl_sync(kFullMask, i0, 31);
-                off[lane] = i0 - c0;
-                off[lane + 32] = tot0 + i1 - c1;
-                if (lane == 31) tile_total = tot0 + i1;
-                if (c0) gbase[lane] = atomicAdd(&cur[lane], c0);
-                if (c1) gbase[lane + 32] = atomicAdd(&cur[lane + 32], c1);
+                o0 = i0 - c0;
+                o1 = tot0 + i1 - c1;
+                off[lane] = o0;
+                off[lane + 32] = o1;
+                if (lane == 31) off[kMaxBuckets] = tot0 + i1;
+                // the L2 round trip of the reservations overlaps the staging below; results are used after it
+                if (lane < uB && c0) gb0 = atomicAdd(&cur[lane], c0);
+                if (lane + 32 < uB && c1) gb1 = atomicAdd(&cur[lane + 32], c1);
             }
-            __syncthreads();
+            group_sync(g);
 #pragma unroll
             for (int j = 0; j < kKeysPerThread; ++j)
-                if (k[j] < nbins) stage[off[k[j] >> kBucketBits] + rank[j]] = k[j];
-            __syncthreads();
-            const unsigned total = tile_total;
-            for (unsigned sb = 0; sb < total; sb += kPartThreads) {   // warp-uniform trip count
-                const unsigned slot = sb + tid;
-                const bool valid = slot < total;
-                unsigned key = 0, dst = 0, b = 0;
-                if (valid) {
-                    key = stage[slot];
-                    b = key >> kBucketBits;
-                    dst = gbase[b] + (slot - off[b]);
+                stage[off[min(k[j] >> kBucketBits, uB)] + rank[j]] = k[j];
+            if (gtid < 32) {
+                gbase[lane] = gb0;
+                gbase[lane + 32] = gb1;
+                delta[lane] = lane * cap + gb0 - o0;
+                delta[lane + 32] = (lane + 32) * cap + gb1 - o1;
+                const bool over = __any_sync(kFullMask, (gb0 + c0 > cap) || (gb1 + c1 > cap));
+                if (lane == 0) s_ovf[g] = over;
+            }
+            group_sync(g);
+            const unsigned total = off[uB];   // valid keys of the tile (the out-of-range bucket sorts last)
+            const unsigned ovf_tile = s_ovf[g];
+            if (total == unsigned(kTileKeys) && !ovf_tile) {
+                unsigned key[kKeysPerThread], d[kKeysPerThread];
+#pragma unroll
+                for (int j = 0; j < kKeysPerThread; ++j) key[j] = stage[j * kGroupThreads + gtid];
+#pragma unroll
+                for (int j = 0; j < kKeysPerThread; ++j) d[j] = delta[key[j] >> kBucketBits];
+#pragma unroll
+                for (int j = 0; j < kKeysPerThread; ++j) bufc[j * kGroupThreads + gtid + d[j]] = key[j];
+            } else if (!ovf_tile) {
+#pragma unroll
+                for (int j = 0; j < kKeysPerThread; ++j) {
+                    const unsigned slot = j * kGroupThreads + gtid;
+                    if (slot < total) {
+                        const unsigned key = stage[slot];
+                        bufc[slot + delta[key >> kBucketBits]] = key;
+                    }
                 }
-                const bool fits = valid && dst < cap;
-                if (fits) bufc[size_t(b) * cap + dst] = key;
-                const unsigned ovf = __ballot_sync(kFullMask, valid && !fits);
-                if (ovf && valid && !fits) {
-                    // bucket region full (skew): warp-aggregated atomic straight into the bins
-                    const unsigned peers = __match_any_sync(ovf, key);
-                    if (lane == unsigned(__ffs(peers) - 1)) atomicAdd(bins + key, cval * V(__popc(peers)));
+            } else {
+                // a bucket region is full (skewed keys): what does not fit goes straight to the bins
+                for (unsigned sb = 0; sb < total; sb += kGroupThreads) {   // warp-uniform trip count
+                    const unsigned slot = sb + gtid;
+                    const bool valid = slot < total;
+                    unsigned key = 0, dst = 0, b = 0;
+                    if (valid) {
+                        key = stage[slot];
+                        b = key >> kBucketBits;
+                        dst = gbase[b] + (slot - off[b]);
+                    }
+                    const bool fits = valid && dst < cap;
+                    if (fits) bufc[size_t(b) * cap + dst] = key;
+                    const unsigned ovf = __ballot_sync(kFullMask, valid && !fits);
+                    if (valid && !fits) {
+                        const unsigned peers = __match_any_sync(ovf, key);
+                        if (lane == unsigned(__ffs(peers) - 1) && key < nbins) atomicAdd(bins + key, cval * V(__popc(peers)));
+                    }
                 }
             }
-            __syncthreads();
+            // no barrier here: the next tile touches cnt only (zeroed above) until its first group_sync
         }
         grid.sync();
         // ------------------------------ phase B: histogram ------------------------------
@@ -150,12 +216,12 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
             const unsigned nvec = (hi - lo) / 4;
             const uint4* v4 = reinterpret_cast<const uint4*>(src + lo);
             unsigned v = tid;
-            for (; v + 3 * kPartThreads < nvec; v += 4 * kPartThreads) {
-                uint4 w[4];
+            for (; v + (kPhaseBUnroll - 1) * kPartThreads < nvec; v += kPhaseBUnroll * kPartThreads) {
+                uint4 w[kPhaseBUnroll];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) w[u] = __ldcg(v4 + v + u * kPartThreads);
+                for (int u = 0; u < kPhaseBUnroll; ++u) w[u] = __ldcg(v4 + v + u * kPartThreads);
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < kPhaseBUnroll; ++u) {
                     smem_add_v(hist + (w[u].x & (kBucketBins - 1)), cval);
                     smem_add_v(hist + (w[u].y & (kBucketBins - 1)), cval);
                     smem_add_v(hist + (w[u].z & (kBucketBins - 1)), cval);
@@ -207,12 +273,18 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Laun
     const int sms = sm_count();
     if (B > kMaxBuckets || B > sms) return cudaErrorNotSupported;
     const int S = sms / B;
-    const size_t chunk = kChunkKeys;
+    // every group of every CTA gets the same number of tiles per chunk (the grid barrier waits for the slowest)
+    const size_t wave = size_t(sms) * kPartThreads * kKeysPerThread;
+    size_t chunk = wave * std::max<size_t>(1, (kChunkKeysDefault + wave / 2) / wave);
+    if (const char* ev = getenv("DACE_B200_PART_CHUNK_LOG2")) {   // tuning knob for experiments
+        const int lg = atoi(ev);
+        if (lg >= 20 && lg <= 26) chunk = wave * std::max<size_t>(1, ((size_t(1) << lg) + wave / 2) / wave);
+    }
     const size_t nchunks = (a.n + chunk - 1) / chunk;
     if (nchunks > kMaxChunks) return cudaErrorNotSupported;
     // 1.5x the uniform share per bucket, multiple of 4 words so every bucket base stays 16-byte aligned
     const unsigned cap = unsigned(((chunk * 3 / 2) / B + 3) & ~size_t(3));
-    const size_t smem = size_t(kBucketBins) * sizeof(V) + size_t(kTileKeys) * sizeof(unsigned);
+    const size_t smem = size_t(kBucketBins) * sizeof(V) + size_t(kGroups) * kTileKeys * sizeof(unsigned);
     auto kern = scatter_partition_kernel<V>;
 
     std::lock_guard<std::mutex> lock(g_part_mutex);
@@ -236,7 +308,7 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Laun
     if (ps.buf == nullptr || ps.buf_words < buf_words) {
         if (ps.buf) { cudaFree(ps.buf); ps.buf = nullptr; }
         // 2 * 1.5 * chunk words (+ rounding slack for any B) = ~96 MiB
-        const size_t alloc_words = 2 * (chunk * 3 / 2 + 4 * size_t(kMaxBuckets));
+        const size_t alloc_words = buf_words + 8 * size_t(kMaxBuckets);
         e = cudaMalloc(&ps.buf, alloc_words * sizeof(unsigned));
         if (e != cudaSuccess) { ps.buf = nullptr; return e; }
         ps.buf_words = alloc_words;
