@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 2
+VERSION = 3
 
 
 def up_to_date() -> bool:
@@ -104,6 +104,49 @@ def _programs(dace):
     st.add_nedge(st.add_read('A'), r, dace.Memlet.from_array('A', sdfg.arrays['A']))
     st.add_nedge(r, st.add_write('B'), dace.Memlet.from_array('B', sdfg.arrays['B']))
     progs.append(sdfg)
+
+    # (5) WCR maps (scatter-add / histograms): unmodified @dace.programs; the map is rewritten into a
+    #     ScatterReduce library node expanded with 'B200' (dace_b200/scatter_node.py).
+    from dace_b200 import scatter_node as SN
+
+    @dace.program
+    def b200_hist_augassign(keys: dace.int32[N], bins: dace.int32[M]):
+        for i in dace.map[0:N]:
+            bins[keys[i]] += 1
+
+    @dace.program
+    def b200_hist_explicit_wcr(keys: dace.int32[N], bins: dace.uint32[M]):   # reference samples/explicit/histogram.py:13-26
+        for i in dace.map[0:N]:
+            with dace.tasklet:
+                k << keys[i]
+                out >> bins(1, lambda x, y: x + y)[:]
+                out[k] = 1
+
+    @dace.program
+    def b200_hist_weighted_f32(keys: dace.int32[N], w: dace.float32[N], bins: dace.float32[M]):
+        for i in dace.map[0:N]:
+            bins[keys[i]] += w[i]
+
+    @dace.program
+    def b200_scatter_max_f64(keys: dace.int64[N], w: dace.float64[N], bins: dace.float64[M]):
+        for i in dace.map[0:N]:
+            with dace.tasklet:
+                k << keys[i]
+                v << w[i]
+                out >> bins(1, lambda x, y: max(x, y))[:]
+                out[k] = v
+
+    for j, p in enumerate((b200_hist_augassign, b200_hist_explicit_wcr, b200_hist_weighted_f32, b200_scatter_max_f64)):
+        sdfg = p.to_sdfg(simplify=True)
+        if j % 2 == 0:   # both orders of the two rewrites are supported
+            sdfg.apply_gpu_transformations()
+            applied = SN.use_b200_scatter(sdfg)
+        else:
+            applied = SN.use_b200_scatter(sdfg)
+            sdfg.apply_gpu_transformations()
+        if applied != 1:
+            raise RuntimeError('%s: WCRMapToScatterReduce applied %d times' % (sdfg.name, applied))
+        progs.append(sdfg)
     return progs
 
 
@@ -136,7 +179,7 @@ def build_all(verbose=True):
             manifest['programs'][name] = {
                 'lib': lib, 'args': args,
                 'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
-                'b200_calls': src.count('dace_b200_reduce_nd('),
+                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter('),
             }
             if verbose:
                 print('built', name, [a['name'] for a in args], 'b200 calls:', manifest['programs'][name]['b200_calls'],

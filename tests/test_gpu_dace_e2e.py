@@ -127,3 +127,46 @@ def test_device_resident_arrays(cuda):
     torch.cuda.synchronize()
     p._exit(state)
     assert abs(out.item() - x.double().sum().item()) <= 1e-5 * x.double().abs().sum().item()
+
+
+# ---- WCR maps rewritten into the ScatterReduce library node (dace_b200/scatter_node.py) ----
+
+def test_histogram_augassign_program(cuda):
+    """``bins[keys[i]] += 1`` in a @dace.program (the npbench azimint_hist pattern)."""
+    rng = np.random.default_rng(7)
+    for n, m in ((100000, 256), (1 << 22, 1 << 20), (5, 3)):
+        keys = rng.integers(0, m, n).astype(np.int32)
+        bins = rng.integers(0, 9, m).astype(np.int32)
+        exp = O.wcr_scatter(O.SUM, bins.copy(), keys)
+        prog('b200_hist_augassign')(keys=keys, bins=bins, N=n, M=m)
+        np.testing.assert_array_equal(bins, exp)
+        np.testing.assert_array_equal(bins, exp)
+
+
+def test_histogram_explicit_wcr_tasklet(cuda):
+    """reference samples/explicit/histogram.py:13-26 (explicit WCR memlet), uint32 bins."""
+    rng = np.random.default_rng(8)
+    keys = rng.integers(0, 1000, 300000).astype(np.int32)
+    bins = np.zeros(1000, np.uint32)
+    prog('b200_hist_explicit_wcr')(keys=keys, bins=bins, N=keys.size, M=bins.size)
+    np.testing.assert_array_equal(bins, np.bincount(keys, minlength=1000).astype(np.uint32))
+
+
+def test_weighted_histogram_f32(cuda):
+    rng = np.random.default_rng(9)
+    keys = rng.integers(0, 4096, 200000).astype(np.int32)
+    w = rng.random(200000, dtype=np.float32)
+    bins = np.zeros(4096, np.float32)
+    prog('b200_hist_weighted_f32')(keys=keys, w=w, bins=bins, N=keys.size, M=bins.size)
+    ref = np.bincount(keys, weights=w.astype(np.float64), minlength=4096)
+    np.testing.assert_allclose(bins, ref, rtol=1e-5)
+
+
+def test_scatter_max_f64(cuda):
+    rng = np.random.default_rng(10)
+    keys = rng.integers(0, 777, 50000)
+    w = rng.standard_normal(50000)
+    bins = np.full(777, -0.25)
+    exp = O.wcr_scatter(O.MAX, bins.copy(), keys, w)
+    prog('b200_scatter_max_f64')(keys=keys, w=w, bins=bins, N=keys.size, M=bins.size)
+    np.testing.assert_array_equal(bins, exp)
