@@ -221,6 +221,69 @@ def cpu_reference_run(workload, budget_s=12.0, max_reps=5):
             'best_s': best, 'reps': len(times), 'nbytes': nbytes}
 
 
+# ---------------------------------------------------------------------------
+# The reference's own GPU expansions (CUB 'CUDA (device)', 'GPUAuto', generated
+# WCR-map kernel) built for sm_100 by oracle/build_ref.py, on device-resident
+# arrays of the same shapes: the on-box GPU comparison (--extras only).  The
+# generated programs launch on their own streams, so they are timed by wall clock
+# with a device synchronise after every call.
+# ---------------------------------------------------------------------------
+def reference_gpu_run(torch, dev, reps=10):
+    from oracle import ref_loader
+    if not ref_loader.available():
+        return None
+    have = ref_loader.manifest()['programs']
+    out = {}
+
+    def run(tag, prog, nbytes, make):
+        if prog not in have:
+            return
+        try:
+            p = ref_loader.RefProgram(prog)
+            keep, kwargs = make()
+            for _ in range(2):
+                p(**kwargs)
+                torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                p(**kwargs)
+                torch.cuda.synchronize()
+            ms = (time.perf_counter() - t0) / reps * 1e3
+            out[tag] = {'GB/s': nbytes / (ms * 1e-3) / 1e9, 'ms': ms, 'program': prog}
+            p.close()
+            del keep
+        except Exception as ex:
+            out[tag] = {'error': str(ex)[:200]}
+        torch.cuda.empty_cache()
+
+    def c2():
+        a = torch.rand(1 << 30, device=dev)
+        b = torch.zeros(1, device=dev)
+        return (a, b), {'A': a.data_ptr(), 'B': b.data_ptr(), 'D0': a.numel()}
+
+    def c3():
+        a = torch.randn(65536, 8192, device=dev, dtype=torch.bfloat16)
+        b = torch.zeros(65536, device=dev, dtype=torch.bfloat16)
+        return (a, b), {'A': a.data_ptr(), 'B': b.data_ptr(), 'D0': 65536, 'D1': 8192}
+
+    def c5():
+        a = torch.rand(1 << 19, 4096, device=dev)
+        b = torch.zeros(4096, device=dev)
+        return (a, b), {'A': a.data_ptr(), 'B': b.data_ptr(), 'D0': 1 << 19, 'D1': 4096}
+
+    def c4():
+        k = torch.randint(0, 1 << 20, (1 << 28, ), device=dev, dtype=torch.int32)
+        b = torch.zeros(1 << 20, device=dev, dtype=torch.int32)
+        return (k, b), {'keys': k.data_ptr(), 'bins': b.data_ptr(), 'N': k.numel()}
+
+    run('c2_cub', 'refgpu_full_sum_f32_cub', WORKLOADS['c2'][1], c2)
+    run('c2_gpuauto', 'refgpu_full_sum_f32_gpuauto', WORKLOADS['c2'][1], c2)
+    run('c3_rowsum_bf16_cub', 'refgpu_row_sum_bf16_cub', 65536 * 8192 * 2 + 65536 * 2, c3)
+    run('c4_wcr_map_kernel', 'refgpu_hist_i32', WORKLOADS['c4'][1], c4)
+    run('c5_shard_colsum_gpuauto', 'refgpu_col_sum_f32_gpuauto', WORKLOADS['c5'][1], c5)
+    return out
+
+
 def run_reference_arm(args):
     """--impl reference: the reference's own CPU expansion of the path on the host cores."""
     rank = int(os.environ.get('RANK', '0'))
@@ -399,6 +462,14 @@ def main():
                             'frac_of_hbm_peak': WORKLOADS[name][1] / (t_ms * 1e-3) / 1e9 / peaks()[0]}
             del ww
             torch.cuda.empty_cache()
+        flush_buf = None
+        torch.cuda.empty_cache()
+        try:
+            refgpu = reference_gpu_run(torch, dev)
+        except Exception as ex:
+            refgpu = {'error': str(ex)[:200]}
+        if refgpu:
+            others['reference_gpu'] = refgpu
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -27,7 +27,7 @@ from .refenv import import_reference, reference_available  # noqa: F401
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REF_DIR = os.path.join(_HERE, '_ref')
 MANIFEST = os.path.join(REF_DIR, 'manifest.json')
-VERSION = 4
+VERSION = 5
 
 
 def up_to_date() -> bool:
@@ -146,6 +146,51 @@ def _programs(dace):
     return progs
 
 
+def _gpu_programs(dace):
+    """The reference's own GPU lowerings of the path, on device-resident (GPU_Global) arrays, built
+    for sm_100: the on-box GPU comparison SURVEY.md 8(d) asks for (C2 "vs the reference CUB
+    expansion").  Expansions: 'CUDA (device)' = CUB (reference reduce.py:391-622), 'GPUAuto'
+    (reduce.py:886-1343), and the generated one-atomic-per-key WCR kernel (cpu.py:965-1013)."""
+    add, mx = 'lambda a, b: a + b', 'lambda a, b: max(a, b)'
+    f32, i32 = dace.float32, dace.int32
+    G = dace.StorageType.GPU_Global
+    progs = []
+    fmax = 3.4028234663852886e38
+    for name, din, dout, nd, axes, wcr, ident, impl in (
+        ('refgpu_full_sum_f32_cub', f32, f32, 1, None, add, 0, 'CUDA (device)'),
+        ('refgpu_full_sum_f32_gpuauto', f32, f32, 1, None, add, 0, 'GPUAuto'),
+        ('refgpu_row_sum_f32_cub', f32, f32, 2, [1], add, 0, 'CUDA (device)'),
+        ('refgpu_row_sum_f32_gpuauto', f32, f32, 2, [1], add, 0, 'GPUAuto'),
+        ('refgpu_row_max_f32_cub', f32, f32, 2, [1], mx, -fmax, 'CUDA (device)'),
+        ('refgpu_col_sum_f32_gpuauto', f32, f32, 2, [0], add, 0, 'GPUAuto'),
+        ('refgpu_row_sum_i32_cub', i32, i32, 2, [1], add, 0, 'CUDA (device)'),
+        ('refgpu_row_sum_bf16_cub', dace.bfloat16, dace.bfloat16, 2, [1], add, 0, 'CUDA (device)'),
+    ):
+        sdfg = _reduce_sdfg(dace, name, din, dout, nd, axes, wcr, ident, impl)
+        sdfg.arrays['A'].storage = G
+        sdfg.arrays['B'].storage = G
+        progs.append((sdfg, {'kind': 'reduce_gpu', 'impl': impl, 'axes': axes, 'wcr': wcr, 'identity': ident}))
+
+    N, NB = dace.symbol('N', dace.int64), dace.symbol('NB', dace.int64)
+
+    @dace.program
+    def refgpu_hist_i32(keys: dace.int32[N], bins: dace.int32[NB]):
+        for i in dace.map[0:N]:
+            with dace.tasklet:
+                k << keys[i]
+                out >> bins(1, lambda x, y: x + y)[:]
+                out[k] = 1
+
+    sdfg = refgpu_hist_i32.to_sdfg()
+    sdfg.arrays['keys'].storage = G
+    sdfg.arrays['bins'].storage = G
+    for n, _ in sdfg.all_nodes_recursive():
+        if isinstance(n, dace.nodes.MapEntry):
+            n.map.schedule = dace.ScheduleType.GPU_Device
+    progs.append((sdfg, {'kind': 'wcr_map_gpu', 'impl': 'wcr-gpu-atomic'}))
+    return progs
+
+
 def build_all(verbose: bool = True) -> dict:
     tmp = tempfile.mkdtemp(prefix='dace_b200_refbuild_')
     cwd = os.getcwd()
@@ -156,9 +201,18 @@ def build_all(verbose: bool = True) -> dict:
             raise RuntimeError('reference checkout not available')
         os.makedirs(REF_DIR, exist_ok=True)
         manifest = {'version': VERSION, 'reference_version': dace.__version__, 'programs': {}}
-        for sdfg, meta in _programs(dace):
+        manifest['failed'] = {}
+        for sdfg, meta in _programs(dace) + _gpu_programs(dace):
             name = sdfg.name
-            csdfg = sdfg.compile()
+            try:
+                csdfg = sdfg.compile()
+            except Exception as ex:   # only tolerated for the GPU comparison programs
+                if not meta['kind'].endswith('_gpu'):
+                    raise
+                manifest['failed'][name] = str(ex).splitlines()[0][:300] if str(ex) else type(ex).__name__
+                if verbose:
+                    print('FAILED', name, manifest['failed'][name], file=sys.stderr)
+                continue
             lib = 'lib%s.so' % name
             shutil.copyfile(csdfg.filename, os.path.join(REF_DIR, lib))
             # Signatures are only final after library-node expansion: read them

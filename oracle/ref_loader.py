@@ -1,4 +1,5 @@
-"""ctypes loader for the reference's own compiled CPU programs in oracle/_ref/.
+"""ctypes loader for the reference's own compiled programs in oracle/_ref/ (CPU expansions, and the
+reference's GPU expansions built for sm_100 as the on-box GPU comparison).
 
 TEST INFRASTRUCTURE ONLY (checker + timed CPU baseline).  Needs no DaCe import:
 the generated libraries export ``__dace_init_<n>(symbols...) -> state*``,
@@ -62,7 +63,9 @@ class RefProgram:
         call = []
         for a in self.meta['args']:
             v = kwargs[a['name']]
-            if a['kind'] == 'array':
+            if a['kind'] == 'array' and isinstance(v, int):
+                call.append(v)   # raw (device) pointer for GPU_Global arrays of the reference's GPU programs
+            elif a['kind'] == 'array':
                 if not isinstance(v, np.ndarray) or not v.flags.c_contiguous:
                     raise ValueError('array argument %s must be a C-contiguous ndarray' % a['name'])
                 call.append(v.ctypes.data)
