@@ -38,6 +38,15 @@ WORKLOADS = {
 }
 
 
+def recorded_traffic(workload):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
+            return json.load(f).get(workload, {}).get('bytes')
+    except Exception:
+        return None
+
+
 def peaks():
     path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     try:
@@ -492,7 +501,7 @@ def main():
                        'l2': 'L2 flushed (512 MiB write) between timed iterations' if needs_flush and others is None
                              else 'inputs (>= 1 GiB) far larger than the 126 MB L2'},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': UNIT, 'frac': achieved / peak,
-                         'traffic': None, 'peak_source': peak_src, 'kernel_ms': kernel_ms,
+                         'traffic': recorded_traffic(args.workload) if world == 1 else None, 'peak_source': peak_src, 'kernel_ms': kernel_ms,
                          'frac_of_8TBs_nominal': achieved / 8000.0},
             'cpu_baseline': cpu, 'e2e': e2e, 'gpu_launches': args.steps, 'clocks': clocks,
         }
