@@ -116,26 +116,48 @@ scatter_global_kernel(const I* __restrict__ idx, const V* __restrict__ values, V
         if (h > n) h = n;
         const char* pv = reinterpret_cast<const char*>(idx + h);
         const size_t nvec = (n - h) / N;
-        size_t v = tid;
-        for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
+        // Warp-uniform trip count (every lane of a warp runs the same iterations, out-of-range lanes
+        // carry an invalid key), so the warp can vote.  Every 16th iteration the warp samples one key
+        // per lane: if a quarter of the lanes see a duplicate, the keys are skewed and the next
+        // iterations merge equal keys inside the warp (match.any + one atomic per distinct key)
+        // instead of hammering one L2 address 32 times.  Uniform keys never pay for the merge.
+        constexpr bool kCanMerge = RED == RT_Sum || RED == RT_Min || RED == RT_Max;
+        const unsigned lane = threadIdx.x & 31;
+        bool merge = false;
+        unsigned it = 0;
+        for (size_t vb = tid - lane; vb < nvec; vb += size_t(U) * nthr, ++it) {
             Words<16> w[U];
+            bool have[U];
 #pragma unroll
-            for (int u = 0; u < U; ++u) w[u] = ldg_stream16(pv + (v + size_t(u) * nthr) * 16);
+            for (int u = 0; u < U; ++u) {
+                const size_t vi = vb + lane + size_t(u) * nthr;
+                have[u] = vi < nvec;
+                if (have[u]) w[u] = ldg_stream16(pv + vi * 16);
+            }
+            if constexpr (kCanMerge) {
+                if ((it & 15u) == 0) {
+                    const long long k0 = have[0] ? idx_at<I>(w[0], 0) : -1 - (long long)lane;
+                    const unsigned same = __match_any_sync(kFullMask, k0);
+                    merge = __popc(__ballot_sync(kFullMask, __popc(same) > 1)) >= 8;
+                }
+            }
 #pragma unroll
             for (int u = 0; u < U; ++u)
 #pragma unroll
                 for (int j = 0; j < N; ++j) {
-                    long long k = idx_at<I>(w[u], j);
-                    if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(bins + k, cval);
+                    const long long k = have[u] ? idx_at<I>(w[u], j) : -1;
+                    const bool ok = k >= 0 && (size_t)k < nbins;
+                    if (kCanMerge && merge) {
+                        const unsigned act = __ballot_sync(kFullMask, ok);
+                        if (ok) {
+                            const unsigned peers = __match_any_sync(act, k);
+                            if (lane == unsigned(__ffs(peers) - 1))
+                                atomic_reduce<RED, V>(bins + k, RED == RT_Sum ? V(cval * V(__popc(peers))) : cval);
+                        }
+                    } else if (ok) {
+                        atomic_reduce<RED, V>(bins + k, cval);
+                    }
                 }
-        }
-        for (; v < nvec; v += nthr) {
-            Words<16> w = ldg_stream16(pv + v * 16);
-#pragma unroll
-            for (int j = 0; j < N; ++j) {
-                long long k = idx_at<I>(w, j);
-                if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(bins + k, cval);
-            }
         }
         for (size_t i = tid; i < h; i += nthr) {
             long long k = (long long)ldg_scalar(idx + i);

@@ -198,3 +198,33 @@ def test_partitioned_histogram_variants(cuda):
     torch.cuda.synchronize()
     np.testing.assert_array_equal(b1.cpu().numpy(), 3 * ref)
     np.testing.assert_array_equal(b2.cpu().numpy(), 3 * ref)
+
+
+@pytest.mark.parametrize('dist', ['all_equal', 'sorted', 'zipf', 'uniform'])
+def test_global_path_merges_equal_keys_in_a_warp(dist, cuda):
+    """Large int64 / min / max bin arrays take the global-atomic kernel, which switches to
+    warp-merged atomics when a warp samples duplicate keys (skewed or sorted inputs)."""
+    rng = np.random.default_rng(11)
+    n, nbins = (1 << 22) + 77, 1 << 18
+    if dist == 'all_equal':
+        keys = np.full(n, 4242)
+    elif dist == 'sorted':
+        keys = np.sort(rng.integers(0, nbins, n))
+    elif dist == 'zipf':
+        keys = np.minimum(rng.zipf(1.2, n) - 1, nbins - 1)
+    else:
+        keys = rng.integers(-2, nbins + 2, n)
+    keys = keys.astype(np.int32)
+    tk = torch.from_numpy(keys).to(cuda)
+    ok = keys[(keys >= 0) & (keys < nbins)]
+    b64 = torch.zeros(nbins, dtype=torch.int64, device=cuda)
+    db.wcr_scatter('lambda a, b: a + b', b64, tk, 5)
+    np.testing.assert_array_equal(b64.cpu().numpy(), 5 * np.bincount(ok, minlength=nbins))
+    bmax = torch.full((nbins, ), -7, dtype=torch.int32, device=cuda)
+    db.wcr_scatter('lambda a, b: max(a, b)', bmax, tk, 9)
+    exp = np.full(nbins, -7, np.int32)
+    exp[np.unique(ok)] = 9
+    np.testing.assert_array_equal(bmax.cpu().numpy(), exp)
+    bf = torch.zeros(nbins, dtype=torch.float64, device=cuda)
+    db.wcr_scatter('lambda a, b: a + b', bf, tk, 0.25)
+    np.testing.assert_array_equal(bf.cpu().numpy(), 0.25 * np.bincount(ok, minlength=nbins))
