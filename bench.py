@@ -336,6 +336,8 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--e2e-steps', type=int, default=3)
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--combine', choices=('peer', 'nccl'), default='peer',
+                    help='N>1: combine the per-GPU partials with the one-shot NVLink peer-memory kernel (default) or NCCL')
     ap.add_argument('--extras', action='store_true', help='also time the other configs (device-only) into "others"')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
@@ -364,6 +366,14 @@ def main():
     desc, bytes_per_gpu = WORKLOADS[args.workload]
     w = make_workload(args.workload, dev, rank, torch, db)
     step, result, combine = w['step'], w['result'], w['combine']
+    combine_desc = 'none'
+    if dist is not None and combine is not None:
+        combine_desc = 'NCCL allreduce of the per-GPU partials'
+        if args.combine == 'peer':
+            pc = sharding.enable_peer_combine()
+            if pc.supports(result, sharding.resolve('Sum')):
+                combine_desc = ('one-shot all-reduce kernel over NVLink peer memory (dace_b200_peer_allreduce), '
+                                '%d B per GPU' % (result.numel() * result.element_size()))
     input_bytes = sum(t.numel() * t.element_size() for t in w['inputs'])
     needs_flush = input_bytes < (256 << 20)       # inputs smaller than ~2x L2: flush between iterations
     flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device=dev) if needs_flush else None
@@ -371,7 +381,7 @@ def main():
     def full_step():
         step()
         if dist is not None and combine is not None:
-            sharding.combine(result, 'Sum')   # NCCL allreduce over NVLink, same stream as the kernel
+            sharding.combine(result, 'Sum')   # peer-memory kernel or NCCL, same stream as the local kernel
 
     def barrier():
         if dist is not None:
@@ -497,7 +507,7 @@ def main():
             'vs_baseline': None, 'dtype': dtype_of(args.workload), 'data': 'synthetic',
             'config': {'workload': desc, 'bytes_per_step_per_gpu': bytes_per_gpu,
                        'sharding': 'outer dimension, one shard per GPU' if world > 1 else 'single GPU',
-                       'combine': ('NCCL allreduce of the per-GPU partials' if (world > 1 and combine) else 'none'),
+                       'combine': combine_desc,
                        'l2': 'L2 flushed (512 MiB write) between timed iterations' if needs_flush and others is None
                              else 'inputs (>= 1 GiB) far larger than the 126 MB L2'},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': UNIT, 'frac': achieved / peak,
@@ -509,6 +519,7 @@ def main():
             line['others'] = others
         print(json.dumps(line))
     if dist is not None:
+        sharding.disable_peer_combine()
         dist.barrier()
         dist.destroy_process_group()
     return 0

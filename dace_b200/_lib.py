@@ -45,6 +45,16 @@ _PROTOTYPES = {
         _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p,
         _c.c_size_t, _c.c_void_p
     ]),
+    'dace_b200_peer_buffer_bytes': (_c.c_size_t, [_c.c_int, _c.c_size_t]),
+    'dace_b200_peer_alloc': (_c.c_int, [_c.c_size_t, _c.POINTER(_c.c_void_p)]),
+    'dace_b200_peer_free': (_c.c_int, [_c.c_void_p]),
+    'dace_b200_peer_export': (_c.c_int, [_c.c_void_p, _c.c_char_p]),
+    'dace_b200_peer_open': (_c.c_int, [_c.c_char_p, _c.POINTER(_c.c_void_p)]),
+    'dace_b200_peer_close': (_c.c_int, [_c.c_void_p]),
+    'dace_b200_peer_allreduce': (_c.c_int, [
+        _c.c_int, _c.c_int, _c.c_void_p, _c.c_size_t, _c.POINTER(_c.c_void_p), _c.c_int, _c.c_int, _c.c_uint64,
+        _c.c_size_t, _c.c_void_p
+    ]),
 }
 
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)

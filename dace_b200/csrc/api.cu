@@ -272,4 +272,44 @@ int dace_b200_wcr_scatter(int redtype, int dtype_idx, int dtype_val, const void*
     return (int)launch_scatter(redtype, dtype_idx, dtype_val, a, l);
 }
 
+// ---- multi-GPU: exchange buffers in peer memory + one-shot all-reduce (peer_combine.cu) ----
+
+size_t dace_b200_peer_buffer_bytes(int world, size_t cap_bytes) { return peer_buffer_bytes(world, cap_bytes); }
+
+int dace_b200_peer_alloc(size_t bytes, void** ptr) {
+    if (!ptr || bytes == 0) return (int)cudaErrorInvalidValue;
+    cudaError_t e = cudaMalloc(ptr, bytes);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaMemset(*ptr, 0, bytes);   // flags start at epoch 0
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    return (int)e;
+}
+
+int dace_b200_peer_free(void* ptr) { return (int)cudaFree(ptr); }
+
+int dace_b200_peer_export(void* ptr, unsigned char* handle64) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    if (!ptr || !handle64) return (int)cudaErrorInvalidValue;
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, ptr);
+    if (e == cudaSuccess) memcpy(handle64, &h, 64);
+    return (int)e;
+}
+
+int dace_b200_peer_open(const unsigned char* handle64, void** ptr) {
+    if (!ptr || !handle64) return (int)cudaErrorInvalidValue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    return (int)cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess);
+}
+
+int dace_b200_peer_close(void* ptr) { return (int)cudaIpcCloseMemHandle(ptr); }
+
+int dace_b200_peer_allreduce(int redtype, int dtype, void* data, size_t nelem, void* const* peer_bases, int rank,
+                             int world, unsigned long long epoch, size_t cap_bytes, dace_b200_stream_t stream) {
+    if (nelem > 0 && (!data || !peer_bases)) return (int)cudaErrorInvalidValue;
+    return (int)launch_peer_allreduce(redtype, dtype, data, nelem, peer_bases, rank, world, epoch, cap_bytes,
+                                      (cudaStream_t)stream);
+}
+
 }  // extern "C"

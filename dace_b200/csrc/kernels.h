@@ -64,6 +64,11 @@ struct ScatterArgs {
 cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l);
 // Partition + shared-memory histogram path for large bin arrays (wcr_partition.cu);
 // cudaErrorNotSupported = does not apply, use the global-atomic kernel.
+// peer_combine.cu: one-shot all-reduce of small partials through IPC-mapped peer buffers.
+cudaError_t launch_peer_allreduce(int red, int dtype, void* data, size_t nelem, void* const* bases, int rank, int world,
+                                  unsigned long long epoch, size_t cap_bytes, cudaStream_t stream);
+size_t peer_buffer_bytes(int world, size_t cap_bytes);
+
 cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l);
 
 }  // namespace db200

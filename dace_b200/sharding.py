@@ -72,12 +72,108 @@ def collective_op(rt: ReductionType):
     return table[rt]
 
 
+class PeerCombiner:
+    """One-shot all-reduce of small partials through NVLink peer memory
+    (``dace_b200_peer_allreduce``, dace_b200/csrc/peer_combine.cu).
+
+    Every rank allocates one exchange buffer in the kernel library, ships its CUDA IPC
+    handle to the other ranks of ``group`` (``all_gather_object``: plumbing only) and maps
+    theirs.  :meth:`allreduce` then needs no NCCL call: one small kernel pushes the partial
+    to all peers, raises a flag and folds what arrived in rank order.  Payloads up to
+    ``cap_bytes``; larger ones and unsupported dtypes/operators stay with NCCL."""
+
+    _DT = {torch.float32: 0, torch.float64: 1, torch.int32: 2, torch.int64: 3, torch.uint32: 4, torch.uint64: 5}
+    _OPS = (ReductionType.Sum, ReductionType.Product, ReductionType.Min, ReductionType.Max, ReductionType.Bitwise_And,
+            ReductionType.Bitwise_Or, ReductionType.Bitwise_Xor)
+
+    def __init__(self, group=None, cap_bytes: int = 64 << 10):
+        import ctypes
+        import torch.distributed as dist
+        from . import _lib
+        self._lib = _lib.load()
+        self._check = _lib.check
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world > 16:
+            raise ValueError('PeerCombiner supports up to 16 GPUs of one box')
+        self.cap_bytes = int(cap_bytes)
+        self.epoch = 0
+        nbytes = self._lib.dace_b200_peer_buffer_bytes(self.world, self.cap_bytes)
+        own = ctypes.c_void_p()
+        self._check(self._lib.dace_b200_peer_alloc(nbytes, ctypes.byref(own)), 'dace_b200_peer_alloc')
+        self._own = own.value
+        handle = ctypes.create_string_buffer(64)
+        self._check(self._lib.dace_b200_peer_export(self._own, handle), 'dace_b200_peer_export')
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle.raw, group=group)
+        self._opened = []
+        bases = (ctypes.c_void_p * self.world)()
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                bases[r] = self._own
+                continue
+            ptr = ctypes.c_void_p()
+            self._check(self._lib.dace_b200_peer_open(ctypes.create_string_buffer(h, 64), ctypes.byref(ptr)),
+                        'dace_b200_peer_open')
+            bases[r] = ptr.value
+            self._opened.append(ptr.value)
+        self._bases = bases
+        dist.barrier(group=group)   # everybody has mapped everybody before the first push
+
+    def supports(self, partial: torch.Tensor, rt: ReductionType) -> bool:
+        return (partial.is_cuda and partial.is_contiguous() and partial.dtype in self._DT and rt in self._OPS
+                and 0 < partial.numel() * partial.element_size() <= self.cap_bytes)
+
+    def allreduce(self, partial: torch.Tensor, rt: ReductionType, stream=None) -> torch.Tensor:
+        self.epoch += 1
+        s = stream if stream is not None else torch.cuda.current_stream(partial.device)
+        self._check(self._lib.dace_b200_peer_allreduce(int(rt), self._DT[partial.dtype], partial.data_ptr(),
+                                                       partial.numel(), self._bases, self.rank, self.world, self.epoch,
+                                                       self.cap_bytes, s.cuda_stream), 'dace_b200_peer_allreduce')
+        return partial
+
+    def close(self):
+        """Unmap the peers and free the own buffer (all ranks' streams must be idle)."""
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+        for p in self._opened:
+            self._lib.dace_b200_peer_close(p)
+        self._opened = []
+        dist.barrier(group=self.group)
+        if self._own:
+            self._lib.dace_b200_peer_free(self._own)
+            self._own = None
+
+
+_PEER = {}
+
+
+def enable_peer_combine(group=None, cap_bytes: int = 64 << 10) -> PeerCombiner:
+    """Route small all-reduces of :func:`combine` through NVLink peer memory for ``group``
+    (collective call: every rank of the group must make it)."""
+    pc = PeerCombiner(group, cap_bytes)
+    _PEER[group] = pc
+    return pc
+
+
+def disable_peer_combine(group=None):
+    pc = _PEER.pop(group, None)
+    if pc is not None:
+        pc.close()
+
+
 def combine(partial: torch.Tensor, op, group=None) -> torch.Tensor:
-    """All-reduce ``partial`` in place across the ranks (enqueued on the current stream)."""
+    """All-reduce ``partial`` in place across the ranks (enqueued on the current stream): the
+    one-shot peer-memory kernel when enabled and applicable, else one NCCL / gloo all-reduce."""
     import torch.distributed as dist
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return partial
-    dist.all_reduce(partial, op=collective_op(resolve(op)), group=group)
+    rt = resolve(op)
+    pc = _PEER.get(group)
+    if pc is not None and pc.supports(partial, rt):
+        return pc.allreduce(partial, rt)
+    dist.all_reduce(partial, op=collective_op(rt), group=group)
     return partial
 
 

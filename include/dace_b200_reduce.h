@@ -163,6 +163,29 @@ DACE_B200_API int dace_b200_wcr_scatter(int redtype, int dtype_idx, int dtype_va
                                         const void* values, const void* const_value, size_t n, void* bins,
                                         size_t nbins, dace_b200_stream_t stream);
 
+/* ---- Multi-GPU combine of small partials over NVLink peer memory --------------
+ * When the sharded axis is the reduced one, every GPU's local call above leaves a partial that
+ * must be all-reduced across the GPUs of the box.  The reference's analogue is the MPI Allreduce
+ * library node issued after the local computation (reference
+ * dace/libraries/mpi/nodes/allreduce.py:9-60, dace/libraries/mpi/environments/mpi.py:6-22).
+ * Each rank allocates ONE exchange buffer (`_peer_alloc`, size `_peer_buffer_bytes(world, cap)`),
+ * exports a 64-byte CUDA IPC handle (`_peer_export`) that the host side ships to the other ranks
+ * (any transport; dace_b200/sharding.py uses torch.distributed), and maps the peers' buffers
+ * (`_peer_open`).  `_peer_allreduce` then combines `data[0:nelem]` (f32/f64/i32/u32/i64/u64;
+ * nelem * sizeof <= cap_bytes) in place on every rank: push to all peers, release/acquire flags,
+ * fold in rank order (bit-identical on all ranks).  `epoch` is a host counter starting at 1 and
+ * incremented per call, identical on all ranks.  `peer_bases[r]` is THIS process' mapping of rank
+ * r's buffer (its own allocation for r == rank).  Enqueued on `stream`; never synchronises. */
+DACE_B200_API size_t dace_b200_peer_buffer_bytes(int world, size_t cap_bytes);
+DACE_B200_API int dace_b200_peer_alloc(size_t bytes, void** ptr);
+DACE_B200_API int dace_b200_peer_free(void* ptr);
+DACE_B200_API int dace_b200_peer_export(void* ptr, unsigned char* handle64);
+DACE_B200_API int dace_b200_peer_open(const unsigned char* handle64, void** ptr);
+DACE_B200_API int dace_b200_peer_close(void* ptr);
+DACE_B200_API int dace_b200_peer_allreduce(int redtype, int dtype, void* data, size_t nelem, void* const* peer_bases,
+                                           int rank, int world, unsigned long long epoch, size_t cap_bytes,
+                                           dace_b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -42,6 +42,34 @@ sharding.sharded_reduce("lambda a, b: a + b", x, s, axis=None, identity=0)
 ref = torch.tensor([x.double().sum().item()], dtype=torch.float64, device=dev)
 dist.all_reduce(ref)
 assert abs(s.item() - ref.item()) <= 1e-5 * ref.item()
+# ---- the same partials through the one-shot NVLink peer-memory kernel instead of NCCL ----
+pc = sharding.enable_peer_combine()
+for it in range(40):                      # many epochs: both slots, flags only ever grow
+    part = torch.full((520,), rank + it, dtype=torch.int32, device=dev)
+    assert pc.supports(part, sharding.resolve("lambda a, b: a + b"))
+    sharding.combine(part, "lambda a, b: a + b")
+    assert bool((part == sum(r + it for r in range(world))).all()), "peer all-reduce, epoch %d" % it
+assert pc.epoch == 40
+out2 = torch.zeros(520, dtype=torch.int32, device=dev)
+sharding.sharded_reduce("lambda a, b: a + b", shard, out2, axis=0, identity=5)
+assert torch.equal(out2, out), "peer-combined column sum == NCCL-combined column sum"
+tot2 = torch.zeros((), dtype=torch.int32, device=dev)
+sharding.sharded_reduce("lambda a, b: max(a, b)", shard, tot2, axis=None, identity=-2**31)
+assert tot2.item() == full.max()
+s2 = torch.zeros((), device=dev)
+sharding.sharded_reduce("lambda a, b: a + b", x, s2, axis=None, identity=0)
+assert abs(s2.item() - ref.item()) <= 1e-5 * ref.item()
+gathered = [torch.zeros((), device=dev) for _ in range(world)]
+dist.all_gather(gathered, s2)
+assert all(g.item() == s2.item() for g in gathered), "rank-ordered fold: bit-identical on every rank"
+d64 = torch.full((8192,), 0.5 + rank, dtype=torch.float64, device=dev)   # 64 KiB: the largest peer payload
+sharding.combine(d64, "lambda a, b: min(a, b)")
+assert bool((d64 == 0.5).all())
+big = torch.ones(1 << 20, dtype=torch.int32, device=dev)                 # 4 MiB: stays with NCCL
+assert not pc.supports(big, sharding.resolve("lambda a, b: a + b"))
+sharding.combine(big, "lambda a, b: a + b")
+assert bool((big == world).all())
+sharding.disable_peer_combine()
 dist.barrier(); dist.destroy_process_group()
 print("rank", rank, "ok")
 '''
