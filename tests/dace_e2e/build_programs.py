@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 3
+VERSION = 4
 
 
 def up_to_date() -> bool:
@@ -147,6 +147,21 @@ def _programs(dace):
         if applied != 1:
             raise RuntimeError('%s: WCRMapToScatterReduce applied %d times' % (sdfg.name, applied))
         progs.append(sdfg)
+
+    # (6) Whole-program route: the reference's auto_optimize(device=GPU) with the backend selected
+    #     automatically (dace_b200/auto.py): two Reduce nodes and one WCR map in one program.
+    from dace_b200 import auto as AUTO
+
+    @dace.program
+    def b200_auto_optimized(A: dace.float32[N, M], keys: dace.int32[N], bins: dace.int32[M], rs: dace.float32[N],
+                            mx: dace.float32[1]):
+        rs[:] = np.sum(A, axis=1)
+        mx[0] = np.max(A)
+        for i in dace.map[0:N]:
+            bins[keys[i]] += 1
+
+    sdfg = AUTO.auto_optimize(b200_auto_optimized.to_sdfg(simplify=True), dace.DeviceType.GPU)
+    progs.append(sdfg)
     return progs
 
 

@@ -159,3 +159,27 @@ def test_b200_expansion_refuses_host_storage(env):
     assert applied == 1
     with pytest.raises(ValueError, match='GPU_Global or CPU_Pinned'):
         sdfg.expand_library_nodes()
+
+
+def test_auto_optimize_selects_the_backend(env):
+    """the reference's auto_optimize(device=GPU) would pick GPUAuto for the
+    Reduce nodes (auto_optimize.py:439-458) and leave the WCR map as an atomic kernel."""
+    dace, SN, _ = env
+    from dace_b200 import auto as AUTO
+    N, M = dace.symbol('N'), dace.symbol('M')
+
+    @dace.program
+    def mixed(A: dace.float32[N, M], keys: dace.int32[N], bins: dace.int32[M], rs: dace.float32[N], mx: dace.float32[1]):
+        rs[:] = np.sum(A, axis=1)
+        mx[0] = np.max(A)
+        for i in dace.map[0:N]:
+            bins[keys[i]] += 1
+
+    import dace.transformation.auto.auto_optimize as ao
+    before = ao.set_fast_implementations
+    sdfg = AUTO.auto_optimize(mixed.to_sdfg(simplify=True), dace.DeviceType.GPU)
+    assert ao.set_fast_implementations is before          # the hook is removed again
+    code = ''.join(c.clean_code for c in sdfg.generate_code())
+    assert code.count('dace_b200_reduce_nd(') == 2 and code.count('dace_b200_wcr_scatter(') == 1
+    assert 'reduce_atomic' not in code
+    assert AUTO.find_fast_library(dace.DeviceType.GPU) == ['B200'] and AUTO.find_fast_library(dace.DeviceType.CPU) == []

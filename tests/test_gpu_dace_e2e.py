@@ -170,3 +170,19 @@ def test_scatter_max_f64(cuda):
     exp = O.wcr_scatter(O.MAX, bins.copy(), keys, w)
     prog('b200_scatter_max_f64')(keys=keys, w=w, bins=bins, N=keys.size, M=bins.size)
     np.testing.assert_array_equal(bins, exp)
+
+
+def test_auto_optimized_program_uses_the_backend_everywhere(cuda):
+    """dace_b200.auto.auto_optimize: reference auto_optimize(device=GPU) + automatic selection; the
+    program has two Reduce nodes and one WCR map, all three served by the library."""
+    assert ref_loader.manifest(BUILT)['programs']['b200_auto_optimized']['b200_calls'] == 3
+    rng = np.random.default_rng(11)
+    n, m = 3000, 700
+    a = rng.standard_normal((n, m)).astype(np.float32)
+    keys = rng.integers(0, m, n).astype(np.int32)
+    bins = np.zeros(m, np.int32)
+    rs, mx = np.zeros(n, np.float32), np.zeros(1, np.float32)
+    prog('b200_auto_optimized')(A=a, keys=keys, bins=bins, rs=rs, mx=mx, N=n, M=m)
+    assert close_f32(rs, a.astype(np.float64).sum(1), a, (1, ))
+    assert mx[0] == a.max()
+    np.testing.assert_array_equal(bins, np.bincount(keys, minlength=m).astype(np.int32))
