@@ -14,6 +14,7 @@
 // Rows are split over gridDim.x; the CTAs of a cluster (<= 8 along x) combine in
 // DSMEM, clusters combine through workspace partials + a ticket, folded in a
 // fixed order (deterministic, no float atomics, no second kernel).
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -153,6 +154,152 @@ cols_kernel(const L* __restrict__ in, S* __restrict__ out, size_t outer, size_t 
     if (lane == 0) counters[yz] = 0;
 }
 
+// ---------------------------------------------------------------------------
+// Wide rows (>= 4 KiB of contiguous columns, many rows; BASELINE C5): one 1024-thread CTA per SM.
+// WC warps lie side by side along the columns (a warp covers 32 vectors = 1 KiB), the other
+// WR = 32 / WC warps take consecutive rows, and every thread keeps U rows in flight - for a
+// [R, 4096] f32 matrix each CTA step reads 16 consecutive full rows = 256 KiB of contiguous
+// memory, the access pattern of the split kernel (DRAM pages stay open, 256 KiB per SM in
+// flight).  Row splits go over gridDim.x; their partials meet in the workspace and the last CTA
+// of a column group (ticket) folds them in split order - deterministic, one launch.
+// ---------------------------------------------------------------------------
+constexpr int kWideThreads = 1024;
+constexpr int kWideMaxGroups = 16;
+
+// op-fold of `count` values `stride` apart, in index order, eight L2 loads in flight.
+template <class A, class Op>
+__device__ __forceinline__ A fold_in_order(const A* p, size_t stride, unsigned count) {
+    A v = __ldcg(p);
+    unsigned k = 1;
+    for (; k + 8 <= count; k += 8) {
+        A t[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) t[q] = __ldcg(p + size_t(k + q) * stride);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v = Op::apply(v, t[q]);
+    }
+    for (; k < count; ++k) v = Op::apply(v, __ldcg(p + size_t(k) * stride));
+    return v;
+}
+
+constexpr int kWideWarps = kWideThreads / 32;
+
+template <class L, class A, class S, class Op, int N, int U>
+__global__ void __launch_bounds__(kWideThreads, 1)
+cols_wide_kernel(const L* __restrict__ in, S* __restrict__ out, size_t outer, size_t reduced, size_t inner,
+                 size_t so, size_t sr, ptrdiff_t oo, ptrdiff_t oi, Finish<A> fin,
+                 unsigned* __restrict__ counters, A* __restrict__ partials,
+                 int WC, size_t colgroups, size_t rows_per_split, unsigned gsize) {
+    extern __shared__ __align__(16) unsigned char wide_smem[];
+    A* sm = reinterpret_cast<A*>(wide_smem);   // [kWideWarps][32 * N] when WR > 1
+    __shared__ unsigned s_ticket;
+
+    const unsigned tid = threadIdx.x;
+    const unsigned lane = tid & 31, warp = tid >> 5;
+    const unsigned WR = kWideWarps / unsigned(WC);
+    const unsigned wc = warp % unsigned(WC), wr = warp / unsigned(WC);
+    const size_t yz = size_t(blockIdx.z) * gridDim.y + blockIdx.y;
+    if (yz >= colgroups * outer) return;
+    const size_t o = yz / colgroups, cgi = yz % colgroups;
+    const size_t c0 = ((cgi * WC + wc) * 32 + lane) * N;
+    const bool col_ok = c0 < inner;
+
+    const size_t r_begin = size_t(blockIdx.x) * rows_per_split;
+    size_t r_end = r_begin + rows_per_split;
+    if (r_end > reduced) r_end = reduced;
+
+    A acc[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) acc[j] = Op::neutral();
+    if (col_ok) {
+        const L* base = in + o * so + c0;
+        size_t r = r_begin + wr;
+        for (; r + size_t(U - 1) * WR < r_end; r += size_t(U) * WR) {
+            A x[U][N];
+#pragma unroll
+            for (int u = 0; u < U; ++u) load_cols<L, A, N>(base + (r + size_t(u) * WR) * sr, x[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int j = 0; j < N; ++j) acc[j] = Op::apply(acc[j], x[u][j]);
+        }
+        for (; r < r_end; r += WR) {
+            A x[N];
+            load_cols<L, A, N>(base + r * sr, x);
+#pragma unroll
+            for (int j = 0; j < N; ++j) acc[j] = Op::apply(acc[j], x[j]);
+        }
+    }
+    // warps that share a column chunk (different row slots) meet in shared memory
+    if (WR > 1) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) sm[(warp * 32 + lane) * N + j] = acc[j];
+        __syncthreads();
+        if (wr == 0) {
+            for (unsigned k = 1; k < WR; ++k)
+#pragma unroll
+                for (int j = 0; j < N; ++j) acc[j] = Op::apply(acc[j], sm[((k * WC + wc) * 32 + lane) * N + j]);
+        }
+    }
+    const bool owner = wr == 0;
+    const unsigned nsplits = gridDim.x;
+    S* obase = out + ptrdiff_t(o) * oo;
+    if (nsplits == 1) {
+        if (owner && col_ok) {
+#pragma unroll
+            for (int j = 0; j < N; ++j) write_result<Op, A, S>(obase + ptrdiff_t(c0 + j) * oi, acc[j], fin);
+        }
+        return;
+    }
+    // Two-level, fixed-order combine through the workspace: splits form groups of `gsize`; the last
+    // CTA of a group (ticket) folds the group's partials in split order into a group partial, the
+    // last group folds the group partials in group order.  One CTA folding all ~148 partials would
+    // be bound by a single SM's L2 bandwidth and latency (~45 us measured on C5); two levels of ~12
+    // cost a few microseconds.
+    const size_t slot = size_t(WC) * 32 * N;
+    const unsigned ngroups = (nsplits + gsize - 1) / gsize;
+    const unsigned grp = blockIdx.x / gsize;
+    const unsigned in_grp = min(gsize, nsplits - grp * gsize);
+    A* level1 = partials + yz * (size_t(nsplits) + ngroups) * slot;   // [nsplits][slot]
+    A* level2 = level1 + size_t(nsplits) * slot;                        // [ngroups][slot]
+    unsigned* ctr = counters + yz * (1 + kWideMaxGroups);               // [0] top, [1 + g] group g
+    if (owner) {
+        A* my = level1 + size_t(blockIdx.x) * slot + (size_t(wc) * 32 + lane) * N;
+#pragma unroll
+        for (int j = 0; j < N; ++j) my[j] = acc[j];
+        __threadfence();
+    }
+    __syncthreads();
+    if (tid == 0) s_ticket = atomicAdd(&ctr[1 + grp], 1u);
+    __syncthreads();
+    if (s_ticket != in_grp - 1) return;
+    __threadfence();
+    const bool single_group = ngroups == 1;
+    const size_t cbase = cgi * WC * 32 * N;
+    for (size_t idx = tid; idx < slot; idx += kWideThreads) {
+        const A v = fold_in_order<A, Op>(level1 + size_t(grp) * gsize * slot + idx, slot, in_grp);
+        if (single_group) {
+            if (cbase + idx < inner) write_result<Op, A, S>(obase + ptrdiff_t(cbase + idx) * oi, v, fin);
+        } else {
+            level2[size_t(grp) * slot + idx] = v;
+        }
+    }
+    if (tid == 0) ctr[1 + grp] = 0;
+    if (single_group) return;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_ticket = atomicAdd(&ctr[0], 1u);
+    __syncthreads();
+    if (s_ticket != ngroups - 1) return;
+    __threadfence();
+    for (size_t idx = tid; idx < slot; idx += kWideThreads) {
+        if (cbase + idx >= inner) continue;
+        const A v = fold_in_order<A, Op>(level2 + idx, slot, ngroups);
+        write_result<Op, A, S>(obase + ptrdiff_t(cbase + idx) * oi, v, fin);
+    }
+    if (tid == 0) ctr[0] = 0;
+}
+
 static inline size_t ceil_div(size_t a, size_t b) { return (a + b - 1) / b; }
 
 template <class T, class Op, int N>
@@ -216,6 +363,58 @@ static cudaError_t launch_cols_n(const ColsArgs& a, const Launch& l) {
                               l.ws.counters, (A*)l.ws.partials, P, colgroups, rows_per_split);
 }
 
+// Returns cudaErrorNotSupported when the shape is not a wide-row one (caller uses cols_kernel).
+template <class T, class Op, int N>
+static cudaError_t launch_cols_wide(const ColsArgs& a, const Launch& l) {
+    using L = typename T::L; using A = typename T::A; using S = typename T::S;
+    constexpr int U = 8;
+    if (getenv("DACE_B200_NO_WIDE_COLS")) return cudaErrorNotSupported;
+    const size_t colvecs = ceil_div(a.inner, N);
+    if (colvecs < 128) return cudaErrorNotSupported;                 // rows narrower than 4 KiB
+    int WC = 4;
+    while (WC < kWideWarps && size_t(WC) * 32 < colvecs) WC <<= 1;
+    const unsigned WR = kWideWarps / WC;
+    const size_t colgroups = ceil_div(colvecs, size_t(WC) * 32);
+    const size_t total = colgroups * a.outer;
+    if (a.reduced < size_t(WR) * U * 4) return cudaErrorNotSupported;  // too few rows to stream
+    size_t splits = ceil_div(size_t(sm_count()), total);
+    const size_t max_by_rows = a.reduced / (size_t(WR) * U * 2);
+    if (splits > max_by_rows) splits = max_by_rows;
+    if (splits < 1) splits = 1;
+    const size_t slot_bytes = size_t(WC) * 32 * N * sizeof(A);
+    if (splits > 256) splits = 256;
+    if (splits > 1) {
+        if (total * (1 + kWideMaxGroups) > kCounters) splits = 1;
+        else {
+            // level-1 partials (splits) + level-2 partials (<= 16 groups) per column group
+            const size_t fit = kPartialBytes / (slot_bytes * total);
+            if (fit < 2 + kWideMaxGroups) return cudaErrorNotSupported;
+            if (splits > fit - kWideMaxGroups) splits = fit - kWideMaxGroups;
+        }
+    }
+    const size_t rows_per_split = ceil_div(a.reduced, splits);
+    splits = ceil_div(a.reduced, rows_per_split);
+    unsigned gsize = 1;
+    while (size_t(gsize) * gsize < splits) ++gsize;          // ceil(sqrt(splits)): two balanced levels
+    size_t gy = total, gz = 1;
+    if (gy > 65535) { gz = ceil_div(total, 65535); gy = 65535; }
+    if (gz > 65535) return cudaErrorNotSupported;
+    auto kern = cols_wide_kernel<L, A, S, Op, N, U>;
+    const size_t smem = WR > 1 ? size_t(kWideThreads) * N * sizeof(A) : 0;
+    static bool attr_set = false;   // per instantiation
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             int(size_t(kWideThreads) * N * sizeof(A)));
+        if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }
+        attr_set = true;
+    }
+    Finish<A> fin = make_finish<A, S>(a.identity);
+    kern<<<dim3((unsigned)splits, (unsigned)gy, (unsigned)gz), kWideThreads, smem, l.stream>>>(
+        (const L*)a.in, (S*)a.out, a.outer, a.reduced, a.inner, a.in_stride_o, a.in_stride_r, a.out_stride_o,
+        a.out_stride_i, fin, l.ws.counters, (A*)l.ws.partials, WC, colgroups, rows_per_split, gsize);
+    return cudaGetLastError();
+}
+
 template <class T, class Op>
 static cudaError_t launch_cols_t(const ColsArgs& a, const Launch& l) {
     using L = typename T::L;
@@ -223,7 +422,11 @@ static cudaError_t launch_cols_t(const ColsArgs& a, const Launch& l) {
     const size_t vb = 32;
     const bool vec_ok = (reinterpret_cast<size_t>(a.in) % vb == 0) && (a.inner % NV == 0) &&
                         ((a.in_stride_o * sizeof(L)) % vb == 0) && ((a.in_stride_r * sizeof(L)) % vb == 0);
-    if (vec_ok) return launch_cols_n<T, Op, NV>(a, l);
+    if (vec_ok) {
+        cudaError_t e = launch_cols_wide<T, Op, NV>(a, l);
+        if (e != cudaErrorNotSupported) return e;
+        return launch_cols_n<T, Op, NV>(a, l);
+    }
     return launch_cols_n<T, Op, 1>(a, l);
 }
 

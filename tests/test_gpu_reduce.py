@@ -338,3 +338,40 @@ def test_deterministic_and_workspace(cuda):
     m = x.view(4096, 4096)
     c = [db.reduce('lambda a, b: a + b', m, axis=0, identity=0, workspace=ws) for _ in range(3)]
     assert torch.equal(c[0], c[1]) and torch.equal(c[1], c[2])
+
+
+@pytest.mark.parametrize('outer,red,inner,dtype', [
+    (1, 5000, 1024, np.float32), (1, 3001, 4096, np.float32), (1, 20000, 2048 + 8, np.float32),
+    (1, 4000, 512, np.float64), (3, 2000, 1024, np.int32), (1, 70000, 1024, np.int64), (2, 999, 8192, np.float32),
+    (1, 1 << 15, 1024, np.uint32), (300, 400, 2048, np.float32),
+])
+def test_cols_wide_rows_kernel(outer, red, inner, dtype, cuda):
+    """Rows of >= 4 KiB take cols_wide_kernel (1024-thread CTAs, warps side by side along the
+    columns, two-level fixed-order combine through the workspace): all ops, partial column chunks,
+    outer > 1, split counts from 1 to the SM count, identity None, repeatability."""
+    rng = np.random.default_rng(red)
+    a = _data(rng, (outer, red, inner), dtype)
+    for op in ('sum', 'max'):
+        got, ref = _run(a, (1, ), op, cuda)
+        _check(got, ref, dtype, a, (1, ), op)
+    init = _data(rng, (outer, inner), dtype)
+    got, ref = _run(a, (1, ), 'sum', cuda, identity=None, out_init=init)
+    if np.issubdtype(dtype, np.floating):
+        scale = np.abs(a.astype(np.float64)).sum(axis=1) + np.abs(init)
+        assert np.all(np.abs(got.astype(np.float64) - ref.astype(np.float64)) <= 1e-5 * np.maximum(scale, 1e-30))
+    else:
+        np.testing.assert_array_equal(got, ref)
+    ta = torch.from_numpy(a).to(cuda)
+    r1 = db.reduce('lambda a, b: a + b', ta, axis=(1, ), identity=0)
+    r2 = db.reduce('lambda a, b: a + b', ta, axis=(1, ), identity=0)
+    assert torch.equal(r1, r2)                       # fixed fold order: bit-identical from run to run
+
+
+def test_cols_wide_rows_bf16_and_2d(cuda):
+    x = torch.randn(6000, 4096, device=cuda).to(torch.bfloat16)
+    got = torch.zeros(4096, device=cuda)
+    db.reduce('lambda a, b: a + b', x, got, axis=(0, ), identity=0)   # bf16 in, fp32 out, fp32 accumulate
+    ref = x.double().sum(0)
+    assert bool(((got.double() - ref).abs() <= 1e-5 * x.double().abs().sum(0)).all())
+    gmax = db.reduce('lambda a, b: max(a, b)', x, axis=(0, ), identity=-3e38)
+    assert torch.equal(gmax.float(), x.float().max(0).values)
