@@ -155,12 +155,11 @@ cols_kernel(const L* __restrict__ in, S* __restrict__ out, size_t outer, size_t 
 }
 
 // ---------------------------------------------------------------------------
-// Wide rows (>= 4 KiB of contiguous columns, many rows; BASELINE C5): one 1024-thread CTA per SM.
-// WC warps lie side by side along the columns (a warp covers 32 vectors = 1 KiB), the other
-// WR = 32 / WC warps take consecutive rows, and every thread keeps U rows in flight - for a
-// [R, 4096] f32 matrix each CTA step reads 16 consecutive full rows = 256 KiB of contiguous
-// memory, the access pattern of the split kernel (DRAM pages stay open, 256 KiB per SM in
-// flight).  Row splits go over gridDim.x; their partials meet in the workspace and the last CTA
+// Wide rows (>= 4 KiB of contiguous columns, >= 1024 rows; BASELINE C5): one 1024-thread CTA per SM.
+// WC = 4 warps lie side by side along the columns (a warp covers 32 vectors = 1 KiB, a CTA 4 KiB
+// of each row), the other WR = 8 warps take consecutive rows, and every thread keeps U = 8 rows
+// in flight: 64 rows x 4 KiB = 256 KiB per SM outstanding in 4 KiB contiguous pieces (the split
+// kernel's recipe; 1 KiB pieces in cols_kernel reach 6.7 TB/s, these 7.15).  Row splits go over gridDim.x; their partials meet in the workspace and the last CTA
 // of a column group (ticket) folds them in split order - deterministic, one launch.
 // ---------------------------------------------------------------------------
 constexpr int kWideThreads = 1024;
@@ -371,13 +370,17 @@ static cudaError_t launch_cols_wide(const ColsArgs& a, const Launch& l) {
     if (getenv("DACE_B200_NO_WIDE_COLS")) return cudaErrorNotSupported;
     const size_t colvecs = ceil_div(a.inner, N);
     if (colvecs < 128) return cudaErrorNotSupported;                 // rows narrower than 4 KiB
+    // 4 warps (4 KiB) side by side measured best or within 1 % of best from 16 MiB to 8 GiB (tools/cols_sweep.py):
+    // wider CTAs only make the partials bigger.
+    int wc_max = 4;
+    if (const char* ev = getenv("DACE_B200_WIDE_WC")) wc_max = atoi(ev);   // tuning knob for experiments
     int WC = 4;
-    while (WC < kWideWarps && size_t(WC) * 32 < colvecs) WC <<= 1;
+    while (WC < wc_max && size_t(WC) * 32 < colvecs) WC <<= 1;
     const unsigned WR = kWideWarps / WC;
     const size_t colgroups = ceil_div(colvecs, size_t(WC) * 32);
     const size_t total = colgroups * a.outer;
-    if (a.reduced < size_t(WR) * U * 4) return cudaErrorNotSupported;  // too few rows to stream
-    size_t splits = ceil_div(size_t(sm_count()), total);
+    if (a.reduced < 1024 || a.reduced < size_t(WR) * U * 4) return cudaErrorNotSupported;  // too few rows to stream
+    size_t splits = size_t(sm_count()) / total;   // one wave: never more CTAs than SMs
     const size_t max_by_rows = a.reduced / (size_t(WR) * U * 2);
     if (splits > max_by_rows) splits = max_by_rows;
     if (splits < 1) splits = 1;
