@@ -41,6 +41,10 @@ _PROTOTYPES = {
     'dace_b200_reduce_rows_max_sum': (_c.c_int, [
         _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_size_t, _c.c_size_t, _c.c_void_p
     ]),
+    'dace_b200_reduce_arg': (_c.c_int, [
+        _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_size_t, _c.c_size_t,
+        _c.c_int64, _c.c_int64, _c.c_int64, _c.c_size_t, _c.c_size_t, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p
+    ]),
     'dace_b200_wcr_scatter': (_c.c_int, [
         _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p,
         _c.c_size_t, _c.c_void_p

@@ -185,6 +185,82 @@ def rows_max_sum(in_array: torch.Tensor, out_max: Optional[torch.Tensor] = None,
     return out_max, out_sum
 
 
+def _arg_reduce(red: int, in_array: torch.Tensor, axis, out_idx, out_val, init, idx_dtype, stream, workspace):
+    lib = _lib.load()
+    _require_cuda(in_array, 'in_array')
+    a = in_array
+    if axis is None:
+        a = a.reshape(-1)      # a view when possible, like the frontend's flat() (reduction.py:281-283)
+        axis = 0
+    axis = _normalize_axes(axis, a.dim())[0]
+    if not a.is_contiguous():
+        # any [outer, reduced, inner] factorisation needs mergeable leading / trailing dims
+        lead, trail = a.shape[:axis], a.shape[axis + 1:]
+        ok = all(a.stride(i) == a.stride(i + 1) * a.shape[i + 1] for i in range(axis - 1)) and \
+            all(a.stride(i) == a.stride(i + 1) * a.shape[i + 1] for i in range(axis + 1, a.dim() - 1))
+        if not ok:
+            raise NotImplementedError('argmin/argmax: leading and trailing dimensions must each be mergeable')
+    outer = int(np.prod(a.shape[:axis], dtype=np.int64))
+    inner = int(np.prod(a.shape[axis + 1:], dtype=np.int64))
+    reduced = a.shape[axis]
+    so = a.stride(axis - 1) if axis > 0 else 0
+    si = a.stride(a.dim() - 1) if axis < a.dim() - 1 else 1
+    sr = a.stride(axis)
+    kept = tuple(a.shape[:axis]) + tuple(a.shape[axis + 1:])
+    created = out_idx is None
+    if created:
+        if init is None:
+            raise ValueError('init=None folds into existing outputs: out_idx and out_val are required')
+        out_idx = torch.empty(kept, dtype=idx_dtype, device=a.device)
+    if out_val is None and init is None:
+        raise ValueError('init=None folds into existing outputs: out_val is required')
+    for o, what in ((out_idx, 'out_idx'), (out_val, 'out_val')):
+        if o is None:
+            continue
+        _require_cuda(o, what)
+        if not o.is_contiguous() or o.numel() != outer * inner:
+            raise ValueError('%s must be contiguous with one element per kept position' % what)
+    if out_idx.dtype not in (torch.int32, torch.int64):
+        raise NotImplementedError('index dtype %s' % out_idx.dtype)
+    if out_val is not None and out_val.dtype != a.dtype:
+        raise ValueError('out_val must have the input dtype')
+    dt_in = dtype_code(a.dtype)
+    if isinstance(init, str):
+        if a.dtype.is_floating_point:
+            init = torch.finfo(a.dtype).min if red == int(ReductionType.Max_Location) else torch.finfo(a.dtype).max
+        else:
+            info = torch.iinfo(a.dtype) if a.dtype != torch.bool else None
+            init = (info.min if red == int(ReductionType.Max_Location) else info.max) if info else \
+                (0 if red == int(ReductionType.Max_Location) else 1)
+    ibuf = ctypes.create_string_buffer(scalar_bytes(init, dt_in), 8) if init is not None else None
+    ws_ptr, ws_bytes = (workspace.ptr, workspace.nbytes) if workspace is not None else (None, 0)
+    with torch.cuda.device(a.device):
+        status = lib.dace_b200_reduce_arg(red, dt_in, dtype_code(out_idx.dtype), a.data_ptr(), out_idx.data_ptr(),
+                                          out_val.data_ptr() if out_val is not None else None, outer, reduced, inner,
+                                          so, sr, si, 0, 0, ibuf, ws_ptr, ws_bytes, _stream_ptr(stream))
+    _lib.check(status, 'dace_b200_reduce_arg')
+    return out_idx if created else None
+
+
+def argmax(in_array: torch.Tensor, axis: Optional[int] = None, out_idx: Optional[torch.Tensor] = None,
+           out_val: Optional[torch.Tensor] = None, init='default', idx_dtype=torch.int32, stream=None,
+           workspace: Optional[Workspace] = None):
+    """``np.argmax(in_array, axis)`` with the fold rule of the reference frontend's lowering
+    (reference dace/frontend/python/replacements/reduction.py:245-348): first maximum wins; the
+    pair starts as ``(init, -1)`` with ``init = min_value(dtype)`` by default, so a slice with no
+    element above ``init`` yields -1.  ``init=None`` folds into ``out_val`` / ``out_idx``."""
+    return _arg_reduce(int(ReductionType.Max_Location), in_array, axis, out_idx, out_val, init, idx_dtype, stream,
+                       workspace)
+
+
+def argmin(in_array: torch.Tensor, axis: Optional[int] = None, out_idx: Optional[torch.Tensor] = None,
+           out_val: Optional[torch.Tensor] = None, init='default', idx_dtype=torch.int32, stream=None,
+           workspace: Optional[Workspace] = None):
+    """``np.argmin`` - see :func:`argmax`."""
+    return _arg_reduce(int(ReductionType.Min_Location), in_array, axis, out_idx, out_val, init, idx_dtype, stream,
+                       workspace)
+
+
 def wcr_scatter(op, bins: torch.Tensor, indices: torch.Tensor, values=None, stream=None) -> None:
     """``bins[indices[i]] = op(bins[indices[i]], values[i])`` - the WCR map
     ``out >> bins(1, wcr)[:]; out[idx] = v`` of reference

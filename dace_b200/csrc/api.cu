@@ -260,6 +260,24 @@ int dace_b200_reduce_rows_max_sum(int dtype_in, const void* in, float* out_max, 
     return (int)launch_rows_max_sum(dtype_in, a, l);
 }
 
+int dace_b200_reduce_arg(int redtype, int dtype_in, int dtype_idx, const void* in, void* out_idx, void* out_val,
+                         size_t outer, size_t reduced, size_t inner, int64_t in_stride_outer,
+                         int64_t in_stride_reduced, int64_t in_stride_inner, size_t out_idx_stride_bytes,
+                         size_t out_val_stride_bytes, const void* init, void* workspace, size_t workspace_bytes,
+                         dace_b200_stream_t stream) {
+    if (dtype_idx != DT_I32 && dtype_idx != DT_I64) return (int)cudaErrorNotSupported;
+    if (outer == 0 || inner == 0) return (int)cudaSuccess;
+    if (!out_idx || (reduced != 0 && !in) || (!init && !out_val)) return (int)cudaErrorInvalidValue;
+    if (in_stride_outer < 0 || in_stride_reduced < 0 || in_stride_inner < 0) return (int)cudaErrorNotSupported;
+    Launch l;
+    l.stream = (cudaStream_t)stream;
+    cudaError_t e = resolve_workspace(workspace, workspace_bytes, l);
+    if (e != cudaSuccess) return (int)e;
+    ArgArgs a{in, out_idx, out_val, outer, reduced, inner, in_stride_outer, in_stride_reduced, in_stride_inner,
+              (long long)out_idx_stride_bytes, (long long)out_val_stride_bytes, dtype_idx == DT_I64 ? 8 : 4, init};
+    return (int)launch_arg(redtype, dtype_in, a, l);
+}
+
 int dace_b200_wcr_scatter(int redtype, int dtype_idx, int dtype_val, const void* idx, const void* values,
                           const void* const_value, size_t n, void* bins, size_t nbins,
                           dace_b200_stream_t stream) {

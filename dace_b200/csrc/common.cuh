@@ -150,6 +150,11 @@ __device__ __forceinline__ Words<16> ldg_stream16(const void* p) {
                  : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]) : "l"(p));
     return r;
 }
+__device__ __forceinline__ Words<8> ldg_stream8(const void* p) {
+    Words<8> r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.w[0]), "=r"(r.w[1]) : "l"(p));
+    return r;
+}
 __device__ __forceinline__ Words<32> ldg_stream32(const void* p) {
     Words<32> r;
     asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -158,6 +163,7 @@ __device__ __forceinline__ Words<32> ldg_stream32(const void* p) {
     return r;
 }
 template <int BYTES> __device__ __forceinline__ Words<BYTES> ldg_stream(const void* p);
+template <> __device__ __forceinline__ Words<8> ldg_stream<8>(const void* p) { return ldg_stream8(p); }
 template <> __device__ __forceinline__ Words<16> ldg_stream<16>(const void* p) { return ldg_stream16(p); }
 template <> __device__ __forceinline__ Words<32> ldg_stream<32>(const void* p) { return ldg_stream32(p); }
 

@@ -56,6 +56,17 @@ cudaError_t launch_generic(int red, int dtin, int dtout, const GenericArgs& a, c
 cudaError_t launch_fill(int dtout, void* out, int nk, const long long* kshape, const long long* kout,
                         const void* identity, const Launch& l);
 
+// argmin / argmax: in[o][r][i] (element strides) -> (index along r, value) at output o * inner + i.
+struct ArgArgs {
+    const void* in; void* out_idx; void* out_val;   // out_val may be null when init is given
+    size_t outer, reduced, inner;
+    long long in_stride_o, in_stride_r, in_stride_i;              // elements
+    long long out_idx_stride_bytes, out_val_stride_bytes;         // 0 = densely packed
+    int idx_bytes;                                                // 4 (int32) or 8 (int64)
+    const void* init;   // host pointer to the initial value (input dtype) or null = fold into the outputs
+};
+cudaError_t launch_arg(int red, int dtin, const ArgArgs& a, const Launch& l);
+
 // WCR scatter: bins[idx[i]] = op(bins[idx[i]], values ? values[i] : *const_value).
 struct ScatterArgs {
     const void* idx; const void* values; const void* const_value;

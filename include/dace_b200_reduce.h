@@ -57,7 +57,9 @@ enum dace_b200_redtype {
     DACE_B200_LOGICAL_OR = 7,
     DACE_B200_BITWISE_OR = 8,
     DACE_B200_LOGICAL_XOR = 9,
-    DACE_B200_BITWISE_XOR = 10
+    DACE_B200_BITWISE_XOR = 10,
+    DACE_B200_MIN_LOCATION = 11, /* dace_b200_reduce_arg only */
+    DACE_B200_MAX_LOCATION = 12  /* dace_b200_reduce_arg only */
 };
 
 /* Element types. Supported (in -> out) pairs: T -> T for every type below, plus
@@ -148,6 +150,30 @@ DACE_B200_API int dace_b200_reduce_cols(int redtype, int dtype_in, int dtype_out
 DACE_B200_API int dace_b200_reduce_rows_max_sum(int dtype_in, const void* in, float* out_max, float* out_sum,
                                                 size_t num_segments, size_t segment_size, size_t segment_stride,
                                                 dace_b200_stream_t stream);
+
+/* ---- argmin / argmax (ReductionType Min_Location / Max_Location) --------------
+ * in[o][r][i] with ELEMENT strides (in_stride_outer, in_stride_reduced, in_stride_inner);
+ * for every (o, i) the index along r of the first minimum / maximum and, optionally, its
+ * value are written to output position o * inner + i:
+ *     *(idx_t*)((char*)out_idx + pos * out_idx_stride_bytes),  idx_t = dtype_idx (i32 or i64)
+ *     *(T*)    ((char*)out_val + pos * out_val_stride_bytes),  T = dtype_in
+ * (stride 0 = densely packed), so the two outputs may be the fields of the interleaved
+ * struct array `_val_and_idx {idx; val}` the reference frontend reduces into
+ * (reference dace/frontend/python/replacements/reduction.py:299-334).  Semantics of that
+ * map's WCR lambda `val = max(x.val, y.val), idx = y.idx if x.val < y.val else x.idx`
+ * evaluated in index order: strictly-better replaces, first occurrence wins.  `init` is a
+ * HOST pointer to the initial value (dtype_in); the running pair starts as (*init, -1), and
+ * elements equal to *init never replace it (the frontend's init state writes
+ * min_value(dtype) / max_value(dtype), reduction.py:303-304).  init == NULL folds into the
+ * (val, idx) pairs already stored in the outputs (out_val required then).
+ * Replaces: the generated WCR-map kernel with dace::wcr_custom<T>::reduce_atomic CAS loops
+ * (reference dace/runtime/include/dace/reduction.h:56-75) and cub::DeviceReduce::ArgMin/ArgMax
+ * of the CUB expansion (reference dace/libraries/standard/nodes/reduce.py:399-402). */
+DACE_B200_API int dace_b200_reduce_arg(int redtype, int dtype_in, int dtype_idx, const void* in, void* out_idx,
+                                       void* out_val, size_t outer, size_t reduced, size_t inner,
+                                       int64_t in_stride_outer, int64_t in_stride_reduced, int64_t in_stride_inner,
+                                       size_t out_idx_stride_bytes, size_t out_val_stride_bytes, const void* init,
+                                       void* workspace, size_t workspace_bytes, dace_b200_stream_t stream);
 
 /* ---- WCR map reductions (scatter-add / histogram) ---------------------------
  *     bins[idx[i]] = op(bins[idx[i]], values ? values[i] : *const_value)   i in [0, n)

@@ -13,7 +13,10 @@ answers do: small seeded inputs + the outputs the reference produced for them.
 * redtype_golden.json - dace.frontend.operations.detect_reduction_type on a
   list of lambdas (reference dace/frontend/operations.py:130-185).
 
-Usage (from a writable cwd):  PYTHONPATH=/root/repo python -m oracle.make_golden
+* arg_golden.npz - np.argmax / np.argmin through the frontend's struct-WCR lowering
+  (reference tests/numpy/reductions_test.py:58-84), generated with one OpenMP thread.
+
+Usage (from a writable cwd):  PYTHONPATH=/root/repo python -m oracle.make_golden [--arg]
 """
 import json
 import os
@@ -224,6 +227,89 @@ def _wcr_cases(dace):
     return out, meta
 
 
+def _arg_cases(dace):
+    """np.argmax / np.argmin through @dace.program (reference tests/numpy/reductions_test.py:58-84,
+    tests/numpy/ndarray_attributes_methods_test.py:95-111).  The frontend lowers them to a struct WCR map
+    (reference dace/frontend/python/replacements/reduction.py:261-348) that the CPU code generator runs as an
+    OpenMP loop with a critical section per element, so ties are resolved in whatever order the threads arrive.
+    The vectors are generated with OMP_NUM_THREADS=1: index order, which is also NumPy's first-occurrence rule."""
+    rng = np.random.default_rng(11)
+    out, meta = {}, []
+    N, M, K = dace.symbol('N'), dace.symbol('M'), dace.symbol('K')
+
+    def make(func, dt, axis, ndim):
+        shape = [N, M, K][:ndim]
+        fn = np.argmax if func == 'max' else np.argmin
+        if axis is None:
+            @dace.program
+            def prog(A: dt[tuple(shape)]):
+                return fn(A)
+        else:
+            @dace.program
+            def prog(A: dt[tuple(shape)]):
+                return fn(A, axis=axis)
+        return prog
+
+    f32, f64, i32, i64 = dace.float32, dace.float64, dace.int32, dace.int64
+    npdt = {f32: np.float32, f64: np.float64, i32: np.int32, i64: np.int64}
+    cases = [
+        ('argmax_f64_axis1', 'max', f64, 1, (10, 5, 3), 'uniform'),
+        ('argmin_f64_axis1', 'min', f64, 1, (10, 5, 3), 'uniform'),
+        ('argmin_i32_axis1', 'min', i32, 1, (10, 5, 3), 'ties'),
+        ('argmax_i32_axis1', 'max', i32, 1, (10, 5, 3), 'ties'),
+        ('argmin_i64_axis1', 'min', i64, 1, (10, 5, 3), 'ties'),
+        ('argmax_i64_axis1', 'max', i64, 1, (10, 5, 3), 'ties'),
+        ('argmax_f32_flat', 'max', f32, None, (7, 9, 11), 'uniform'),
+        ('argmin_f32_flat', 'min', f32, None, (7, 9, 11), 'uniform'),
+        ('argmax_f32_axis0', 'max', f32, 0, (300, 40), 'uniform'),
+        ('argmin_f32_last', 'min', f32, 1, (40, 300), 'uniform'),
+        ('argmax_i32_ties_rows', 'max', i32, 1, (33, 500), 'ties'),
+        ('argmax_i32_all_min', 'max', i32, 1, (4, 50), 'allmin'),      # nothing above min_value -> index -1
+        ('argmax_f32_neg_inf', 'max', f32, 0, (50, 6), 'neginf'),      # -inf never beats -finfo.max -> -1
+        ('argmin_f64_all_equal', 'min', f64, 1, (5, 64), 'equal'),
+    ]
+    for tag, func, dt, axis, shape, kind in cases:
+        nd = npdt[dt]
+        if kind == 'uniform':
+            A = rng.uniform(-10, 10, shape).astype(nd)
+        elif kind == 'ties':
+            A = rng.integers(-3, 4, shape).astype(nd)
+        elif kind == 'allmin':
+            A = np.full(shape, np.iinfo(nd).min, nd)
+            A[1, 7] = 5
+        elif kind == 'neginf':
+            A = np.full(shape, -np.inf, nd)
+            A[10:12, 2] = 1.5
+            A[3, 4] = np.finfo(nd).min
+        else:
+            A = np.full(shape, 2.5, nd)
+        prog = make(func, dt, axis, len(shape))
+        syms = dict(zip('NMK', shape))
+        res = prog(A=A, **syms)
+        out[tag + '__in'] = A
+        out[tag + '__out'] = np.asarray(res).copy()
+        meta.append({'tag': tag, 'func': func, 'axis': axis, 'dtype': np.dtype(nd).name, 'kind': kind})
+    return out, meta
+
+
+def main_arg():
+    os.environ['OMP_NUM_THREADS'] = '1'
+    tmp = tempfile.mkdtemp(prefix='dace_b200_golden_')
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    try:
+        dace = import_reference(os.path.join(tmp, '.dacecache'))
+        assert dace is not None, 'reference checkout not available'
+        o, m = _arg_cases(dace)
+        np.savez_compressed(os.path.join(GOLDEN, 'arg_golden.npz'), **o)
+        with open(os.path.join(GOLDEN, 'arg_golden_meta.json'), 'w') as f:
+            json.dump({'reference_version': dace.__version__, 'omp_num_threads': 1, 'arg': m}, f, indent=1)
+        print('wrote arg golden vectors to', GOLDEN)
+    finally:
+        os.chdir(cwd)
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
 def main():
     tmp = tempfile.mkdtemp(prefix='dace_b200_golden_')
     cwd = os.getcwd()
@@ -254,4 +340,9 @@ def main():
 
 
 if __name__ == '__main__':
-    main()
+    import sys
+    if '--arg' in sys.argv:      # only the argmin/argmax vectors (the other files stay byte-identical)
+        main_arg()
+    else:
+        main()
+        main_arg()

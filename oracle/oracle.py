@@ -15,6 +15,7 @@ LIB = os.path.join(_HERE, 'build', 'libreduce_oracle.so')
 
 F32, F64, I32, I64, U32, U64, BF16, F16, I8, U8, I16, U16 = range(12)
 MIN, MAX, SUM, PRODUCT, LAND, BAND, LOR, BOR, LXOR, BXOR = range(1, 11)
+MIN_LOCATION, MAX_LOCATION = 11, 12
 
 _NP2DT = {np.dtype(np.float32): F32, np.dtype(np.float64): F64, np.dtype(np.int32): I32, np.dtype(np.int64): I64,
           np.dtype(np.uint32): U32, np.dtype(np.uint64): U64, np.dtype(np.float16): F16, np.dtype(np.int8): I8,
@@ -43,6 +44,9 @@ def load():
         _lib.oracle_wcr_scatter.restype = ctypes.c_int
         _lib.oracle_wcr_scatter.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                             ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t]
+        _lib.oracle_reduce_arg.restype = ctypes.c_int
+        _lib.oracle_reduce_arg.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                           ctypes.c_void_p] + [ctypes.c_int64] * 8 + [ctypes.c_void_p]
     return _lib
 
 
@@ -125,3 +129,42 @@ def wcr_scatter(red: int, bins: np.ndarray, idx: np.ndarray, values=None) -> np.
     if rc != 0:
         raise RuntimeError('oracle_wcr_scatter failed with %d' % rc)
     return bins
+
+
+def default_arg_init(red: int, a: np.ndarray, in_bf16: bool = False):
+    """What the frontend's init state writes: dtypes.min_value / max_value of the input type
+    (reference dace/frontend/python/replacements/reduction.py:303-304, dace/dtypes.py:426-449)."""
+    if in_bf16:
+        return -3.3895313892515355e38 if red == MAX_LOCATION else 3.3895313892515355e38
+    info = np.finfo(a.dtype) if np.issubdtype(a.dtype, np.floating) else np.iinfo(a.dtype)
+    return info.min if red == MAX_LOCATION else info.max
+
+
+def reduce_arg(red: int, a: np.ndarray, axis: int = None, init='default', out_idx: np.ndarray = None,
+               out_val: np.ndarray = None, idx_dtype=np.int32, in_bf16: bool = False):
+    """argmin / argmax of ``a`` along ``axis`` (None = flattened) with the reference's fold rule.
+    Returns (idx, val).  ``init=None`` folds into the given ``out_idx`` / ``out_val``."""
+    lib = load()
+    if axis is None:
+        a = a.reshape(-1)
+        axis = 0
+    axis %= a.ndim
+    a = np.ascontiguousarray(a)
+    outer = int(np.prod(a.shape[:axis], dtype=np.int64))
+    reduced = a.shape[axis]
+    inner = int(np.prod(a.shape[axis + 1:], dtype=np.int64))
+    kept = a.shape[:axis] + a.shape[axis + 1:]
+    dt = dtype_code(a, in_bf16)
+    if out_idx is None:
+        out_idx = np.empty(kept, dtype=idx_dtype)
+    if out_val is None:
+        out_val = np.empty(kept, dtype=a.dtype)
+    assert out_idx.flags.c_contiguous and out_val.flags.c_contiguous
+    if isinstance(init, str):
+        init = default_arg_init(red, a, in_bf16)
+    ibuf = ctypes.create_string_buffer(_scalar(init, dt), 8) if init is not None else None
+    rc = lib.oracle_reduce_arg(red, dt, out_idx.dtype.itemsize, a.ctypes.data, out_idx.ctypes.data, out_val.ctypes.data,
+                               outer, reduced, inner, reduced * inner, inner, 1, 0, 0, ibuf)
+    if rc != 0:
+        raise RuntimeError('oracle_reduce_arg failed with %d' % rc)
+    return out_idx, out_val
