@@ -49,7 +49,7 @@ def _data(rng, shape, dtype, ties):
     # stay off the type's extreme values: an element equal to the start value (min_value / max_value of the
     # type) never replaces the (init, -1) pair in the reference, which NumPy's argmin/argmax do not model
     if ties:
-        return rng.integers(max(info.min, -4), min(info.max, 4) + 1, shape).astype(dtype)
+        return rng.integers(max(info.min + 1, -4), min(info.max - 1, 4) + 1, shape).astype(dtype)
     return rng.integers(max(info.min + 1, -30000), min(info.max - 1, 30000) + 1, shape).astype(dtype)
 
 
