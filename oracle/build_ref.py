@@ -182,6 +182,7 @@ def _gpu_programs(dace):
                 out[k] = 1
 
     sdfg = refgpu_hist_i32.to_sdfg()
+    sdfg.name = 'refgpu_hist_i32'  # the frontend prefixes the module name unless run as __main__
     sdfg.arrays['keys'].storage = G
     sdfg.arrays['bins'].storage = G
     for n, _ in sdfg.all_nodes_recursive():
@@ -191,7 +192,7 @@ def _gpu_programs(dace):
     return progs
 
 
-def build_all(verbose: bool = True) -> dict:
+def build_all(verbose: bool = True, only=None) -> dict:
     tmp = tempfile.mkdtemp(prefix='dace_b200_refbuild_')
     cwd = os.getcwd()
     os.chdir(tmp)  # the reference writes .dacecache/ into the cwd
@@ -202,8 +203,19 @@ def build_all(verbose: bool = True) -> dict:
         os.makedirs(REF_DIR, exist_ok=True)
         manifest = {'version': VERSION, 'reference_version': dace.__version__, 'programs': {}}
         manifest['failed'] = {}
+        if only:   # rebuild a few programs, keep the rest of an existing manifest
+            try:
+                with open(MANIFEST) as f:
+                    old = json.load(f)
+                manifest['programs'] = {k: v for k, v in old['programs'].items()
+                                        if os.path.exists(os.path.join(REF_DIR, v['lib']))}
+                manifest['failed'] = old.get('failed', {})
+            except Exception:
+                pass
         for sdfg, meta in _programs(dace) + _gpu_programs(dace):
             name = sdfg.name
+            if only and name not in only:
+                continue
             try:
                 csdfg = sdfg.compile()
             except Exception as ex:   # only tolerated for the GPU comparison programs
@@ -241,4 +253,4 @@ def build_all(verbose: bool = True) -> dict:
 
 
 if __name__ == '__main__':
-    build_all()
+    build_all(only=set(sys.argv[1:]) or None)

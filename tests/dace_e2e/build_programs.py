@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 4
+VERSION = 6
 
 
 def up_to_date() -> bool:
@@ -29,6 +29,14 @@ def up_to_date() -> bool:
                                                    for e in m['programs'].values())
     except Exception:
         return False
+
+
+def _to_sdfg(prog, **kwargs):
+    """The frontend prefixes the SDFG name with the defining module unless that is __main__; the manifest
+    keys must not depend on how this file was loaded (script vs. __graft_entry__.build())."""
+    sdfg = prog.to_sdfg(**kwargs)
+    sdfg.name = prog.f.__name__
+    return sdfg
 
 
 def _programs(dace):
@@ -56,7 +64,7 @@ def _programs(dace):
             sm_out[:] = np.sum(A, axis=1)
 
         for p in (b200_c1_npsum_axis1, b200_np_max_axis0_i64, b200_softmax_stats):
-            sdfg = p.to_sdfg()
+            sdfg = _to_sdfg(p)
             sdfg.apply_gpu_transformations()
             E.use_b200_reductions(sdfg)
             progs.append(sdfg)
@@ -137,7 +145,7 @@ def _programs(dace):
                 out[k] = v
 
     for j, p in enumerate((b200_hist_augassign, b200_hist_explicit_wcr, b200_hist_weighted_f32, b200_scatter_max_f64)):
-        sdfg = p.to_sdfg(simplify=True)
+        sdfg = _to_sdfg(p, simplify=True)
         if j % 2 == 0:   # both orders of the two rewrites are supported
             sdfg.apply_gpu_transformations()
             applied = SN.use_b200_scatter(sdfg)
@@ -160,12 +168,73 @@ def _programs(dace):
         for i in dace.map[0:N]:
             bins[keys[i]] += 1
 
-    sdfg = AUTO.auto_optimize(b200_auto_optimized.to_sdfg(simplify=True), dace.DeviceType.GPU)
+    sdfg = AUTO.auto_optimize(_to_sdfg(b200_auto_optimized, simplify=True), dace.DeviceType.GPU)
+    progs.append(sdfg)
+
+    # (7) In-kernel reductions: 'B200 (block)' on the SDFG of reference tests/blockreduce_cudatest.py:11-43
+    #     (register items per thread -> one value per block), and 'B200 (block allreduce)' reached through
+    #     the reference's ReduceExpansion transformation (reference
+    #     tests/transformations/subgraph_fusion/block_allreduce_cudatest.py:17-45).
+    from dace_b200 import block_expansion  # noqa: F401  (registers the expansions)
+    progs.append(_blockreduce_sdfg(dace, 'b200_blockreduce_f32', add, f32, nblocks=2, nthreads=32, items=2))
+    progs.append(_blockreduce_sdfg(dace, 'b200_blockreduce_i32_max', mx, i32, nblocks=5, nthreads=160, items=3))
+    progs.append(_blockreduce_sdfg(dace, 'b200_blockreduce_f64_min', 'lambda a, b: min(a, b)', f64, nblocks=3,
+                                   nthreads=1024, items=1))
+    progs.append(_blockreduce_sdfg(dace, 'b200_blockreduce_custom_i64', 'lambda a, b: a + b + a * b', dace.int64,
+                                   nblocks=4, nthreads=72, items=2))
+
+    from dace.transformation.dataflow import ReduceExpansion
+
+    @dace.program
+    def b200_blockallreduce(A: dace.float32[N, 96], B: dace.float32[N]):
+        B[:] = dace.reduce(lambda a, b: max(a, b), A, axis=1, identity=0)
+
+    sdfg = _to_sdfg(b200_blockallreduce)
+    sdfg.apply_gpu_transformations()
+    found = [(n, st) for st in sdfg.nodes() for n in st.nodes() if isinstance(n, E.Reduce)]
+    assert len(found) == 1
+    node, st = found[0]
+    node.implementation = 'B200 (block allreduce)'   # ReduceExpansion hands it on to the inner node
+    xf = ReduceExpansion()
+    xf.setup_match(sdfg, 0, sdfg.node_id(st), {ReduceExpansion.reduce: st.node_id(node)}, 0)
+    xf.apply(st, sdfg)
     progs.append(sdfg)
     return progs
 
 
-def build_all(verbose=True):
+def _blockreduce_sdfg(dace, name, wcr, dt, nblocks, nthreads, items):
+    """nblocks x nthreads x items values -> one value per block through a Reduce node inside the kernel."""
+    from dace.memlet import Memlet
+    from dace.transformation.interstate import GPUTransformSDFG
+    per_block = nthreads * items
+    sdfg = dace.SDFG(name)
+    sdfg.add_array('A', (nblocks * per_block, ), dt)
+    sdfg.add_array('B', (nblocks, ), dt)
+    sdfg.add_transient('tA', (items, ), dt)
+    sdfg.add_transient('tB', (1, ), dt)
+    st = sdfg.add_state('a')
+    A, B, tA, tB = st.add_access('A'), st.add_access('B'), st.add_access('tA'), st.add_access('tB')
+    me, mx = st.add_map('blocks', dict(bi='0:%d' % nblocks))
+    mei, mxi = st.add_map('threads', dict(i='0:%d' % nthreads))
+    red = st.add_reduce(wcr, None, 0)
+    red.implementation = 'B200 (block)'
+    wt = st.add_tasklet('writeout', {'inp'}, {'out'}, 'if i == 0: out = inp')
+    st.add_edge(A, None, me, None, Memlet.simple(A, '0:%d' % (nblocks * per_block)))
+    st.add_edge(me, None, mei, None, Memlet.simple(A, '(%d*bi):(%d*bi+%d)' % (per_block, per_block, per_block)))
+    st.add_edge(mei, None, tA, None,
+                Memlet.simple('A', '(%d*bi+%d*i):(%d*bi+%d*i+%d)' % (per_block, items, per_block, items, items)))
+    st.add_edge(tA, None, red, None, Memlet.simple(tA, '0:%d' % items))
+    st.add_edge(red, None, tB, None, Memlet.simple(tB, '0'))
+    st.add_edge(tB, None, wt, 'inp', Memlet.simple(tB, '0'))
+    st.add_edge(wt, 'out', mxi, None, Memlet.simple('B', 'bi', num_accesses=-1))
+    st.add_edge(mxi, None, mx, None, Memlet.simple(B, 'bi'))
+    st.add_edge(mx, None, B, None, Memlet.simple(B, '0:%d' % nblocks))
+    sdfg.fill_scope_connectors()
+    sdfg.apply_transformations(GPUTransformSDFG, options={'sequential_innermaps': False})
+    return sdfg
+
+
+def build_all(verbose=True, only=None):
     from oracle.refenv import import_reference
     tmp = tempfile.mkdtemp(prefix='dace_b200_e2e_')
     cwd = os.getcwd()
@@ -176,8 +245,17 @@ def build_all(verbose=True):
             raise RuntimeError('reference checkout not available')
         os.makedirs(OUT, exist_ok=True)
         manifest = {'version': VERSION, 'reference_version': dace.__version__, 'programs': {}}
+        if only:
+            try:
+                old = json.load(open(os.path.join(OUT, 'manifest.json')))
+                manifest['programs'] = {k: v for k, v in old['programs'].items()
+                                        if os.path.exists(os.path.join(OUT, v['lib']))}
+            except Exception:
+                pass
         for sdfg in _programs(dace):
             name = sdfg.name
+            if only and name not in only:
+                continue
             csdfg = sdfg.compile()
             lib = 'lib%s.so' % name
             shutil.copyfile(csdfg.filename, os.path.join(OUT, lib))
@@ -190,11 +268,15 @@ def build_all(verbose=True):
                 else:
                     args.append({'name': aname, 'kind': 'symbol', 'ctype': g.symbols[aname].ctype})
             init_names = [n.strip() for n in g.init_signature(for_call=True).split(',') if n.strip()]
-            src = open(os.path.join(os.path.dirname(os.path.dirname(csdfg.filename)), 'src', 'cpu', name + '.cpp')).read()
+            srcdir = os.path.join(os.path.dirname(os.path.dirname(csdfg.filename)), 'src')
+            src = open(os.path.join(srcdir, 'cpu', name + '.cpp')).read()
+            cu = os.path.join(srcdir, 'cuda', name + '_cuda.cu')
+            cu = open(cu).read() if os.path.exists(cu) else ''
             manifest['programs'][name] = {
                 'lib': lib, 'args': args,
                 'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
-                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter('),
+                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') +
+                cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
             }
             if verbose:
                 print('built', name, [a['name'] for a in args], 'b200 calls:', manifest['programs'][name]['b200_calls'],
@@ -207,4 +289,4 @@ def build_all(verbose=True):
 
 
 if __name__ == '__main__':
-    build_all()
+    build_all(only=set(sys.argv[1:]) or None)

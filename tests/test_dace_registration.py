@@ -89,3 +89,55 @@ def test_no_cpu_fallback_and_custom_rejected(dace):
         custom.expand_library_nodes()
     ok = _sdfg(dace, 'b200_codegen_custommin', [1], 'lambda a, b: a if a < b else b', 1e30)
     assert 'dace_b200_reduce_nd(1, 0, 0,' in ''.join(c.clean_code for c in ok.generate_code())
+
+
+# ---- in-kernel expansions (dace_b200/block_expansion.py) ----
+
+def _load_build_programs():
+    import importlib.util
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'dace_e2e', 'build_programs.py')
+    spec = importlib.util.spec_from_file_location('dace_e2e_build_programs_for_tests', path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_block_expansions_registered(dace):
+    from dace.libraries.standard.nodes.reduce import Reduce
+    from dace_b200 import block_expansion as BE
+    assert Reduce.implementations['B200 (block)'] is BE.ExpandReduceB200Block
+    assert Reduce.implementations['B200 (block allreduce)'] is BE.ExpandReduceB200BlockAll
+    assert BE.B200BlockReduce.headers['cuda'] == ['dace_b200_block_reduce.cuh']
+    assert BE.B200BlockReduce.cmake_libraries == []      # header-only: nothing to link
+
+
+def test_block_expansion_generated_kernel_calls_the_header(dace):
+    bp = _load_build_programs()
+    from dace_b200 import block_expansion  # noqa: F401
+    sdfg = bp._blockreduce_sdfg(dace, 'b200_cg_block_i32', 'lambda a, b: a + b', dace.int32, nblocks=3, nthreads=96, items=4)
+    code = ''.join(c.clean_code for c in sdfg.generate_code())
+    assert '#include "dace_b200_block_reduce.cuh"' in code
+    assert 'dace_b200::block_reduce<int, 96, ' in code
+    assert 'reinterpret_cast<const int (&)[4]>(*_in), dace_b200::op<3, int>()' in code
+    assert 'cub::' not in code
+    custom = bp._blockreduce_sdfg(dace, 'b200_cg_block_custom', 'lambda a, b: a + b + a * b', dace.int64, 2, 64, 1)
+    code = ''.join(c.clean_code for c in custom.generate_code())
+    assert 'struct __b200_reduce_b200_cg_block_custom_' in code and 'dace_b200::block_reduce<int64_t, 64, ' in code \
+        or 'dace_b200::block_reduce<long long, 64, ' in code
+
+
+def test_block_expansion_errors_match_the_reference(dace):
+    """Outside a kernel / without identity: same ValueErrors as reference reduce.py:665-716."""
+    from oracle.build_ref import _reduce_sdfg
+    from dace_b200 import block_expansion  # noqa: F401
+    host = _reduce_sdfg(dace, 'b200_cg_block_host', dace.float32, dace.float32, 1, None, 'lambda a, b: a + b', 0,
+                        'B200 (block)')
+    with pytest.raises(ValueError, match='within a GPU kernel|register'):
+        host.expand_library_nodes()
+    bp = _load_build_programs()
+    noident = bp._blockreduce_sdfg(dace, 'b200_cg_block_noident', 'lambda a, b: a + b', dace.float32, 2, 32, 2)
+    for n, _ in noident.all_nodes_recursive():
+        if isinstance(n, block_expansion.Reduce):
+            n.identity = None
+    with pytest.raises(ValueError, match='initial value'):
+        noident.expand_library_nodes()

@@ -186,3 +186,44 @@ def test_auto_optimized_program_uses_the_backend_everywhere(cuda):
     assert close_f32(rs, a.astype(np.float64).sum(1), a, (1, ))
     assert mx[0] == a.max()
     np.testing.assert_array_equal(bins, np.bincount(keys, minlength=m).astype(np.int32))
+
+
+# ---- in-kernel reductions: 'B200 (block)' / 'B200 (block allreduce)' (dace_b200/block_expansion.py) ----
+
+@pytest.mark.parametrize('name,dt,nblocks,nthreads,items,red', [
+    ('b200_blockreduce_f32', np.float32, 2, 32, 2, 'sum'),          # reference tests/blockreduce_cudatest.py:11-56
+    ('b200_blockreduce_i32_max', np.int32, 5, 160, 3, 'max'),
+    ('b200_blockreduce_f64_min', np.float64, 3, 1024, 1, 'min'),
+    ('b200_blockreduce_custom_i64', np.int64, 4, 72, 2, 'affine'),  # custom lambda a + b + a*b -> generated functor
+])
+def test_block_reduce_inside_a_generated_kernel(cuda, name, dt, nblocks, nthreads, items, red):
+    rng = np.random.default_rng(11)
+    n = nblocks * nthreads * items
+    if red == 'affine':
+        a = rng.integers(-3, 4, n).astype(dt)
+    elif np.issubdtype(dt, np.floating):
+        a = rng.random(n).astype(dt)
+    else:
+        a = rng.integers(-10**9, 10**9, n).astype(dt)
+    b = np.full(nblocks, 77).astype(dt)
+    prog(name)(A=a, B=b)
+    blocks = a.reshape(nblocks, -1)
+    if red == 'sum':
+        assert close_f32(b, blocks.astype(np.float64).sum(1), blocks, (1, ))
+        assert close_f32(b, O.reduce(O.SUM, blocks, (1, ), identity=0, wide=True), blocks, (1, ))
+    elif red == 'max':
+        np.testing.assert_array_equal(b, O.reduce(O.MAX, blocks, (1, ), identity=np.iinfo(dt).min))
+    elif red == 'min':
+        np.testing.assert_array_equal(b, O.reduce(O.MIN, blocks, (1, ), identity=np.finfo(dt).max))
+    else:
+        np.testing.assert_array_equal(b, np.prod(1 + blocks, axis=1, dtype=np.int64) - 1)
+
+
+def test_block_allreduce_through_reduce_expansion(cuda):
+    """dace.reduce(max, A, axis=1) -> ReduceExpansion -> inner node 'B200 (block allreduce)': one block per row,
+    96 threads, result stored by thread 0 (reference block_allreduce_cudatest.py:17-45)."""
+    a = np.random.default_rng(12).standard_normal((301, 96)).astype(np.float32)
+    b = np.zeros(301, np.float32)
+    prog('b200_blockallreduce')(A=a, B=b, N=301)
+    np.testing.assert_array_equal(b, O.reduce(O.MAX, a, (1, ), identity=0))   # identity 0 like the reference test
+    np.testing.assert_array_equal(b, np.maximum(a.max(1), 0))
