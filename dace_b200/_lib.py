@@ -59,6 +59,16 @@ _PROTOTYPES = {
         _c.c_int, _c.c_int, _c.c_void_p, _c.c_size_t, _c.POINTER(_c.c_void_p), _c.c_int, _c.c_int, _c.c_uint64,
         _c.c_size_t, _c.c_void_p
     ]),
+    'dace_b200_comm_unique_id': (_c.c_int, [_c.c_char_p]),
+    'dace_b200_comm_create': (_c.c_int, [_c.c_int, _c.c_int, _c.c_char_p, _c.POINTER(_c.c_void_p)]),
+    'dace_b200_comm_create_from_env': (_c.c_int, [_c.POINTER(_c.c_void_p)]),
+    'dace_b200_comm_destroy': (_c.c_int, [_c.c_void_p]),
+    'dace_b200_comm_rank': (_c.c_int, [_c.c_void_p]),
+    'dace_b200_comm_world': (_c.c_int, [_c.c_void_p]),
+    'dace_b200_comm_uses_peer_memory': (_c.c_int, [_c.c_void_p]),
+    'dace_b200_comm_set_default': (_c.c_int, [_c.c_void_p]),
+    'dace_b200_comm_default': (_c.c_int, [_c.POINTER(_c.c_void_p)]),
+    'dace_b200_comm_allreduce': (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p, _c.c_size_t, _c.c_void_p]),
 }
 
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)

@@ -212,6 +212,42 @@ DACE_B200_API int dace_b200_peer_allreduce(int redtype, int dtype, void* data, s
                                            int rank, int world, unsigned long long epoch, size_t cap_bytes,
                                            dace_b200_stream_t stream);
 
+/* ---- Communicator for generated programs (one process per GPU) ----------------------------
+ * What the `B200` expansion of the AllReduceCombine library node (dace_b200/comm_node.py) calls
+ * right after a local reduction whose sharded axis is the reduced one.  Plays the role of the
+ * reference's MPI environment + Allreduce node (reference dace/libraries/mpi/environments/mpi.py:6-22,
+ * dace/libraries/mpi/nodes/allreduce.py:9-60): NCCL over NVLink / NVSwitch, bound at run time
+ * (dlopen of libnccl.so.2; DACE_B200_NCCL_LIB overrides), plus the one-shot peer-memory kernel
+ * above for payloads <= 64 KiB when CUDA IPC works between the ranks (DACE_B200_NO_PEER=1 turns
+ * it off).  The IPC handles travel through NCCL itself (all-gather), so no other transport is
+ * needed.
+ *   _unique_id / _create : explicit rendezvous, `id128` (128 bytes, made on rank 0) shipped by the
+ *                          host over any transport; world == 1 needs neither an id nor NCCL.
+ *   _create_from_env     : RANK / WORLD_SIZE from the environment (torchrun, mpirun wrappers);
+ *                          the id travels through the file DACE_B200_RENDEZVOUS (default
+ *                          /tmp/dace_b200_nccl_<MASTER_ADDR>_<MASTER_PORT>.id).  The CUDA device
+ *                          must already be selected (cudaSetDevice / CUDA_VISIBLE_DEVICES).
+ *   _default             : process-wide communicator: the one installed with _set_default, else
+ *                          created from the environment on first use (generated init code).
+ *   _allreduce           : in place on `data[0:nelem]`, enqueued on `stream`, never synchronises.
+ *                          Sum / Product / Min / Max for every dtype of this header that NCCL
+ *                          has; Logical_And/Or as Min/Max of the 0/1 partials; bitwise operators
+ *                          and Logical_Xor only on the peer-memory path (32/64-bit integers,
+ *                          <= 64 KiB), else cudaErrorNotSupported.  Results of the peer path are
+ *                          folded in rank order: bit-identical on every rank.
+ * All calls are collective over the ranks of the communicator. */
+DACE_B200_API int dace_b200_comm_unique_id(unsigned char* id128);
+DACE_B200_API int dace_b200_comm_create(int rank, int world, const unsigned char* id128, void** comm);
+DACE_B200_API int dace_b200_comm_create_from_env(void** comm);
+DACE_B200_API int dace_b200_comm_destroy(void* comm);
+DACE_B200_API int dace_b200_comm_rank(void* comm);
+DACE_B200_API int dace_b200_comm_world(void* comm);
+DACE_B200_API int dace_b200_comm_uses_peer_memory(void* comm);
+DACE_B200_API int dace_b200_comm_set_default(void* comm);
+DACE_B200_API int dace_b200_comm_default(void** comm);
+DACE_B200_API int dace_b200_comm_allreduce(void* comm, int redtype, int dtype, void* data, size_t nelem,
+                                           dace_b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

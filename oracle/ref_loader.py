@@ -59,6 +59,8 @@ class RefProgram:
         if self._state is None or syms != self._state_syms:
             self.close()
             self._state = self._init(*syms)
+            if not self._state:
+                raise RuntimeError('__dace_init_%s failed (returned NULL)' % self.name)
             self._state_syms = syms
         call = []
         for a in self.meta['args']:

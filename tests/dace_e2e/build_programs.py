@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 6
+VERSION = 7
 
 
 def up_to_date() -> bool:
@@ -199,6 +199,28 @@ def _programs(dace):
     xf.setup_match(sdfg, 0, sdfg.node_id(st), {ReduceExpansion.reduce: st.node_id(node)}, 0)
     xf.apply(st, sdfg)
     progs.append(sdfg)
+
+    # (8) Multi-GPU: every rank runs this program on its own row / key shard; the sharding transformation
+    #     (dace_b200/comm_node.py) inserts AllReduceCombine after the reductions over the sharded axis
+    #     (column sum, full max with a non-neutral identity, histogram) and leaves the row sum local.
+    from dace_b200 import comm_node as CN
+
+    @dace.program
+    def b200_sharded(A: dace.float32[N, M], keys: dace.int32[N], cs: dace.float32[M], tot: dace.float32[1],
+                     rs: dace.float32[N], bins: dace.int32[M]):
+        cs[:] = np.sum(A, axis=0)
+        tot[0] = dace.reduce(lambda a, b: max(a, b), A, identity=0.25)
+        rs[:] = np.sum(A, axis=1)
+        for i in dace.map[0:N]:
+            bins[keys[i]] += 1
+
+    sdfg = _to_sdfg(b200_sharded, simplify=True)
+    sdfg.apply_gpu_transformations()
+    AUTO.apply_b200(sdfg)
+    counts = CN.shard_reductions(sdfg, {'A': 0, 'keys': 0})
+    if counts != {'reduce': 2, 'scatter': 1, 'local': 1}:
+        raise RuntimeError('b200_sharded: unexpected sharding result %s' % counts)
+    progs.append(sdfg)
     return progs
 
 
@@ -277,6 +299,7 @@ def build_all(verbose=True, only=None):
                 'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
                 'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') +
                 cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
+                'comm_calls': src.count('dace_b200_comm_allreduce('),
             }
             if verbose:
                 print('built', name, [a['name'] for a in args], 'b200 calls:', manifest['programs'][name]['b200_calls'],

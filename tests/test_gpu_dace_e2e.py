@@ -227,3 +227,28 @@ def test_block_allreduce_through_reduce_expansion(cuda):
     prog('b200_blockallreduce')(A=a, B=b, N=301)
     np.testing.assert_array_equal(b, O.reduce(O.MAX, a, (1, ), identity=0))   # identity 0 like the reference test
     np.testing.assert_array_equal(b, np.maximum(a.max(1), 0))
+
+
+# ---- multi-GPU sharding transformation (dace_b200/comm_node.py), single rank: the combine is a no-op ----
+
+def test_sharded_program_single_rank(cuda):
+    """b200_sharded was rewritten by shard_reductions({'A': 0, 'keys': 0}): three AllReduceCombine nodes.
+    With one process (no WORLD_SIZE) the communicator has world 1 and the program must behave like the
+    unsharded one - in particular identities count exactly once (non-neutral identity 0.25 of the max)."""
+    m = ref_loader.manifest(BUILT)['programs']['b200_sharded']
+    assert m['comm_calls'] == 3
+    rng = np.random.default_rng(21)
+    a = rng.standard_normal((777, 300)).astype(np.float32)
+    keys = rng.integers(0, 300, 777).astype(np.int32)
+    cs, tot, rs = np.zeros(300, np.float32), np.zeros(1, np.float32), np.zeros(777, np.float32)
+    bins = np.full(300, 7, np.int32)
+    p = prog('b200_sharded')
+    p(A=a, keys=keys, cs=cs, tot=tot, rs=rs, bins=bins, N=777, M=300)
+    assert close_f32(cs, a.astype(np.float64).sum(0), a, (0, ))
+    assert close_f32(rs, a.astype(np.float64).sum(1), a, (1, ))
+    assert tot[0] == max(a.max(), np.float32(0.25))
+    np.testing.assert_array_equal(bins, 7 + np.bincount(keys, minlength=300).astype(np.int32))
+    neg = -np.abs(a) - 1
+    p(A=neg, keys=keys, cs=cs, tot=tot, rs=rs, bins=bins, N=777, M=300)
+    assert tot[0] == np.float32(0.25)                 # the identity, folded once
+    np.testing.assert_array_equal(bins, 7 + 2 * np.bincount(keys, minlength=300).astype(np.int32))
