@@ -71,6 +71,9 @@ cudaError_t launch_arg(int red, int dtin, const ArgArgs& a, const Launch& l);
 struct ScatterArgs {
     const void* idx; const void* values; const void* const_value;
     size_t n; void* bins; size_t nbins;
+    // Device-side path selection: when `gate` is set, a kernel runs only if *gate == gate_run_if
+    // (written by the key sampler of wcr_partition.cu earlier on the same stream).
+    const int* gate = nullptr; int gate_run_if = 0;
 };
 cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l);
 // Partition + shared-memory histogram path for large bin arrays (wcr_partition.cu);
@@ -80,6 +83,10 @@ cudaError_t launch_peer_allreduce(int red, int dtype, void* data, size_t nelem, 
                                   unsigned long long epoch, size_t cap_bytes, cudaStream_t stream);
 size_t peer_buffer_bytes(int world, size_t cap_bytes);
 
-cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l);
+// On success *gate (may be null afterwards) is the device flag the partitioned kernel was gated on
+// (0 = it ran; 1 = the sampler found clustered keys and it returned at once): the caller then
+// launches the global-atomic kernel gated on 1 and calls scatter_partition_done().
+cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l, const int** gate);
+cudaError_t scatter_partition_done(const Launch& l);
 
 }  // namespace db200

@@ -62,7 +62,9 @@ __device__ __forceinline__ void group_sync(unsigned g) {
 template <class V>
 __global__ void __launch_bounds__(kPartThreads, 1)
 scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict__ bins, unsigned nbins, V cval,
-                         unsigned* buf, unsigned* gcur, size_t chunk, unsigned cap, int B, int S, int aligned) {
+                         unsigned* buf, unsigned* gcur, size_t chunk, unsigned cap, int B, int S, int aligned,
+                         const int* __restrict__ gate) {
+    if (*gate != 0) return;   // clustered keys: the global-atomic kernel behind this one does the work (grid-uniform)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     V* hist = reinterpret_cast<V*>(smem_raw);                                  // [kBucketBins]
     unsigned* stage_all = reinterpret_cast<unsigned*>(smem_raw + size_t(kBucketBins) * sizeof(V));   // [kGroups][kTileKeys]
@@ -251,11 +253,23 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
     }
 }
 
+// Key sampler: 1024 adjacent pairs spread over the keys.  Sorted input or long runs of one key
+// (>= half of the pairs equal) are cheap for warp-merged global atomics and unbalanced for the
+// partition (one bucket gets a whole chunk), so the flag routes the call to the other kernel.
+__global__ void __launch_bounds__(1024) scatter_sample_kernel(const unsigned* __restrict__ keys, size_t n, int* flag) {
+    const size_t stride = (n - 1) / 1024;
+    const size_t p = size_t(threadIdx.x) * stride;
+    const int equal = __ldg(keys + p) == __ldg(keys + p + 1);
+    const int cnt = __syncthreads_count(equal);
+    if (threadIdx.x == 0) *flag = (cnt >= 512) ? 1 : 0;
+}
+
 // Per-device scratch: the double-buffered partitioned keys and the per-chunk
 // bucket cursors.  Uses from different streams are serialised with an event.
 struct PartScratch {
     unsigned* buf = nullptr;
     unsigned* gcur = nullptr;
+    int* flag = nullptr;
     size_t buf_words = 0;
     cudaEvent_t last = nullptr;
     int coop = -1;
@@ -264,7 +278,7 @@ static std::mutex g_part_mutex;
 static PartScratch g_part[64];
 
 template <class V>
-static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Launch& l) {
+static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Launch& l, const int** gate_out) {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
@@ -317,6 +331,10 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Laun
         e = cudaMalloc(&ps.gcur, kMaxChunks * size_t(kMaxBuckets) * sizeof(unsigned));
         if (e != cudaSuccess) { ps.gcur = nullptr; return e; }
     }
+    if (ps.flag == nullptr) {
+        e = cudaMalloc(&ps.flag, 256);
+        if (e != cudaSuccess) { ps.flag = nullptr; return e; }
+    }
     if (ps.last == nullptr) {
         e = cudaEventCreateWithFlags(&ps.last, cudaEventDisableTiming);
         if (e != cudaSuccess) return e;
@@ -329,6 +347,9 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Laun
 
     const unsigned* keys = reinterpret_cast<const unsigned*>(a.idx);
     size_t n = a.n;
+    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(keys, n, ps.flag);
+    const int* gate = ps.flag;
+    *gate_out = gate;
     V* bins = reinterpret_cast<V*>(a.bins);
     unsigned nbins = unsigned(a.nbins);
     unsigned* buf = ps.buf;
@@ -337,23 +358,32 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Laun
     unsigned cap_arg = cap;
     int B_arg = B, S_arg = S;
     int aligned = (reinterpret_cast<size_t>(a.idx) & 15) == 0;
-    void* args[] = {&keys, &n, &bins, &nbins, &cval, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned};
+    void* args[] = {&keys, &n, &bins, &nbins, &cval, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate};
     e = cudaLaunchCooperativeKernel((void*)kern, dim3(sms), dim3(kPartThreads), args, smem, l.stream);
     if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }
-    return cudaEventRecord(ps.last, l.stream);
+    return cudaSuccess;   // the event is recorded by scatter_partition_done(), after the gated global kernel
+}
+
+cudaError_t scatter_partition_done(const Launch& l) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(g_part_mutex);
+    if (dev < 0 || dev >= 64 || g_part[dev].last == nullptr) return cudaErrorInvalidValue;
+    return cudaEventRecord(g_part[dev].last, l.stream);
 }
 
 // Returns cudaErrorNotSupported when the partitioned path does not apply (caller falls back
 // to the global-atomic kernel - still a GPU path).
-cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l) {
+cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l, const int** gate) {
     if (a.values != nullptr) return cudaErrorNotSupported;
     if (dtidx != DT_I32 && dtidx != DT_U32) return cudaErrorNotSupported;
     if (a.n < (size_t(1) << 22)) return cudaErrorNotSupported;
     if (a.nbins * 4 <= (size_t(96) << 10) || a.nbins > size_t(kMaxBuckets) * kBucketBins) return cudaErrorNotSupported;
     switch (dtval) {
-        case DT_I32: { int c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<int>(a, c, l); }
-        case DT_U32: { unsigned c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<unsigned>(a, c, l); }
-        case DT_F32: { float c = 1.f; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<float>(a, c, l); }
+        case DT_I32: { int c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<int>(a, c, l, gate); }
+        case DT_U32: { unsigned c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<unsigned>(a, c, l, gate); }
+        case DT_F32: { float c = 1.f; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<float>(a, c, l, gate); }
         default: return cudaErrorNotSupported;
     }
 }

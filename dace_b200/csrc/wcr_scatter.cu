@@ -100,7 +100,8 @@ template <class I> __device__ __forceinline__ long long idx_at(const Words<16>& 
 template <int RED, class I, class V, bool HAS_VALUES, int U>
 __global__ void __launch_bounds__(512)
 scatter_global_kernel(const I* __restrict__ idx, const V* __restrict__ values, V cval, size_t n,
-                      V* __restrict__ bins, size_t nbins) {
+                      V* __restrict__ bins, size_t nbins, const int* __restrict__ gate, int gate_run_if) {
+    if (gate != nullptr && *gate != gate_run_if) return;   // the partitioned kernel took this call
     const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     const size_t nthr = size_t(gridDim.x) * blockDim.x;
     if constexpr (HAS_VALUES) {
@@ -266,10 +267,10 @@ static cudaError_t launch_scatter_t(const ScatterArgs& a, const Launch& l) {
     if (grid > need) grid = need;
     if (a.values)
         scatter_global_kernel<RED, I, V, true, 4><<<(unsigned)grid, 512, 0, l.stream>>>(
-            (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins);
+            (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins, a.gate, a.gate_run_if);
     else
         scatter_global_kernel<RED, I, V, false, 4><<<(unsigned)grid, 512, 0, l.stream>>>(
-            (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins);
+            (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins, a.gate, a.gate_run_if);
     return cudaGetLastError();
 }
 
@@ -308,7 +309,19 @@ static cudaError_t launch_scatter_val(int red, int dtval, const ScatterArgs& a, 
 
 cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l) {
     if (red == RT_Sum && getenv("DACE_B200_NO_PARTITION") == nullptr) {
-        cudaError_t e = launch_scatter_partitioned(dtidx, dtval, a, l);
+        const int* gate = nullptr;
+        cudaError_t e = launch_scatter_partitioned(dtidx, dtval, a, l, &gate);
+        if (e == cudaSuccess) {
+            // Keys that arrive sorted / in long runs are served better by the warp-merged global
+            // atomics (0.36 ms vs 2.7 ms for sorted C4 keys): the sampler decided on the device,
+            // exactly one of the two kernels does the work, the other returns at once.
+            ScatterArgs g = a;
+            g.gate = gate;
+            g.gate_run_if = 1;
+            e = (dtidx == DT_I32) ? launch_scatter_val<int>(red, dtval, g, l) : launch_scatter_val<unsigned>(red, dtval, g, l);
+            cudaError_t e2 = scatter_partition_done(l);
+            return e != cudaSuccess ? e : e2;
+        }
         if (e != cudaErrorNotSupported) return e;
     }
     switch (dtidx) {

@@ -9,6 +9,7 @@ decision is taken structurally on the lambda's AST.  Numeric values equal the
 C++ enum, which is what the C ABI takes.
 """
 import ast
+import functools
 import enum
 from typing import Optional, Union
 
@@ -105,6 +106,15 @@ def lower_custom(wcr_str: str) -> ReductionType:
     return ReductionType.Min if picks_smaller else ReductionType.Max
 
 
+@functools.lru_cache(maxsize=256)
+def _classify_lambda(op: str) -> ReductionType:
+    # parsing a lambda costs ~20 us; hot loops pass the same string on every call
+    rt = detect_reduction_type(op)
+    if rt == ReductionType.Custom:
+        rt = lower_custom(op)
+    return rt
+
+
 def resolve(op) -> ReductionType:
     """Accept a ReductionType, its name, or a lambda string; reject what the
     precompiled sm_100a kernels cannot run (no CPU fallback)."""
@@ -115,9 +125,7 @@ def resolve(op) -> ReductionType:
     elif isinstance(op, str) and op in ReductionType.__members__:
         rt = ReductionType[op]
     elif isinstance(op, str):
-        rt = detect_reduction_type(op)
-        if rt == ReductionType.Custom:
-            rt = lower_custom(op)
+        rt = _classify_lambda(op)
     else:
         raise TypeError('reduction operator must be a ReductionType, its name or a lambda string')
     if rt is None or rt < ReductionType.Min or rt > ReductionType.Bitwise_Xor:

@@ -228,3 +228,42 @@ def test_global_path_merges_equal_keys_in_a_warp(dist, cuda):
     bf = torch.zeros(nbins, dtype=torch.float64, device=cuda)
     db.wcr_scatter('lambda a, b: a + b', bf, tk, 0.25)
     np.testing.assert_array_equal(bf.cpu().numpy(), 0.25 * np.bincount(ok, minlength=nbins))
+
+
+@pytest.mark.parametrize('dist', ['sorted', 'runs', 'all_equal', 'uniform_then_sorted'])
+def test_device_side_path_selection(dist, cuda):
+    """int32 Sum into a large bin array: a device-side key sample routes sorted / long-run inputs to the
+    warp-merged global-atomic kernel and everything else to the partitioned kernel (exactly one of
+    the two runs).  Whatever is chosen, counts are bit-exact and back-to-back calls on two streams with
+    different decisions do not disturb each other."""
+    rng = np.random.default_rng(23)
+    n, nbins = (1 << 23) + 1234, 1 << 20
+    uniform = rng.integers(0, nbins, n).astype(np.int32)
+    if dist == 'sorted':
+        keys = np.sort(uniform)
+    elif dist == 'runs':
+        keys = np.repeat(rng.integers(0, nbins, n // 64 + 1), 64)[:n].astype(np.int32)
+    elif dist == 'all_equal':
+        keys = np.full(n, 77777, np.int32)
+    else:
+        keys = uniform
+    start = rng.integers(0, 3, nbins).astype(np.int32)
+    bins = torch.from_numpy(start.copy()).to(cuda)
+    tk = torch.from_numpy(keys).to(cuda)
+    db.wcr_scatter('lambda a, b: a + b', bins, tk)
+    np.testing.assert_array_equal(bins.cpu().numpy(), start + np.bincount(keys, minlength=nbins).astype(np.int32))
+    if dist == 'uniform_then_sorted':
+        ts = torch.from_numpy(np.sort(uniform)).to(cuda)
+        b1 = torch.zeros(nbins, dtype=torch.int32, device=cuda)
+        b2 = torch.zeros(nbins, dtype=torch.int32, device=cuda)
+        s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+        torch.cuda.synchronize()
+        for _ in range(3):
+            with torch.cuda.stream(s1):
+                db.wcr_scatter('lambda a, b: a + b', b1, tk)
+            with torch.cuda.stream(s2):
+                db.wcr_scatter('lambda a, b: a + b', b2, ts)
+        torch.cuda.synchronize()
+        ref = 3 * np.bincount(uniform, minlength=nbins).astype(np.int32)
+        np.testing.assert_array_equal(b1.cpu().numpy(), ref)
+        np.testing.assert_array_equal(b2.cpu().numpy(), ref)
