@@ -5,7 +5,10 @@
 // reference's reduction planner does - drop unit dims, merge contiguous dims of
 // the same kind (reference dace/libraries/standard/reduction_planner.py:44-118) -
 // and then picks one of the hand-written kernels instead of emitting a schedule.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
+#include <limits>
 #include <mutex>
 #include "../../include/dace_b200_reduce.h"
 #include "common.cuh"
@@ -84,6 +87,103 @@ static cudaError_t plan_split(int red, int dtin, int dtout, const void* in, void
     return launch_split(red, dtin, dtout, a, l);
 }
 
+// [K, R] with contiguous R: few long rows -> split kernel, else the rows kernel.
+static cudaError_t plan_rows(int red, int dtin, int dtout, const void* in, void* out, size_t rows, size_t n,
+                             size_t row_stride, ptrdiff_t out_stride, const void* identity, const Launch& l) {
+    const size_t row_bytes = n * dtype_size(dtin);
+    if (rows < 2 * (size_t)sm_count() && row_bytes >= (size_t(128) << 10) && rows <= kCounters)
+        return plan_split(red, dtin, dtout, in, out, rows, n, row_stride, out_stride, identity, l);
+    RowsArgs a{in, out, rows, n, row_stride, out_stride, identity};
+    return launch_rows(red, dtin, dtout, a, l);
+}
+
+// Host copy of Op::neutral() for the accumulator types a two-pass plan stores between its passes.
+static bool neutral_bytes(int red, int dt, unsigned char out[8]) {
+    memset(out, 0, 8);
+    auto put = [&](auto v) { memcpy(out, &v, sizeof(v)); return true; };
+    const bool mn = red == RT_Min, mx = red == RT_Max;
+    switch (red) {
+        case RT_Sum: case RT_BOr: case RT_BXor: case RT_LOr: case RT_LXor: return true;   // all-zero bits
+        case RT_Product: case RT_LAnd:
+            switch (dt) {
+                case DT_F32: return put(1.0f);
+                case DT_F64: return put(1.0);
+                case DT_I32: case DT_U32: return put((int)1);
+                case DT_I64: case DT_U64: return put((long long)1);
+                default: return false;
+            }
+        case RT_BAnd: memset(out, 0xff, 8); return dt != DT_F32 && dt != DT_F64;
+        case RT_Min: case RT_Max:
+            switch (dt) {
+                case DT_F32: return put(mn ? 0x7f800000u : 0xff800000u);
+                case DT_F64: return put(mn ? 0x7ff0000000000000ull : 0xfff0000000000000ull);
+                case DT_I32: return put(mn ? std::numeric_limits<int>::max() : std::numeric_limits<int>::lowest());
+                case DT_U32: return put(mn ? std::numeric_limits<unsigned>::max() : 0u);
+                case DT_I64: return put(mn ? std::numeric_limits<long long>::max() : std::numeric_limits<long long>::lowest());
+                case DT_U64: return put(mn ? std::numeric_limits<unsigned long long>::max() : 0ull);
+                default: return false;
+            }
+        default: (void)mx; return false;
+    }
+}
+
+// Scratch between the passes of a two-pass plan: per device, grown on demand, kept; uses from
+// different streams are ordered by an event (same protocol as the partitioned scatter's scratch).
+struct MidScratch {
+    void* buf = nullptr;
+    size_t bytes = 0;
+    cudaEvent_t last = nullptr;
+};
+static std::mutex g_mid_mutex;
+static MidScratch g_mid[64];
+constexpr size_t kMidMaxBytes = size_t(256) << 20;
+
+// [R1, K, R2] with contiguous R2 (e.g. per-channel statistics of an [N, C, H*W] array: axes (0, 2)):
+// pass 1 folds every contiguous R2 run with the row kernels into mid[R1, K] (neutral seed),
+// pass 2 folds mid over R1 with the column kernel and applies the caller's identity.  Both passes
+// are the streaming kernels; the generic strided kernel it replaces ran one warp per output.
+static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, void* out, size_t R1, size_t K,
+                                 size_t R2, size_t row_stride, ptrdiff_t out_stride_k, const void* identity,
+                                 const Launch& l) {
+    const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
+    unsigned char neutral[8];
+    if (!supported_pair(dtin, dtmid) || !supported_pair(dtmid, dtout) || !neutral_bytes(red, dtmid, neutral))
+        return cudaErrorNotSupported;
+    const size_t need = R1 * K * dtype_size(dtmid);
+    if (need > kMidMaxBytes) return cudaErrorNotSupported;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorNotSupported;
+    std::lock_guard<std::mutex> lock(g_mid_mutex);
+    MidScratch& ms = g_mid[dev];
+    if (ms.last == nullptr) {
+        e = cudaEventCreateWithFlags(&ms.last, cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+    } else {
+        e = cudaStreamWaitEvent(l.stream, ms.last, 0);
+        if (e != cudaSuccess) return e;
+    }
+    if (ms.bytes < need) {
+        if (ms.buf) {   // earlier users were ordered before this point by the event wait, but the free itself is immediate
+            e = cudaEventSynchronize(ms.last);
+            if (e != cudaSuccess) return e;
+            cudaFree(ms.buf);
+            ms.buf = nullptr; ms.bytes = 0;
+        }
+        const size_t alloc = std::max(need, size_t(4) << 20);
+        e = cudaMalloc(&ms.buf, alloc);
+        if (e != cudaSuccess) { ms.buf = nullptr; return e; }
+        ms.bytes = alloc;
+    }
+    e = plan_rows(red, dtin, dtmid, in, ms.buf, R1 * K, R2, row_stride, 1, neutral, l);
+    if (e != cudaSuccess) return e;
+    ColsArgs a{ms.buf, out, 1, R1, K, 0, K, 0, out_stride_k, identity};
+    e = launch_cols(red, dtmid, dtout, a, l);
+    if (e != cudaSuccess) return e;
+    return cudaEventRecord(ms.last, l.stream);
+}
+
 static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, void* out, int ndim,
                                   const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,
                                   uint32_t mask, const void* identity, void* workspace, size_t workspace_bytes,
@@ -160,13 +260,8 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
             return plan_split(red, dtin, dtout, in, out, 1, (size_t)c[0].shape, 0, 0, identity, l);
         // [K, R] with contiguous R -> rows.
         if (nc == 2 && !c[0].reduced && c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
-            const size_t rows = (size_t)c[0].shape, n = (size_t)c[1].shape;
-            const size_t row_bytes = n * esz;
-            if (rows < 2 * (size_t)sm_count() && row_bytes >= (size_t(128) << 10) && rows <= kCounters)
-                return plan_split(red, dtin, dtout, in, out, rows, n, (size_t)c[0].in_stride,
-                                  (ptrdiff_t)c[0].out_stride, identity, l);
-            RowsArgs a{in, out, rows, n, (size_t)c[0].in_stride, (ptrdiff_t)c[0].out_stride, identity};
-            return launch_rows(red, dtin, dtout, a, l);
+            return plan_rows(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[0].in_stride,
+                             (ptrdiff_t)c[0].out_stride, identity, l);
         }
         // [R, K] / [K1, R, K2] with contiguous trailing K -> cols.
         if (nc == 2 && c[0].reduced && !c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
@@ -181,6 +276,15 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
                        (ptrdiff_t)c[0].out_stride, (ptrdiff_t)c[2].out_stride, identity};
             return launch_cols(red, dtin, dtout, a, l);
         }
+    }
+    // [R1, K, R2] with contiguous R2 and dense (R1, K): two streaming passes through a small scratch.
+    if (nr > 0 && nc == 3 && c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 &&
+        c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 32 &&
+        getenv("DACE_B200_NO_TWO_PASS") == nullptr) {
+        cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape,
+                                       (size_t)c[2].shape, (size_t)c[1].in_stride, (ptrdiff_t)c[1].out_stride,
+                                       identity, l);
+        if (e2 != cudaErrorNotSupported) return e2;
     }
     // Everything else: generic strided kernel.
     if (nk > kMaxDims || nr > kMaxDims) return cudaErrorNotSupported;

@@ -49,6 +49,7 @@ constexpr int kMaxBuckets = 64;
 constexpr int kCntSlots = kMaxBuckets + 1;      // + the bucket that collects out-of-range keys
 constexpr size_t kChunkKeysDefault = size_t(1) << 24;  // ~64 MiB of keys per chunk (measured best of 2^22..2^26)
 constexpr size_t kMaxChunks = 4096;
+constexpr int kDivertDefault = 0;             // 1 tile in N straight to global atomics (0 = none)
 constexpr int kPhaseBUnroll = 8;              // 128-bit L2 loads in flight per thread in phase B
 
 template <class V>
@@ -63,7 +64,7 @@ template <class V>
 __global__ void __launch_bounds__(kPartThreads, 1)
 scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict__ bins, unsigned nbins, V cval,
                          unsigned* buf, unsigned* gcur, size_t chunk, unsigned cap, int B, int S, int aligned,
-                         const int* __restrict__ gate) {
+                         const int* __restrict__ gate, int divert) {
     if (*gate != 0) return;   // clustered keys: the global-atomic kernel behind this one does the work (grid-uniform)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     V* hist = reinterpret_cast<V*>(smem_raw);                                  // [kBucketBins]
@@ -118,11 +119,21 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
         const unsigned tstride = gridDim.x * kGroups;
         unsigned t = blockIdx.x * kGroups + g;
         if (t < ntiles) load_tile(t, knext);
-        for (; t < ntiles; t += tstride) {
+        for (unsigned it = g; t < ntiles; t += tstride, ++it) {
             unsigned k[kKeysPerThread], rank[kKeysPerThread];
 #pragma unroll
             for (int j = 0; j < kKeysPerThread; ++j) k[j] = knext[j];
             if (t + tstride < ntiles) load_tile(t + tstride, knext);   // software prefetch of the next tile
+            if (divert && (it % unsigned(divert)) == 0) {
+                // Hybrid: one tile in `divert` bypasses the partition and goes straight to the bins with
+                // RED.global.  The L2 atomic units (~190 G keys/s) are idle otherwise, the shared-memory
+                // pipeline that bounds the rest of this kernel is not touched, and the groups of a CTA
+                // take their turn at different iterations (it starts at g), so the two paths overlap.
+#pragma unroll
+                for (int j = 0; j < kKeysPerThread; ++j)
+                    if (k[j] < nbins) atomicAdd(bins + k[j], cval);
+                continue;
+            }
             // rank inside (tile, bucket); keys >= nbins land in bucket index >= B and are dropped
 #pragma unroll
             for (int j = 0; j < kKeysPerThread; ++j)
@@ -358,7 +369,9 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Laun
     unsigned cap_arg = cap;
     int B_arg = B, S_arg = S;
     int aligned = (reinterpret_cast<size_t>(a.idx) & 15) == 0;
-    void* args[] = {&keys, &n, &bins, &nbins, &cval, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate};
+    int divert = kDivertDefault;
+    if (const char* ev = getenv("DACE_B200_PART_DIVERT")) divert = std::max(0, atoi(ev));   // tuning knob (0 = off)
+    void* args[] = {&keys, &n, &bins, &nbins, &cval, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert};
     e = cudaLaunchCooperativeKernel((void*)kern, dim3(sms), dim3(kPartThreads), args, smem, l.stream);
     if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }
     return cudaSuccess;   // the event is recorded by scatter_partition_done(), after the gated global kernel

@@ -375,3 +375,67 @@ def test_cols_wide_rows_bf16_and_2d(cuda):
     assert bool(((got.double() - ref).abs() <= 1e-5 * x.double().abs().sum(0)).all())
     gmax = db.reduce('lambda a, b: max(a, b)', x, axis=(0, ), identity=-3e38)
     assert torch.equal(gmax.float(), x.float().max(0).values)
+
+
+# ---- [R1, K, R2] with contiguous R2: two streaming passes (rows -> scratch -> cols), api.cu plan_two_pass ----
+
+@pytest.mark.parametrize('dtype', [np.float32, np.float64, np.int32, np.int64, np.uint32, np.uint64, np.int8])
+@pytest.mark.parametrize('op', ['sum', 'max', 'min', 'prod'])
+@pytest.mark.parametrize('shape', [[6, 50, 64], [33, 7, 1000], [3, 300, 32], [2, 5, 40000]])
+def test_outer_inner_axes_two_pass(dtype, op, shape, cuda):
+    """Per-channel statistics layout (axes (0, 2) of [N, C, H*W]); int8 has no two-pass plan and must
+    still be right through the generic kernel."""
+    rng = np.random.default_rng(3)
+    a = _data(rng, shape, dtype, op)
+    got, ref = _run(a, (0, 2), op, cuda)
+    _check(got, ref, dtype, a, (0, 2), op)
+    if op in ('sum', 'max'):                       # identity None: fold into what the output holds
+        init = _data(rng, [shape[1]], dtype, op)
+        got, ref = _run(a, (0, 2), op, cuda, identity=None, out_init=init)
+        _check(got, ref, dtype, a, (0, 2), op)
+
+
+def test_two_pass_bitwise_views_and_bf16(cuda):
+    rng = np.random.default_rng(4)
+    a = rng.integers(0, 2**31 - 1, (9, 40, 77)).astype(np.int32)
+    for op, ident in (('band', -1), ('bor', 0), ('bxor', 0)):
+        got, ref = _run(a, (0, 2), op, cuda, identity=ident)
+        np.testing.assert_array_equal(got, ref)
+    # merged kept dims / 4-D: [N, C1, C2, HW] over (0, 3) canonicalises to [R1, K, R2]
+    b = rng.random((5, 4, 6, 130)).astype(np.float32)
+    got, ref = _run(b, (0, 3), 'sum', cuda)
+    _check(got, ref, np.float32, b, (0, 3))
+    # padded rows (row stride > R2) still qualify; a transposed outer pair does not (generic kernel) - same numbers
+    big = torch.from_numpy(rng.random((7, 12, 200)).astype(np.float32)).to(cuda)
+    view = big[:, :, :150]
+    got = db.reduce('lambda a, b: a + b', view, axis=(0, 2), identity=0).cpu().numpy()
+    np.testing.assert_allclose(got, view.cpu().numpy().astype(np.float64).sum((0, 2)), rtol=1e-5)
+    tr = big.permute(1, 0, 2)                      # [12, 7, 200] with swapped strides, reduce (0, 2)
+    got = db.reduce('lambda a, b: a + b', tr, axis=(0, 2), identity=0).cpu().numpy()
+    np.testing.assert_allclose(got, tr.cpu().numpy().astype(np.float64).sum((0, 2)), rtol=1e-5)
+    # bf16 -> f32 output: fp32 scratch between the passes
+    x = torch.randn(16, 24, 512, device=cuda).to(torch.bfloat16)
+    out = torch.zeros(24, dtype=torch.float32, device=cuda)
+    db.reduce('lambda a, b: a + b', x, out, axis=(0, 2), identity=0)
+    ref = x.double().sum((0, 2)).cpu().numpy()
+    scale = x.double().abs().sum((0, 2)).cpu().numpy()
+    assert np.all(np.abs(out.cpu().numpy() - ref) <= 1e-5 * scale)
+    mx = torch.zeros(24, dtype=torch.float32, device=cuda)
+    db.reduce('lambda a, b: max(a, b)', x, mx, axis=(0, 2), identity=-3e38)
+    assert torch.equal(mx, x.float().amax((0, 2)))
+
+
+def test_two_pass_two_streams_share_the_scratch(cuda):
+    rng = np.random.default_rng(5)
+    a = torch.from_numpy(rng.integers(-100, 100, (40, 300, 500)).astype(np.int32)).to(cuda)
+    b = torch.from_numpy(rng.integers(-100, 100, (10, 2000, 64)).astype(np.int32)).to(cuda)
+    oa, ob = torch.zeros(300, dtype=torch.int32, device=cuda), torch.zeros(2000, dtype=torch.int32, device=cuda)
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    torch.cuda.synchronize()
+    for _ in range(5):
+        with torch.cuda.stream(s1):
+            db.reduce('lambda a, b: a + b', a, oa, axis=(0, 2), identity=0)
+        with torch.cuda.stream(s2):
+            db.reduce('lambda a, b: a + b', b, ob, axis=(0, 2), identity=0)
+    torch.cuda.synchronize()
+    assert torch.equal(oa, a.sum((0, 2)).to(torch.int32)) and torch.equal(ob, b.sum((0, 2)).to(torch.int32))
