@@ -225,18 +225,28 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
     if (!out || (nred != 0 && !in)) return cudaErrorInvalidValue;  // empty tensors may carry null pointers
 
     // Canonicalise: drop unit dims, merge mergeable neighbours of the same kind.
+    // A fold does not care in which order the axes are walked and every kept axis carries its own
+    // output stride, so the axes are first put in memory order (largest input stride first, stable):
+    // transposed / permuted views (np.sum(A.T, axis=1), channels-last tensors) then canonicalise to
+    // the same [K, R] / [R, K] / [R1, K, R2] forms as their plain counterparts instead of falling
+    // through to the strided kernel.
+    Dim nz[DACE_B200_MAX_DIMS];
+    int nnz = 0;
+    for (int i = 0; i < ndim; ++i)
+        if (dims[i].shape != 1) nz[nnz++] = dims[i];
+    if (getenv("DACE_B200_NO_AXIS_SORT") == nullptr)
+        std::stable_sort(nz, nz + nnz, [](const Dim& a, const Dim& b) { return a.in_stride > b.in_stride; });
     Dim c[DACE_B200_MAX_DIMS];
     int nc = 0;
-    for (int i = 0; i < ndim; ++i) {
-        if (dims[i].shape == 1) continue;
-        if (nc > 0 && c[nc - 1].reduced == dims[i].reduced &&
-            c[nc - 1].in_stride == dims[i].in_stride * dims[i].shape &&
-            (dims[i].reduced || c[nc - 1].out_stride == dims[i].out_stride * dims[i].shape)) {
-            c[nc - 1].shape *= dims[i].shape;
-            c[nc - 1].in_stride = dims[i].in_stride;
-            c[nc - 1].out_stride = dims[i].out_stride;
+    for (int i = 0; i < nnz; ++i) {
+        if (nc > 0 && c[nc - 1].reduced == nz[i].reduced &&
+            c[nc - 1].in_stride == nz[i].in_stride * nz[i].shape &&
+            (nz[i].reduced || c[nc - 1].out_stride == nz[i].out_stride * nz[i].shape)) {
+            c[nc - 1].shape *= nz[i].shape;
+            c[nc - 1].in_stride = nz[i].in_stride;
+            c[nc - 1].out_stride = nz[i].out_stride;
         } else {
-            c[nc++] = dims[i];
+            c[nc++] = nz[i];
         }
     }
 

@@ -439,3 +439,31 @@ def test_two_pass_two_streams_share_the_scratch(cuda):
             db.reduce('lambda a, b: a + b', b, ob, axis=(0, 2), identity=0)
     torch.cuda.synchronize()
     assert torch.equal(oa, a.sum((0, 2)).to(torch.int32)) and torch.equal(ob, b.sum((0, 2)).to(torch.int32))
+
+
+# ---- permuted / transposed views: axes are put in memory order before a kernel is picked ----
+
+@pytest.mark.parametrize('dtype', [np.float32, np.int64])
+@pytest.mark.parametrize('perm,axes', [((1, 0), (1, )), ((1, 0), (0, )), ((2, 0, 1), (0, )), ((2, 0, 1), (1, 2)),
+                                       ((0, 2, 1), (1, )), ((0, 3, 1, 2), (0, 2, 3)), ((0, 3, 1, 2), (1, )),
+                                       ((3, 2, 1, 0), (0, 2)), ((1, 0, 2), None)])
+def test_permuted_views_match_the_contiguous_result(dtype, perm, axes, cuda):
+    """np.sum(A.T, axis=1), channels-last tensors reduced over (N, H, W), arbitrary permutations: the view is
+    passed as it is (strides, no copy); results must equal the reduction of a contiguous copy."""
+    rng = np.random.default_rng(6)
+    base_shape = [37, 41, 130, 9][:len(perm)] if len(perm) < 4 else [6, 37, 41, 130]
+    base = rng.integers(-50, 50, base_shape).astype(dtype) if dtype == np.int64 else rng.random(base_shape).astype(dtype)
+    view = torch.from_numpy(base).to(cuda).permute(*perm)
+    assert not view.is_contiguous()
+    host = np.ascontiguousarray(np.transpose(base, perm))
+    for op in ('sum', 'max'):
+        red, lam, _ = _OPS[op]
+        ident = _identity(op, np.dtype(dtype))
+        got = db.reduce(lam, view, axis=axes, identity=ident).cpu().numpy()
+        ref = O.reduce(red, host, axes, identity=ident, wide=True)
+        _check(got, ref, dtype, host, axes, op)
+    # strided output view as well (transposed destination)
+    if axes == (1, ) and len(perm) == 3:
+        out = torch.zeros(host.shape[2], host.shape[0], dtype=view.dtype, device=cuda).t()
+        db.reduce('lambda a, b: a + b', view, out, axis=axes, identity=0)
+        _check(out.cpu().numpy(), O.reduce(O.SUM, host, axes, identity=0, wide=True), dtype, host, axes, 'sum')
