@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 7
+VERSION = 8
 
 
 def up_to_date() -> bool:
@@ -221,6 +221,32 @@ def _programs(dace):
     if counts != {'reduce': 2, 'scatter': 1, 'local': 1}:
         raise RuntimeError('b200_sharded: unexpected sharding result %s' % counts)
     progs.append(sdfg)
+
+    # (9) np.argmax / np.argmin: the frontend's struct-WCR map -> ArgReduce library node -> dace_b200_reduce_arg
+    #     (dace_b200/arg_node.py).  The flat form (axis=None) does not survive the reference's own
+    #     apply_gpu_transformations (host interstate edge reading device data), so it is not built here.
+    from dace_b200 import arg_node as AN
+    K = dace.symbol('K', dace.int64)
+
+    @dace.program
+    def b200_argmax_f32_axis1(A: dace.float32[N, M], out: dace.int32[N]):
+        out[:] = np.argmax(A, axis=1)
+
+    @dace.program
+    def b200_argmin_f64_axis0(A: dace.float64[N, M], out: dace.int32[M]):
+        out[:] = np.argmin(A, axis=0)
+
+    @dace.program
+    def b200_argmin_i32_mid(A: dace.int32[N, M, K], out: dace.int32[N, K]):
+        out[:] = np.argmin(A, axis=1)
+
+    for j, p in enumerate((b200_argmax_f32_axis1, b200_argmin_f64_axis0, b200_argmin_i32_mid)):
+        sdfg = _to_sdfg(p, simplify=True)
+        sdfg.apply_gpu_transformations()
+        applied = AN.use_b200_argreduce(sdfg) if j < 2 else AUTO.apply_b200(sdfg)['arg']
+        if applied != 1:
+            raise RuntimeError('%s: ArgReduceMapToLibrary applied %d times' % (sdfg.name, applied))
+        progs.append(sdfg)
     return progs
 
 
@@ -297,7 +323,7 @@ def build_all(verbose=True, only=None):
             manifest['programs'][name] = {
                 'lib': lib, 'args': args,
                 'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
-                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') +
+                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') + src.count('dace_b200_reduce_arg(') +
                 cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
                 'comm_calls': src.count('dace_b200_comm_allreduce('),
             }

@@ -252,3 +252,28 @@ def test_sharded_program_single_rank(cuda):
     p(A=neg, keys=keys, cs=cs, tot=tot, rs=rs, bins=bins, N=777, M=300)
     assert tot[0] == np.float32(0.25)                 # the identity, folded once
     np.testing.assert_array_equal(bins, 7 + 2 * np.bincount(keys, minlength=300).astype(np.int32))
+
+
+# ---- np.argmax / np.argmin in @dace.programs: struct-WCR map -> ArgReduce -> dace_b200_reduce_arg ----
+
+def test_np_argmax_argmin_dace_programs(cuda):
+    rng = np.random.default_rng(31)
+    a = rng.standard_normal((513, 2050)).astype(np.float32)
+    out = np.full(513, -5, np.int32)
+    prog('b200_argmax_f32_axis1')(A=a, out=out, N=513, M=2050)
+    np.testing.assert_array_equal(out, np.argmax(a, axis=1))
+    ridx, _ = O.reduce_arg(O.MAX_LOCATION, a, 1)
+    np.testing.assert_array_equal(out, ridx)
+    t = rng.integers(0, 4, (300, 700)).astype(np.float64)          # many ties: the first occurrence wins
+    out0 = np.zeros(700, np.int32)
+    prog('b200_argmin_f64_axis0')(A=t, out=out0, N=300, M=700)
+    np.testing.assert_array_equal(out0, np.argmin(t, axis=0))
+    m = rng.integers(-9, 9, (33, 1000, 17)).astype(np.int32)
+    outm = np.zeros((33, 17), np.int32)
+    prog('b200_argmin_i32_mid')(A=m, out=outm, N=33, M=1000, K=17)
+    np.testing.assert_array_equal(outm, np.argmin(m, axis=1))
+    # one long row: the split-row kernel (cross-CTA combine of (val, idx) pairs)
+    big = rng.standard_normal((3, 1 << 21)).astype(np.float32)
+    outb = np.zeros(3, np.int32)
+    prog('b200_argmax_f32_axis1')(A=big, out=outb, N=3, M=1 << 21)
+    np.testing.assert_array_equal(outb, np.argmax(big, axis=1))
