@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 8
+VERSION = 9
 
 
 def up_to_date() -> bool:
@@ -247,6 +247,40 @@ def _programs(dace):
         if applied != 1:
             raise RuntimeError('%s: ArgReduceMapToLibrary applied %d times' % (sdfg.name, applied))
         progs.append(sdfg)
+
+    # (10) Row max + row sum of one array (BASELINE C3): the two Reduce nodes are fused into one RowsMaxSum
+    #      node = one pass over the input (dace_b200/fuse_node.py).  f32 from an unmodified @dace.program;
+    #      bf16 -> fp32 outputs needs hand-built nodes (the frontend keeps the input dtype), device-resident.
+    from dace_b200 import fuse_node as FN
+
+    @dace.program
+    def b200_softmax_stats_fused(A: dace.float32[N, M], mx_out: dace.float32[N], sm_out: dace.float32[N]):
+        mx_out[:] = np.max(A, axis=1)
+        sm_out[:] = np.sum(A, axis=1)
+
+    sdfg = _to_sdfg(b200_softmax_stats_fused, simplify=True)
+    sdfg.apply_gpu_transformations()
+    AUTO.apply_b200(sdfg)
+    if FN.fuse_row_max_sum(sdfg) != 1:
+        raise RuntimeError('b200_softmax_stats_fused: the Reduce pair was not fused')
+    progs.append(sdfg)
+
+    sdfg = dace.SDFG('b200_c3_fused_bf16')
+    G = dace.StorageType.GPU_Global
+    sdfg.add_array('A', [N, M], bf16, storage=G)
+    sdfg.add_array('mx', [N], f32, storage=G)
+    sdfg.add_array('sm', [N], f32, storage=G)
+    st = sdfg.add_state()
+    a = st.add_read('A')
+    r1 = st.add_reduce(mx, [1], -fmax)
+    r2 = st.add_reduce(add, [1], 0)
+    st.add_nedge(a, r1, dace.Memlet.from_array('A', sdfg.arrays['A']))
+    st.add_nedge(a, r2, dace.Memlet.from_array('A', sdfg.arrays['A']))
+    st.add_nedge(r1, st.add_write('mx'), dace.Memlet.from_array('mx', sdfg.arrays['mx']))
+    st.add_nedge(r2, st.add_write('sm'), dace.Memlet.from_array('sm', sdfg.arrays['sm']))
+    if FN.fuse_row_max_sum(sdfg) != 1:
+        raise RuntimeError('b200_c3_fused_bf16: the Reduce pair was not fused')
+    progs.append(sdfg)
     return progs
 
 
@@ -323,7 +357,7 @@ def build_all(verbose=True, only=None):
             manifest['programs'][name] = {
                 'lib': lib, 'args': args,
                 'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
-                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') + src.count('dace_b200_reduce_arg(') +
+                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') + src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') +
                 cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
                 'comm_calls': src.count('dace_b200_comm_allreduce('),
             }

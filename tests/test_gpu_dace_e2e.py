@@ -277,3 +277,31 @@ def test_np_argmax_argmin_dace_programs(cuda):
     outb = np.zeros(3, np.int32)
     prog('b200_argmax_f32_axis1')(A=big, out=outb, N=3, M=1 << 21)
     np.testing.assert_array_equal(outb, np.argmax(big, axis=1))
+
+
+# ---- row max + row sum fused into one pass (dace_b200/fuse_node.py -> dace_b200_reduce_rows_max_sum) ----
+
+def test_fused_row_max_sum_programs(cuda):
+    import torch
+    m = ref_loader.manifest(BUILT)['programs']
+    assert m['b200_softmax_stats_fused']['b200_calls'] == 1       # one library call where the unfused program has two
+    assert m['b200_softmax_stats']['b200_calls'] == 2
+    a = np.random.default_rng(41).standard_normal((513, 2050)).astype(np.float32)
+    mx, sm = np.zeros(513, np.float32), np.zeros(513, np.float32)
+    prog('b200_softmax_stats_fused')(A=a, mx_out=mx, sm_out=sm, N=513, M=2050)
+    np.testing.assert_array_equal(mx, a.max(1))
+    np.testing.assert_array_equal(mx, O.reduce(O.MAX, a, (1, ), identity=-3.4e38))
+    assert close_f32(sm, a.astype(np.float64).sum(1), a, (1, ))
+    # BASELINE C3 layout, device-resident bf16 in, fp32 out (scaled down): hand-built Reduce pair, fused
+    x = torch.randn(4096, 8192, device=cuda).to(torch.bfloat16)
+    tmx = torch.zeros(4096, dtype=torch.float32, device=cuda)
+    tsm = torch.zeros(4096, dtype=torch.float32, device=cuda)
+    torch.cuda.synchronize()
+    prog('b200_c3_fused_bf16')(A=x.data_ptr(), mx=tmx.data_ptr(), sm=tsm.data_ptr(), N=4096, M=8192)
+    torch.cuda.synchronize()
+    bits = x.view(torch.int16).cpu().numpy().view(np.uint16)
+    np.testing.assert_array_equal(tmx.cpu().numpy(), O.reduce(O.MAX, bits, (1, ), identity=-3e38, in_bf16=True,
+                                                              out_dtype=np.float32))
+    ref = x.double().sum(1).cpu().numpy()
+    scale = x.double().abs().sum(1).cpu().numpy()
+    assert np.all(np.abs(tsm.cpu().numpy() - ref) <= 1e-5 * scale)
