@@ -59,8 +59,32 @@ def scalar_bytes(value, dt: int) -> bytes:
     return npdt(value).tobytes()
 
 
+_raw_stream = getattr(torch._C, '_cuda_getCurrentRawStream', None)
+
+
+class _on_device:
+    """``with torch.cuda.device(d)`` only when ``d`` is not already current: the context manager costs
+    several microseconds per call, which is the size of a small reduction."""
+    __slots__ = ('ctx', )
+
+    def __init__(self, device):
+        self.ctx = None if device.index is None or device.index == torch.cuda.current_device() \
+            else torch.cuda.device(device)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            return self.ctx.__exit__(*exc)
+        return False
+
+
 def _stream_ptr(stream) -> int:
     if stream is None:
+        if _raw_stream is not None:
+            return _raw_stream(torch.cuda.current_device())
         return torch.cuda.current_stream().cuda_stream
     if isinstance(stream, int):
         return stream
@@ -154,7 +178,7 @@ def reduce(op, in_array: torch.Tensor, out_array: Optional[torch.Tensor] = None,
     if identity is not None:
         ident_buf = ctypes.create_string_buffer(scalar_bytes(identity, dt_out), 8)
     ws_ptr, ws_bytes = (workspace.ptr, workspace.nbytes) if workspace is not None else (None, 0)
-    with torch.cuda.device(in_array.device):
+    with _on_device(in_array.device):
         status = lib.dace_b200_reduce_nd(int(rt), dt_in, dt_out, in_array.data_ptr(), out_array.data_ptr(), nd,
                                          shape, istr, ostr, mask, ident_buf, ws_ptr, ws_bytes, _stream_ptr(stream))
     _lib.check(status, 'dace_b200_reduce_nd')
@@ -177,7 +201,7 @@ def rows_max_sum(in_array: torch.Tensor, out_max: Optional[torch.Tensor] = None,
         _require_cuda(o, 'output')
         if o.dtype != torch.float32 or not o.is_contiguous() or o.numel() != rows:
             raise ValueError('outputs must be contiguous float32[rows]')
-    with torch.cuda.device(in_array.device):
+    with _on_device(in_array.device):
         status = lib.dace_b200_reduce_rows_max_sum(dtype_code(in_array.dtype), in_array.data_ptr(),
                                                    out_max.data_ptr(), out_sum.data_ptr(), rows, n,
                                                    in_array.stride(0), _stream_ptr(stream))
@@ -234,7 +258,7 @@ def _arg_reduce(red: int, in_array: torch.Tensor, axis, out_idx, out_val, init, 
                 (0 if red == int(ReductionType.Max_Location) else 1)
     ibuf = ctypes.create_string_buffer(scalar_bytes(init, dt_in), 8) if init is not None else None
     ws_ptr, ws_bytes = (workspace.ptr, workspace.nbytes) if workspace is not None else (None, 0)
-    with torch.cuda.device(a.device):
+    with _on_device(a.device):
         status = lib.dace_b200_reduce_arg(red, dt_in, dtype_code(out_idx.dtype), a.data_ptr(), out_idx.data_ptr(),
                                           out_val.data_ptr() if out_val is not None else None, outer, reduced, inner,
                                           so, sr, si, 0, 0, ibuf, ws_ptr, ws_bytes, _stream_ptr(stream))
@@ -283,7 +307,7 @@ def wcr_scatter(op, bins: torch.Tensor, indices: torch.Tensor, values=None, stre
         vptr = values.data_ptr()
     elif values is not None:
         cbuf = ctypes.create_string_buffer(scalar_bytes(values, dt_val), 8)
-    with torch.cuda.device(bins.device):
+    with _on_device(bins.device):
         status = lib.dace_b200_wcr_scatter(int(rt), dt_idx, dt_val, indices.data_ptr(), vptr, cbuf,
                                            indices.numel(), bins.data_ptr(), bins.numel(), _stream_ptr(stream))
     _lib.check(status, 'dace_b200_wcr_scatter')

@@ -210,3 +210,58 @@ def test_native_communicator_and_sharded_dace_program(tmp_path, isolate, no_peer
                        env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert r.stdout.count('ok') == n
+
+
+# ---- the same DaCe-built program under dace_b200.launch: no torch in the worker, NCCL found by dlopen ----
+
+LAUNCH_WORKER = r'''
+import ctypes, os, sys, numpy as np
+sys.path.insert(0, os.environ["REPO_ROOT"])
+from dace_b200 import _lib
+from oracle import ref_loader
+assert "torch" not in sys.modules
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+assert os.environ["CUDA_VISIBLE_DEVICES"] == str(rank)
+built = os.path.join(os.environ["REPO_ROOT"], "tests", "dace_e2e", "_built")
+rng = np.random.default_rng(9)
+R, M = 3000 * world + 1, 256
+full = rng.standard_normal((R, M)).astype(np.float32)
+keys = rng.integers(0, M, R).astype(np.int32)
+lo, hi = (R * rank) // world, (R * (rank + 1)) // world
+a, k = np.ascontiguousarray(full[lo:hi]), np.ascontiguousarray(keys[lo:hi])
+cs, tot, rs = np.zeros(M, np.float32), np.zeros(1, np.float32), np.zeros(hi - lo, np.float32)
+bins = np.zeros(M, np.int32)
+p = ref_loader.RefProgram("b200_sharded", built)
+p(A=a, keys=k, cs=cs, tot=tot, rs=rs, bins=bins, N=hi - lo, M=M)
+scale = np.abs(full.astype(np.float64)).sum(0)
+assert np.all(np.abs(cs - full.astype(np.float64).sum(0)) <= 1e-5 * scale)
+assert tot[0] == max(full.max(), np.float32(0.25))
+assert np.array_equal(bins, np.bincount(keys, minlength=M))
+assert np.allclose(rs, a.astype(np.float64).sum(1), rtol=1e-5, atol=1e-4)
+lib = _lib.load()
+c = ctypes.c_void_p()
+_lib.check(lib.dace_b200_comm_default(ctypes.byref(c)), "comm_default")
+assert lib.dace_b200_comm_world(c) == world and lib.dace_b200_comm_rank(c) == rank
+sys.stdout.write("rank %d ok peer=%d\n" % (rank, lib.dace_b200_comm_uses_peer_memory(c)))   # one write: ranks share the pipe
+sys.stdout.flush()
+del p
+lib.dace_b200_comm_destroy(c)
+'''
+
+
+def test_launcher_runs_the_sharded_dace_program(tmp_path):
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip('needs >= 2 GPUs')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.exists(os.path.join(root, 'tests', 'dace_e2e', '_built', 'libb200_sharded.so')):
+        pytest.skip('tests/dace_e2e/_built not present')
+    n = min(n, 4)
+    script = tmp_path / 'launch_worker.py'
+    script.write_text(LAUNCH_WORKER)
+    env = dict(os.environ, REPO_ROOT=root, DACE_B200_DEBUG='1')
+    env.pop('CUDA_VISIBLE_DEVICES', None)
+    r = subprocess.run([sys.executable, '-m', 'dace_b200.launch', '--nproc', str(n), '--timeout', '300', str(script)],
+                       env=env, cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert r.stdout.count('ok peer=') == n, r.stdout
