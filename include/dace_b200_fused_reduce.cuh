@@ -1,0 +1,201 @@
+/* dace_b200_fused_reduce.cuh - map -> reduce in ONE kernel, for DaCe-generated programs on sm_100.
+ *
+ * A DaCe program such as `s[:] = np.sum(np.exp(A - mx[:, None]), axis=1)` is a Map that writes a
+ * transient, followed by a Reduce node that reads it back: three passes over HBM (read A, write
+ * T, read T).  The reference's answer is MapReduceFusion (reference
+ * dace/transformation/dataflow/mapreduce.py:18-146), which turns the pair into a WCR map - one
+ * atomic per element on a GPU (reference dace/codegen/targets/cpu.py:965-1013).  Here the
+ * `FuseMapIntoReduce` rewrite (dace_b200/fused_expansion.py) generates a LOAD FUNCTOR from the
+ * map's tasklet and instantiates the streaming kernels below with it inside the program's own
+ * .cu file: the elementwise producer runs in registers, the transient never exists, one pass.
+ *
+ * Like dace_b200_block_reduce.cuh this part of the boundary is a device header (the functor is
+ * generated code, so it cannot sit behind a precompiled C ABI) - the same mechanism by which the
+ * reference's CUB expansion instantiates cub::DeviceReduce with a generated functor (reference
+ * dace/libraries/standard/nodes/reduce.py:453-463,574-588).
+ *
+ *   out[r * out_stride] = fold(op, identity, load(r, 0), ..., load(r, n - 1))      r in [0, rows)
+ *
+ * `load(row, col)` is any device functor returning a value convertible to the accumulator A.
+ * Lanes walk `col`, so a functor that reads x[row * ld + col] is coalesced.  Long rows are split
+ * over several CTAs; the per-split partials go through the caller's workspace (the partials area
+ * of the dace_b200 workspace, see dace_b200_reduce.h) and a second tiny kernel folds them in index
+ * order: deterministic results, no atomics.  `identity == nullptr` folds into the value already in
+ * `out` (reference dace/frontend/operations.py:251).
+ */
+#ifndef DACE_B200_FUSED_REDUCE_CUH
+#define DACE_B200_FUSED_REDUCE_CUH
+
+#if defined(__CUDACC__)
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "dace_b200_block_reduce.cuh"
+
+namespace dace_b200 {
+
+/* Neutral element of the built-in operators (seed of every thread's private accumulator). */
+template <int RED, typename A>
+__host__ __device__ __forceinline__ A neutral() {
+    if constexpr (RED == kSum || RED == kBitwiseOr || RED == kBitwiseXor || RED == kLogicalOr || RED == kLogicalXor)
+        return A(0);
+    else if constexpr (RED == kProduct || RED == kLogicalAnd) return A(1);
+    else if constexpr (RED == kBitwiseAnd) return (A)(~A(0));
+    else if constexpr (RED == kMin) {
+        if constexpr (sizeof(A) == 4 && A(0.5) != A(0)) { const uint32_t b = 0x7f800000u; A r; __builtin_memcpy(&r, &b, 4); return r; }
+        else if constexpr (sizeof(A) == 8 && A(0.5) != A(0)) { const uint64_t b = 0x7ff0000000000000ull; A r; __builtin_memcpy(&r, &b, 8); return r; }
+        else if constexpr (A(-1) < A(0)) return (A)((~(unsigned long long)0) >> (65 - 8 * sizeof(A)));
+        else return (A)(~A(0));
+    } else {  /* kMax */
+        if constexpr (sizeof(A) == 4 && A(0.5) != A(0)) { const uint32_t b = 0xff800000u; A r; __builtin_memcpy(&r, &b, 4); return r; }
+        else if constexpr (sizeof(A) == 8 && A(0.5) != A(0)) { const uint64_t b = 0xfff0000000000000ull; A r; __builtin_memcpy(&r, &b, 8); return r; }
+        else if constexpr (A(-1) < A(0)) return (A)(-(A)((~(unsigned long long)0) >> (65 - 8 * sizeof(A))) - 1);
+        else return A(0);
+    }
+}
+
+namespace detail {
+
+constexpr int kFusedThreads = 256;
+constexpr int kFusedUnroll = 4;
+
+template <int RED, typename A, typename S>
+__device__ __forceinline__ void fused_store(S* out, A v, A identity, int has_identity) {
+    const A base = has_identity ? identity : (A)(*out);
+    *out = (S)op<RED, A>()(base, v);
+}
+
+/* One CTA per (row, split): threads stride the columns of the split with kFusedUnroll independent
+ * accumulators (that many loads in flight per thread), then a block tree. */
+template <int RED, typename A, typename S, typename Load>
+__global__ void __launch_bounds__(kFusedThreads)
+fused_rows_cta_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t n, unsigned splits,
+                      A* __restrict__ partials, A identity, int has_identity) {
+    const size_t row = blockIdx.y;
+    const unsigned split = blockIdx.x;
+    const size_t seg = (n + splits - 1) / splits;
+    const size_t lo = size_t(split) * seg;
+    const size_t hi = (lo + seg < n) ? lo + seg : n;
+    const op<RED, A> f;
+    A acc[kFusedUnroll];
+#pragma unroll
+    for (int u = 0; u < kFusedUnroll; ++u) acc[u] = neutral<RED, A>();
+    size_t j = lo + threadIdx.x;
+    for (; j + size_t(kFusedUnroll - 1) * kFusedThreads < hi; j += size_t(kFusedUnroll) * kFusedThreads) {
+        A v[kFusedUnroll];
+#pragma unroll
+        for (int u = 0; u < kFusedUnroll; ++u) v[u] = (A)load(row, j + size_t(u) * kFusedThreads);
+#pragma unroll
+        for (int u = 0; u < kFusedUnroll; ++u) acc[u] = f(acc[u], v[u]);
+    }
+    for (; j < hi; j += kFusedThreads) acc[0] = f(acc[0], (A)load(row, j));
+    A r = block_reduce<A, kFusedThreads, 0x7f01>(acc, f);
+    if (threadIdx.x == 0) {
+        if (splits == 1) fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
+        else partials[row * splits + split] = r;
+    }
+}
+
+/* Short rows: one warp per row. */
+template <int RED, typename A, typename S, typename Load>
+__global__ void __launch_bounds__(kFusedThreads)
+fused_rows_warp_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, A identity,
+                       int has_identity) {
+    const unsigned lane = threadIdx.x & 31;
+    const size_t warps_per_grid = size_t(gridDim.x) * (kFusedThreads / 32);
+    const op<RED, A> f;
+    for (size_t row = size_t(blockIdx.x) * (kFusedThreads / 32) + (threadIdx.x >> 5); row < rows; row += warps_per_grid) {
+        A a0 = neutral<RED, A>(), a1 = neutral<RED, A>();
+        size_t j = lane;
+        for (; j + 32 < n; j += 64) {
+            const A v0 = (A)load(row, j), v1 = (A)load(row, j + 32);
+            a0 = f(a0, v0);
+            a1 = f(a1, v1);
+        }
+        if (j < n) a0 = f(a0, (A)load(row, j));
+        const A r = warp_allreduce(f(a0, a1), f);
+        if (lane == 0) fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
+    }
+}
+
+template <int RED, typename A, typename S>
+__global__ void fused_finish_kernel(const A* __restrict__ partials, S* __restrict__ out, ptrdiff_t out_stride, size_t rows,
+                                    unsigned splits, A identity, int has_identity) {
+    const size_t row = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (row >= rows) return;
+    const op<RED, A> f;
+    A r = partials[row * splits];
+    for (unsigned s = 1; s < splits; ++s) r = f(r, partials[row * splits + s]);   /* fixed order */
+    fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
+}
+
+inline int fused_sm_count() {
+    static int cached = 0;
+    if (cached == 0) {
+        int dev = 0, n = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        cached = n;
+    }
+    return cached;
+}
+
+}  // namespace detail
+
+/* Bytes at the start of the dace_b200 workspace that belong to the library's ticket counters
+ * (dace_b200/csrc/common.cuh kCounterBytes); the partials area behind them is free between calls. */
+constexpr size_t kWorkspaceCounterBytes = 16384;
+
+/* Host launcher.  `identity` is a HOST pointer (or nullptr: fold into `out`).  `workspace` /
+ * `workspace_bytes`: the program's dace_b200 workspace; only needed when rows are split. */
+template <int RED, typename A, typename S, typename Load>
+inline cudaError_t fused_rows(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, const A* identity,
+                              void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    using namespace detail;
+    if (rows == 0) return cudaSuccess;
+    const A ident = identity ? *identity : A(0);
+    const int has = identity ? 1 : 0;
+    const size_t sms = (size_t)fused_sm_count();
+    if (n < 2048 && rows >= 2 * sms) {
+        size_t grid = (rows + kFusedThreads / 32 - 1) / (kFusedThreads / 32);
+        if (grid > sms * 8) grid = sms * 8;
+        fused_rows_warp_kernel<RED, A, S, Load><<<(unsigned)grid, kFusedThreads, 0, stream>>>(load, out, out_stride, rows, n,
+                                                                                          ident, has);
+        return cudaGetLastError();
+    }
+    /* CTA per (row, split): aim at >= 4 CTAs per SM, at least 4096 elements per split */
+    size_t splits = 1;
+    if (rows < 4 * sms) {
+        splits = (4 * sms + rows - 1) / rows;
+        const size_t max_by_len = (n + 4095) / 4096;
+        if (splits > max_by_len) splits = max_by_len;
+        if (splits < 1) splits = 1;
+    }
+    A* partials = nullptr;
+    if (splits > 1) {
+        const size_t need = kWorkspaceCounterBytes + rows * splits * sizeof(A);
+        if (workspace == nullptr || workspace_bytes < need) splits = 1;   /* still correct, just fewer CTAs */
+        else partials = reinterpret_cast<A*>(static_cast<char*>(workspace) + kWorkspaceCounterBytes);
+    }
+    if (rows > 65535) {   /* gridDim.y limit: fall back to the warp kernel's row loop */
+        size_t grid = sms * 8;
+        fused_rows_warp_kernel<RED, A, S, Load><<<(unsigned)grid, kFusedThreads, 0, stream>>>(load, out, out_stride, rows, n,
+                                                                                          ident, has);
+        return cudaGetLastError();
+    }
+    fused_rows_cta_kernel<RED, A, S, Load><<<dim3((unsigned)splits, (unsigned)rows), kFusedThreads, 0, stream>>>(
+        load, out, out_stride, n, (unsigned)splits, partials, ident, has);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess || splits == 1) return e;
+    fused_finish_kernel<RED, A, S><<<(unsigned)((rows + 127) / 128), 128, 0, stream>>>(partials, out, out_stride, rows,
+                                                                                    (unsigned)splits, ident, has);
+    return cudaGetLastError();
+}
+
+}  // namespace dace_b200
+
+#endif /* __CUDACC__ */
+#endif /* DACE_B200_FUSED_REDUCE_CUH */

@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 9
+VERSION = 10
 
 
 def up_to_date() -> bool:
@@ -281,6 +281,32 @@ def _programs(dace):
     if FN.fuse_row_max_sum(sdfg) != 1:
         raise RuntimeError('b200_c3_fused_bf16: the Reduce pair was not fused')
     progs.append(sdfg)
+
+    # (11) The other frontend producers of Reduce nodes (reference replacements/reduction.py:102-146):
+    #      np.any / np.all (logical WCRs; np.all carries identity 0 in the reference, so it is all-false -
+    #      a quirk parity has to keep), np.mean (sum + elementwise divide), np.min with `initial`.
+    E.Reduce.default_implementation = 'B200'
+    try:
+        @dace.program
+        def b200_np_any_all(A: dace.int32[N, M], any_out: dace.int32[N], all_out: dace.int32[N]):
+            any_out[:] = np.any(A, axis=1)
+            all_out[:] = np.all(A, axis=1)
+
+        @dace.program
+        def b200_np_mean_axis0(A: dace.float64[N, M], B: dace.float64[M]):
+            B[:] = np.mean(A, axis=0)
+
+        @dace.program
+        def b200_np_min_initial(A: dace.int32[N, M], B: dace.int32[M]):
+            B[:] = np.min(A, axis=0, initial=7)
+
+        for p in (b200_np_any_all, b200_np_mean_axis0, b200_np_min_initial):
+            sdfg = _to_sdfg(p)
+            sdfg.apply_gpu_transformations()
+            E.use_b200_reductions(sdfg)
+            progs.append(sdfg)
+    finally:
+        E.Reduce.default_implementation = 'pure'
     return progs
 
 

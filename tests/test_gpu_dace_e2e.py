@@ -305,3 +305,28 @@ def test_fused_row_max_sum_programs(cuda):
     ref = x.double().sum(1).cpu().numpy()
     scale = x.double().abs().sum(1).cpu().numpy()
     assert np.all(np.abs(tsm.cpu().numpy() - ref) <= 1e-5 * scale)
+
+
+# ---- the other frontend producers: np.any / np.all / np.mean / np.min(initial=) ----
+
+def test_np_any_all_mean_min_programs(cuda):
+    rng = np.random.default_rng(51)
+    a = (rng.random((400, 333)) < 0.004).astype(np.int32) * rng.integers(1, 9, (400, 333)).astype(np.int32)
+    a[7, :] = 3                                         # a row that is all-true
+    any_out, all_out = np.full(400, 9, np.int32), np.full(400, 9, np.int32)
+    prog('b200_np_any_all')(A=a, any_out=any_out, all_out=all_out, N=400, M=333)
+    np.testing.assert_array_equal(any_out, np.any(a, axis=1).astype(np.int32))
+    np.testing.assert_array_equal(any_out, O.reduce(O.LOR, a, (1, ), identity=0))
+    # Reference quirk (replacements/reduction.py:107-109): np.all folds `x and y` from identity 0, so it is false
+    # everywhere - checked against the reference's CPU run when this test was written; the oracle restates it.
+    np.testing.assert_array_equal(all_out, O.reduce(O.LAND, a, (1, ), identity=0))
+    np.testing.assert_array_equal(all_out, np.zeros(400, np.int32))
+    f = rng.standard_normal((1234, 77))
+    b = np.zeros(77)
+    prog('b200_np_mean_axis0')(A=f, B=b, N=1234, M=77)
+    np.testing.assert_allclose(b, f.mean(0), rtol=1e-12, atol=1e-15)
+    m = rng.integers(-3, 50, (90, 41)).astype(np.int32)
+    m[:, 5] = 20                                        # never below the initial value
+    bm = np.zeros(41, np.int32)
+    prog('b200_np_min_initial')(A=m, B=bm, N=90, M=41)
+    np.testing.assert_array_equal(bm, np.minimum(m.min(0), 7))

@@ -1,0 +1,80 @@
+"""GPU: include/dace_b200_fused_reduce.cuh (map -> reduce in one kernel with a load functor) through the
+native harness tests/native/fused_reduce_harness.cu, against NumPy in fp64 / exact integers.  Shapes cover the
+warp-per-row kernel, CTA-per-row, split rows (+ finish kernel through the workspace) and > 65535 rows."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import dace_b200 as db
+
+pytestmark = pytest.mark.gpu
+
+HARNESS = os.path.join(os.path.dirname(__file__), 'native', '_built', 'libfused_reduce_harness.so')
+SHAPES = [(1, 1), (1, 5000001), (3, 100000), (7, 4097), (600, 5000), (5000, 300), (70000, 40), (300, 2047), (2, 0)]
+
+
+@pytest.fixture(scope='module')
+def lib():
+    if not os.path.exists(HARNESS):
+        pytest.fail('tests/native/_built/libfused_reduce_harness.so missing: run __graft_entry__.build()')
+    h = ctypes.CDLL(HARNESS)
+    h.fused_reduce_harness_run.restype = ctypes.c_int
+    h.fused_reduce_harness_run.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong,
+                                           ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_int, ctypes.c_void_p,
+                                           ctypes.c_ulonglong, ctypes.c_void_p]
+    return h
+
+
+def _run(lib, case, in0, in1, out, rows, n, use_identity, ws):
+    rc = lib.fused_reduce_harness_run(case, in0.data_ptr(), in1.data_ptr() if in1 is not None else None, out.data_ptr(),
+                                      out.stride(0) if out.dim() else 1, rows, n, 1 if use_identity else 0,
+                                      ws.ptr if ws is not None else None, ws.nbytes if ws is not None else 0,
+                                      torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize('rows,n', SHAPES)
+def test_fused_exp_shift_sum_f32(cuda, lib, rows, n):
+    ws = db.Workspace(cuda)
+    g = torch.Generator(device=cuda).manual_seed(rows * 31 + n)
+    x = torch.randn(rows, max(n, 1), device=cuda, generator=g)[:, :n].contiguous()
+    m = x.max(dim=1).values if n else torch.zeros(rows, device=cuda)
+    out = torch.full((rows, ), 3.0, device=cuda)
+    _run(lib, 0, x, m, out, rows, n, True, ws)
+    ref = torch.exp(x.double() - m.double()[:, None]).sum(1)
+    assert torch.allclose(out.double(), ref, rtol=2e-5, atol=1e-30)
+    # identity None: fold into the existing output; and no workspace: still right (no row splitting)
+    out2 = torch.full((rows, ), 3.0, device=cuda)
+    _run(lib, 0, x, m, out2, rows, n, False, None)
+    assert torch.allclose(out2.double(), ref + 3.0, rtol=2e-5)
+
+
+@pytest.mark.parametrize('rows,n', SHAPES)
+def test_fused_integer_cases_exact(cuda, lib, rows, n):
+    ws = db.Workspace(cuda)
+    g = torch.Generator(device=cuda).manual_seed(n + 5)
+    a = torch.randint(-1000, 1000, (rows, n), device=cuda, dtype=torch.int32, generator=g)
+    b = torch.randint(-1000, 1000, (rows, n), device=cuda, dtype=torch.int32, generator=g)
+    out = torch.zeros(rows, dtype=torch.int32, device=cuda)
+    _run(lib, 2, a, b, out, rows, n, True, ws)
+    ref = (a - b).abs().max(dim=1).values.clamp(min=-5) if n else torch.full((rows, ), -5, dtype=torch.int32, device=cuda)
+    assert torch.equal(out, ref.to(torch.int32))
+    al = torch.randint(-10**6, 10**6, (rows, n), device=cuda, dtype=torch.int64, generator=g)
+    w = torch.randint(-10**6, 10**6, (n, ), device=cuda, dtype=torch.int64, generator=g)
+    outl = torch.zeros(rows * 2, dtype=torch.int64, device=cuda)[::2]           # strided output
+    _run(lib, 3, al, w, outl, rows, n, True, ws)
+    assert torch.equal(outl, (al * w[None, :]).sum(1) + 11)
+
+
+def test_fused_row_norms_f64_deterministic(cuda, lib):
+    ws = db.Workspace(cuda)
+    x = torch.randn(5, 3000017, device=cuda, dtype=torch.float64)
+    o1, o2 = torch.zeros(5, dtype=torch.float64, device=cuda), torch.zeros(5, dtype=torch.float64, device=cuda)
+    _run(lib, 1, x, None, o1, 5, x.shape[1], True, ws)
+    _run(lib, 1, x, None, o2, 5, x.shape[1], True, ws)
+    assert torch.equal(o1, o2)                                   # fixed combine order
+    assert torch.allclose(o1, (x * x).sum(1), rtol=1e-12)
