@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 10
+VERSION = 11
 
 
 def up_to_date() -> bool:
@@ -307,6 +307,66 @@ def _programs(dace):
             progs.append(sdfg)
     finally:
         E.Reduce.default_implementation = 'pure'
+
+    # (12) Map -> transient -> Reduce fused into one generated kernel (dace_b200/fused_expansion.py): the map body
+    #      becomes a load functor for dace_b200::fused_rows.  `_unfused` twins keep the transient (map kernel by the
+    #      reference's code generator + 'B200' Reduce) for the A/B timing in tools/fused_probe.py.
+    from dace_b200 import fused_expansion as FE
+
+    @dace.program
+    def b200_fused_softmax_den(A: dace.float32[N, M], mx: dace.float32[N], s: dace.float32[N]):
+        tmp = np.ndarray([N, M], dace.float32)
+        for i, j in dace.map[0:N, 0:M]:
+            tmp[i, j] = np.exp(A[i, j] - mx[i])
+        s[:] = np.sum(tmp, axis=1)
+
+    @dace.program
+    def b200_unfused_softmax_den(A: dace.float32[N, M], mx: dace.float32[N], s: dace.float32[N]):
+        tmp = np.ndarray([N, M], dace.float32)
+        for i, j in dace.map[0:N, 0:M]:
+            tmp[i, j] = np.exp(A[i, j] - mx[i])
+        s[:] = np.sum(tmp, axis=1)
+
+    @dace.program
+    def b200_fused_sumsq(A: dace.float64[N, M], s: dace.float64[1]):
+        s[0] = np.sum(A * A)
+
+    @dace.program
+    def b200_fused_absdiff_max(A: dace.int32[N, M], B: dace.int32[N, M], out: dace.int32[N]):
+        tmp = np.ndarray([N, M], dace.int32)
+        for i, j in dace.map[0:N, 0:M]:
+            with dace.tasklet:
+                a << A[i, j]
+                b << B[i, j]
+                o >> tmp[i, j]
+                o = abs(a - b)
+        out[:] = np.max(tmp, axis=1)
+
+    @dace.program
+    def b200_fused_weighted_3d(A: dace.float64[N, M, K], w: dace.float64[K], out: dace.float64[N, M]):
+        tmp = np.ndarray([N, M, K], dace.float64)
+        for i, j, k in dace.map[0:N, 0:M, 0:K]:
+            tmp[i, j, k] = A[i, j, k] * w[k] + i
+        out[:] = np.sum(tmp, axis=2)
+
+    for p in (b200_fused_softmax_den, b200_unfused_softmax_den, b200_fused_sumsq, b200_fused_absdiff_max,
+              b200_fused_weighted_3d):
+        sdfg = _to_sdfg(p, simplify=True)
+        sdfg.apply_gpu_transformations()
+        # device-resident arguments: the probe times kernels, not PCIe copies (tests pass device pointers)
+        if 'softmax_den' in sdfg.name:
+            sdfg = _to_sdfg(p, simplify=True)
+            for a in ('A', 'mx', 's'):
+                sdfg.arrays[a].storage = dace.StorageType.GPU_Global
+            sdfg.apply_gpu_transformations()
+        fused = FE.fuse_maps_into_reductions(sdfg) if '_fused_' in sdfg.name else 0
+        if fused != (1 if '_fused_' in sdfg.name else 0):
+            raise RuntimeError('%s: FuseMapIntoReduce applied %d times' % (sdfg.name, fused))
+        AUTO.apply_b200(sdfg)
+        for n, _ in sdfg.all_nodes_recursive():       # a sensible block size for the unfused twin's map kernel
+            if isinstance(n, dace.nodes.MapEntry) and n.map.schedule == dace.ScheduleType.GPU_Device:
+                n.map.gpu_block_size = [256, 1, 1]
+        progs.append(sdfg)
     return progs
 
 
@@ -383,7 +443,7 @@ def build_all(verbose=True, only=None):
             manifest['programs'][name] = {
                 'lib': lib, 'args': args,
                 'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
-                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') + src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') +
+                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') + src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') + src.count('__b200_fused_') // 2 +
                 cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
                 'comm_calls': src.count('dace_b200_comm_allreduce('),
             }

@@ -1,0 +1,65 @@
+"""CPU: FuseMapIntoReduce (dace_b200/fused_expansion.py) on SDFGs from the real frontend: what matches,
+what the generated functor looks like, what is left alone.  Needs /root/reference; skipped on the GPU box."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle.refenv import import_reference, reference_available
+
+pytestmark = pytest.mark.skipif(not reference_available(), reason='reference checkout not present')
+
+
+@pytest.fixture(scope='module')
+def dace(tmp_path_factory):
+    d = tmp_path_factory.mktemp('dacecache_fused')
+    cwd = os.getcwd()
+    os.chdir(d)
+    mod = import_reference(str(d / '.dacecache'))
+    yield mod
+    os.chdir(cwd)
+
+
+def _den(dace, name, axis=1, gpu=True, reuse_tmp=False):
+    N, M = dace.symbol('N', dace.int64), dace.symbol('M', dace.int64)
+
+    @dace.program
+    def prog(A: dace.float32[N, M], mx: dace.float32[N], s: dace.float32[N if axis == 1 else M], t2: dace.float32[N, M]):
+        tmp = np.ndarray([N, M], dace.float32)
+        for i, j in dace.map[0:N, 0:M]:
+            tmp[i, j] = np.exp(A[i, j] - mx[i])
+        s[:] = np.sum(tmp, axis=axis)
+        if reuse_tmp:
+            t2[:] = tmp
+
+    sdfg = prog.to_sdfg(simplify=True)
+    sdfg.name = name
+    if gpu:
+        sdfg.apply_gpu_transformations()
+    return sdfg
+
+
+def test_map_body_becomes_a_load_functor(dace):
+    from dace_b200 import fused_expansion as FE
+    from dace.libraries.standard.nodes.reduce import Reduce
+    sdfg = _den(dace, 'fused_cg')
+    assert FE.fuse_maps_into_reductions(sdfg) == 1
+    assert not [n for n, _ in sdfg.all_nodes_recursive() if isinstance(n, Reduce)]
+    assert 'tmp' not in sdfg.arrays                       # the transient is gone
+    code = {c.title + c.language: c.clean_code for c in sdfg.generate_code()}
+    cu = ''.join(v for k, v in code.items() if k.endswith('cu'))
+    frame = ''.join(v for k, v in code.items() if k.endswith('cpp'))
+    assert '#include "dace_b200_fused_reduce.cuh"' in cu
+    assert 'struct __b200_load_fused_cg_' in cu and 'const float __in1 = gpu_A[__flat];' in cu
+    assert 'const float __in2 = gpu_mx[i];' in cu and '__out = exp(__in1);' in cu
+    assert 'dace_b200::fused_rows<3, float, float>(__load, __out, (ptrdiff_t)1, (size_t)(N), (size_t)(M), &__identity' in cu
+    assert 'DACE_GPU_CHECK(__b200_fused_fused_cg_' in frame and '__state->dace_b200_workspace' in frame
+    assert '__global__' not in cu.split('struct __b200_load_')[0] or 'reduce_atomic' not in cu   # no WCR map kernel
+    assert FE.fuse_maps_into_reductions(sdfg) == 0
+
+
+def test_things_that_must_not_be_fused(dace):
+    from dace_b200 import fused_expansion as FE
+    assert FE.fuse_maps_into_reductions(_den(dace, 'fused_axis0', axis=0)) == 0     # only last-axis / all-axes folds
+    assert FE.fuse_maps_into_reductions(_den(dace, 'fused_host', gpu=False)) == 0   # host storage: untouched
+    assert FE.fuse_maps_into_reductions(_den(dace, 'fused_reuse', reuse_tmp=True)) == 0   # the transient has another reader

@@ -330,3 +330,37 @@ def test_np_any_all_mean_min_programs(cuda):
     bm = np.zeros(41, np.int32)
     prog('b200_np_min_initial')(A=m, B=bm, N=90, M=41)
     np.testing.assert_array_equal(bm, np.minimum(m.min(0), 7))
+
+
+# ---- Map -> transient -> Reduce fused into one generated kernel (dace_b200/fused_expansion.py) ----
+
+def test_fused_map_reduce_programs(cuda):
+    import torch
+    rng = np.random.default_rng(61)
+    # softmax denominators, device-resident: s[i] = sum_j exp(A[i, j] - mx[i]); fused and unfused twins agree
+    a = torch.randn(777, 3001, device=cuda)
+    mx = a.max(dim=1).values.contiguous()
+    ref = torch.exp(a.double() - mx.double()[:, None]).sum(1)
+    for name in ('b200_fused_softmax_den', 'b200_unfused_softmax_den'):
+        s = torch.zeros(777, device=cuda)
+        torch.cuda.synchronize()
+        prog(name)(A=a.data_ptr(), mx=mx.data_ptr(), s=s.data_ptr(), N=777, M=3001)
+        torch.cuda.synchronize()
+        assert torch.allclose(s.double(), ref, rtol=2e-5), name
+    # all axes, one split row through the workspace: sum(A * A) in fp64
+    f = rng.standard_normal((1500, 2111))
+    out = np.zeros(1)
+    prog('b200_fused_sumsq')(A=f, s=out, N=1500, M=2111)
+    np.testing.assert_allclose(out[0], (f * f).sum(), rtol=1e-12)
+    # explicit tasklet, integer max: exact
+    x = rng.integers(-10**6, 10**6, (333, 4099)).astype(np.int32)
+    y = rng.integers(-10**6, 10**6, (333, 4099)).astype(np.int32)
+    o = np.zeros(333, np.int32)
+    prog('b200_fused_absdiff_max')(A=x, B=y, out=o, N=333, M=4099)
+    np.testing.assert_array_equal(o, np.abs(x - y).max(1))
+    # 3-D, reduce the last axis, a broadcast operand and a map parameter in the expression
+    t = rng.standard_normal((19, 23, 500))
+    w = rng.standard_normal(500)
+    o3 = np.zeros((19, 23))
+    prog('b200_fused_weighted_3d')(A=t, w=w, out=o3, N=19, M=23, K=500)
+    np.testing.assert_allclose(o3, (t * w[None, None, :] + np.arange(19)[:, None, None]).sum(2), rtol=1e-12, atol=1e-9)
