@@ -260,7 +260,7 @@ def _programs(dace):
 
     sdfg = _to_sdfg(b200_softmax_stats_fused, simplify=True)
     sdfg.apply_gpu_transformations()
-    AUTO.apply_b200(sdfg)
+    AUTO.apply_b200(sdfg, fuse=False)
     if FN.fuse_row_max_sum(sdfg) != 1:
         raise RuntimeError('b200_softmax_stats_fused: the Reduce pair was not fused')
     progs.append(sdfg)
@@ -362,7 +362,7 @@ def _programs(dace):
         fused = FE.fuse_maps_into_reductions(sdfg) if '_fused_' in sdfg.name else 0
         if fused != (1 if '_fused_' in sdfg.name else 0):
             raise RuntimeError('%s: FuseMapIntoReduce applied %d times' % (sdfg.name, fused))
-        AUTO.apply_b200(sdfg)
+        AUTO.apply_b200(sdfg, fuse=False)
         for n, _ in sdfg.all_nodes_recursive():       # a sensible block size for the unfused twin's map kernel
             if isinstance(n, dace.nodes.MapEntry) and n.map.schedule == dace.ScheduleType.GPU_Device:
                 n.map.gpu_block_size = [256, 1, 1]

@@ -39,8 +39,10 @@ def _stats(dace, name, dt=None, sum_axis=1, gpu=True):
 def test_pair_is_fused_into_one_call(dace):
     from dace_b200 import auto as AUTO, fuse_node as FN
     from dace.libraries.standard.nodes.reduce import Reduce
+    auto = _stats(dace, 'fuse_auto')
+    assert AUTO.apply_b200(auto)['max_sum'] == 1          # whole-program selection includes the rewrite
     sdfg = _stats(dace, 'fuse_cg')
-    AUTO.apply_b200(sdfg)
+    AUTO.apply_b200(sdfg, fuse=False)
     assert FN.fuse_row_max_sum(sdfg) == 1
     assert not [n for n, _ in sdfg.all_nodes_recursive() if isinstance(n, Reduce)]
     assert len([n for n, _ in sdfg.all_nodes_recursive() if isinstance(n, FN.RowsMaxSum)]) == 1
