@@ -18,7 +18,8 @@ calls it under ``DACE_GPU_CHECK`` on ``__dace_current_stream``.
 Matches (anything else is left untouched):
 * a top-level map whose ranges are exactly the transient's shape, writing ``T[p0, ..., pk]``, nothing else;
 * a body of Python tasklets chained through register scalars, reading single elements of device arrays;
-* ``T`` used nowhere else; the Reduce folds the last axis or all axes with a built-in operator;
+* ``T`` used nowhere else; the Reduce folds the last axis, all axes, or all leading axes (column fold:
+  ``dace_b200::fused_cols``) with a built-in operator;
 * accumulator types f32 / f64 / i32 / i64 / u32 / u64; a dense output.
 """
 import ast
@@ -82,6 +83,7 @@ class _Match:
         self.tasklets = []          # topological order
         self.scalars = []           # access nodes between tasklets
         self.all_axes = False
+        self.cols = False           # fold the leading axes, keep the last one
         self.redtype = None
 
 
@@ -128,10 +130,13 @@ def _match(state, sdfg, red: Reduce):
     if not all(_is_true(sz == sh) for sz, sh in zip(ie.data.subset.size(), tdesc.shape)):
         return None
     axes = sorted(a % nd for a in red.axes) if red.axes is not None else list(range(nd))
+    cols = False
     if axes == list(range(nd)):
         all_axes = True
     elif axes == [nd - 1]:
         all_axes = False
+    elif nd >= 2 and axes == list(range(nd - 1)):
+        all_axes, cols = False, True       # every leading axis folded, the last (contiguous) one kept
     else:
         return None
     odesc = sdfg.arrays[oe.data.data]
@@ -179,6 +184,7 @@ def _match(state, sdfg, red: Reduce):
     m = _Match()
     m.entry, m.exit, m.trans, m.reduce = entry, mexit, tnode, red
     m.tasklets, m.scalars, m.all_axes, m.redtype = tasklets, scalars, all_axes, rt
+    m.cols = cols
     return m
 
 
@@ -303,12 +309,12 @@ DACE_EXPORTED cudaError_t __b200_fused_{id}({sig});
 cudaError_t __b200_fused_{id}({sig}) {{
     __b200_load_{id} __load{{{init}}};
     {ident_decl}
-    return dace_b200::fused_rows<{red}, {acc}, {out_t}>(__load, __out, (ptrdiff_t)1, (size_t)({rows}), (size_t)({n}), {ident_arg},
+    return dace_b200::{fn}<{red}, {acc}, {out_t}>(__load, __out, (ptrdiff_t)1, (size_t)({rows}), (size_t)({n}), {ident_arg},
                                                       __workspace, __workspace_bytes, __stream);
 }}
 """.format(id=ident, members='\n    '.join(members), acc=acc, out_t=out_t, flat=flat_expr, pcode='\n        '.join(pcode),
            body='\n        '.join(body), sig=', '.join(sig), init=', '.join(arrays + syms), ident_decl=ident_decl,
-           red=int(m.redtype), rows=symstr(rows_expr, cpp_mode=True), n=symstr(n_expr, cpp_mode=True), ident_arg=ident_arg)
+           fn='fused_cols' if m.cols else 'fused_rows', red=int(m.redtype), rows=symstr(rows_expr, cpp_mode=True), n=symstr(n_expr, cpp_mode=True), ident_arg=ident_arg)
     frame_decl = 'DACE_EXPORTED cudaError_t __b200_fused_%s(%s);\n' % (ident, ', '.join(sig))
     call = ('DACE_GPU_CHECK(__b200_fused_%s(%s));' %
             (ident, ', '.join(['_in_' + a for a in arrays] + ['_out'] + syms +

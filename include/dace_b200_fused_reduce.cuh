@@ -131,6 +131,58 @@ __global__ void fused_finish_kernel(const A* __restrict__ partials, S* __restric
     fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
 }
 
+/* Column fold: out[c] = fold over r of load(r, c).  A CTA owns 32 adjacent columns (one per lane, so the
+ * functor's reads of x[r * ld + c] are coalesced) and one slice of the rows; its 8 warps take rows
+ * warp, warp + 8, ... with kFusedColUnroll rows in flight per warp. */
+constexpr int kFusedColUnroll = 8;
+
+template <int RED, typename A, typename S, typename Load>
+__global__ void __launch_bounds__(kFusedThreads)
+fused_cols_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, unsigned splits,
+                  A* __restrict__ partials, A identity, int has_identity) {
+    constexpr int kWarps = kFusedThreads / 32;
+    __shared__ A tile[kWarps][33];
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t col = size_t(blockIdx.x) * 32 + lane;
+    const unsigned split = blockIdx.y;
+    const size_t seg = (rows + splits - 1) / splits;
+    const size_t lo = size_t(split) * seg;
+    const size_t hi = (lo + seg < rows) ? lo + seg : rows;
+    const op<RED, A> f;
+    A acc = neutral<RED, A>();
+    if (col < n) {
+        size_t r = lo + warp;
+        for (; r + size_t(kFusedColUnroll - 1) * kWarps < hi; r += size_t(kFusedColUnroll) * kWarps) {
+            A v[kFusedColUnroll];
+#pragma unroll
+            for (int u = 0; u < kFusedColUnroll; ++u) v[u] = (A)load(r + size_t(u) * kWarps, col);
+#pragma unroll
+            for (int u = 0; u < kFusedColUnroll; ++u) acc = f(acc, v[u]);
+        }
+        for (; r < hi; r += kWarps) acc = f(acc, (A)load(r, col));
+    }
+    tile[warp][lane] = acc;
+    __syncthreads();
+    if (warp == 0 && col < n) {
+        A r = tile[0][lane];
+#pragma unroll
+        for (int w = 1; w < kWarps; ++w) r = f(r, tile[w][lane]);
+        if (splits == 1) fused_store<RED, A, S>(out + (ptrdiff_t)col * out_stride, r, identity, has_identity);
+        else partials[size_t(split) * n + col] = r;
+    }
+}
+
+template <int RED, typename A, typename S>
+__global__ void fused_cols_finish_kernel(const A* __restrict__ partials, S* __restrict__ out, ptrdiff_t out_stride, size_t n,
+                                         unsigned splits, A identity, int has_identity) {
+    const size_t col = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (col >= n) return;
+    const op<RED, A> f;
+    A r = partials[col];
+    for (unsigned s = 1; s < splits; ++s) r = f(r, partials[size_t(s) * n + col]);   /* fixed order, coalesced */
+    fused_store<RED, A, S>(out + (ptrdiff_t)col * out_stride, r, identity, has_identity);
+}
+
 inline int fused_sm_count() {
     static int cached = 0;
     if (cached == 0) {
@@ -192,6 +244,40 @@ inline cudaError_t fused_rows(Load load, S* out, ptrdiff_t out_stride, size_t ro
     if (e != cudaSuccess || splits == 1) return e;
     fused_finish_kernel<RED, A, S><<<(unsigned)((rows + 127) / 128), 128, 0, stream>>>(partials, out, out_stride, rows,
                                                                                     (unsigned)splits, ident, has);
+    return cudaGetLastError();
+}
+
+/* out[c * out_stride] = fold(op, identity, load(0, c), ..., load(rows - 1, c))      c in [0, n) */
+template <int RED, typename A, typename S, typename Load>
+inline cudaError_t fused_cols(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, const A* identity,
+                              void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    using namespace detail;
+    if (n == 0) return cudaSuccess;
+    const A ident = identity ? *identity : A(0);
+    const int has = identity ? 1 : 0;
+    const size_t sms = (size_t)fused_sm_count();
+    const size_t col_tiles = (n + 31) / 32;
+    size_t splits = 1;
+    if (col_tiles < 8 * sms) {
+        splits = (8 * sms + col_tiles - 1) / col_tiles;
+        const size_t max_by_rows = (rows + 63) / 64;          /* at least 64 rows per slice */
+        if (splits > max_by_rows) splits = max_by_rows;
+        if (splits > 65535) splits = 65535;
+        if (splits < 1) splits = 1;
+    }
+    A* partials = nullptr;
+    if (splits > 1) {
+        const size_t avail = (workspace != nullptr && workspace_bytes > kWorkspaceCounterBytes)
+                                 ? (workspace_bytes - kWorkspaceCounterBytes) / (n * sizeof(A)) : 0;
+        if (splits > avail) splits = avail > 0 ? avail : 1;
+        if (splits > 1) partials = reinterpret_cast<A*>(static_cast<char*>(workspace) + kWorkspaceCounterBytes);
+    }
+    fused_cols_kernel<RED, A, S, Load><<<dim3((unsigned)col_tiles, (unsigned)splits), kFusedThreads, 0, stream>>>(
+        load, out, out_stride, rows, n, (unsigned)splits, partials, ident, has);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess || splits == 1) return e;
+    fused_cols_finish_kernel<RED, A, S><<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(partials, out, out_stride, n,
+                                                                                      (unsigned)splits, ident, has);
     return cudaGetLastError();
 }
 

@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 11
+VERSION = 12
 
 
 def up_to_date() -> bool:
@@ -349,8 +349,15 @@ def _programs(dace):
             tmp[i, j, k] = A[i, j, k] * w[k] + i
         out[:] = np.sum(tmp, axis=2)
 
+    @dace.program
+    def b200_fused_colstats(A: dace.float32[N, M, K], mean: dace.float32[K], out: dace.float32[K]):
+        tmp = np.ndarray([N, M, K], dace.float32)
+        for i, j, k in dace.map[0:N, 0:M, 0:K]:
+            tmp[i, j, k] = (A[i, j, k] - mean[k]) * (A[i, j, k] - mean[k])
+        out[:] = np.sum(tmp, axis=(0, 1))
+
     for p in (b200_fused_softmax_den, b200_unfused_softmax_den, b200_fused_sumsq, b200_fused_absdiff_max,
-              b200_fused_weighted_3d):
+              b200_fused_weighted_3d, b200_fused_colstats):
         sdfg = _to_sdfg(p, simplify=True)
         sdfg.apply_gpu_transformations()
         # device-resident arguments: the probe times kernels, not PCIe copies (tests pass device pointers)

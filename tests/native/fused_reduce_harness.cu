@@ -39,6 +39,13 @@ extern "C" __attribute__((visibility("default"))) int fused_reduce_harness_run(
                   return fused_rows<kMax, int, int>(f, (int*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
         case 3: { const long long id = 11; MulLL f{(const long long*)in0, (const long long*)in1, (size_t)n};
                   return fused_rows<kSum, long long, long long>(f, (long long*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
+        /* column folds: out[c] = fold_r load(r, c) */
+        case 10: { const float id = 0.f; ExpShift f{(const float*)in0, (const float*)in1, (size_t)n};
+                   return fused_cols<kSum, float, float>(f, (float*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
+        case 12: { const int id = -5; AbsDiffI f{(const int*)in0, (const int*)in1, (size_t)n};
+                   return fused_cols<kMax, int, int>(f, (int*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
+        case 13: { const long long id = 11; MulLL f{(const long long*)in0, (const long long*)in1, (size_t)n};
+                   return fused_cols<kSum, long long, long long>(f, (long long*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
         default: return cudaErrorInvalidValue;
     }
 }

@@ -364,3 +364,14 @@ def test_fused_map_reduce_programs(cuda):
     o3 = np.zeros((19, 23))
     prog('b200_fused_weighted_3d')(A=t, w=w, out=o3, N=19, M=23, K=500)
     np.testing.assert_allclose(o3, (t * w[None, None, :] + np.arange(19)[:, None, None]).sum(2), rtol=1e-12, atol=1e-9)
+
+
+def test_fused_map_reduce_column_fold(cuda):
+    """Per-channel sum of squared deviations over [N, H*W, C] (channels last): leading axes folded, last kept."""
+    rng = np.random.default_rng(62)
+    a = rng.standard_normal((37, 301, 96)).astype(np.float32)
+    mean = a.mean((0, 1)).astype(np.float32)
+    out = np.zeros(96, np.float32)
+    prog('b200_fused_colstats')(A=a, mean=mean, out=out, N=37, M=301, K=96)
+    ref = ((a.astype(np.float64) - mean.astype(np.float64)) ** 2).sum((0, 1))
+    np.testing.assert_allclose(out, ref, rtol=2e-5)

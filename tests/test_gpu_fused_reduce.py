@@ -78,3 +78,34 @@ def test_fused_row_norms_f64_deterministic(cuda, lib):
     _run(lib, 1, x, None, o2, 5, x.shape[1], True, ws)
     assert torch.equal(o1, o2)                                   # fixed combine order
     assert torch.allclose(o1, (x * x).sum(1), rtol=1e-12)
+
+
+# ---- column folds: out[c] = fold over r of load(r, c) ----
+
+COL_SHAPES = [(1, 1), (5000001, 1), (100000, 3), (4097, 40), (5000, 600), (300, 5000), (64, 70000), (1000, 4096), (0, 5)]
+
+
+@pytest.mark.parametrize('rows,n', COL_SHAPES)
+def test_fused_column_folds(cuda, lib, rows, n):
+    ws = db.Workspace(cuda)
+    g = torch.Generator(device=cuda).manual_seed(rows * 7 + n)
+    x = torch.randn(max(rows, 1), n, device=cuda, generator=g)[:rows].contiguous()
+    m = torch.randn(max(rows, 1), device=cuda, generator=g)[:rows].contiguous() * 0.1
+    out = torch.full((n, ), 3.0, device=cuda)
+    _run(lib, 10, x, m, out, rows, n, True, ws)
+    ref = torch.exp(x.double() - m.double()[:, None]).sum(0)
+    assert torch.allclose(out.double(), ref, rtol=2e-5, atol=1e-30)
+    out2 = torch.full((n, ), 3.0, device=cuda)
+    _run(lib, 10, x, m, out2, rows, n, False, None)                 # identity None, no workspace (no row slices)
+    assert torch.allclose(out2.double(), ref + 3.0, rtol=2e-5)
+    a = torch.randint(-1000, 1000, (rows, n), device=cuda, dtype=torch.int32, generator=g)
+    b = torch.randint(-1000, 1000, (rows, n), device=cuda, dtype=torch.int32, generator=g)
+    oi = torch.zeros(n, dtype=torch.int32, device=cuda)
+    _run(lib, 12, a, b, oi, rows, n, True, ws)
+    refi = (a - b).abs().max(dim=0).values.clamp(min=-5) if rows else torch.full((n, ), -5, dtype=torch.int32, device=cuda)
+    assert torch.equal(oi, refi.to(torch.int32))
+    al = torch.randint(-10**6, 10**6, (rows, n), device=cuda, dtype=torch.int64, generator=g)
+    w = torch.randint(-10**6, 10**6, (n, ), device=cuda, dtype=torch.int64, generator=g)
+    ol = torch.zeros(n * 2, dtype=torch.int64, device=cuda)[::2]
+    _run(lib, 13, al, w, ol, rows, n, True, ws)
+    assert torch.equal(ol, (al * w[None, :]).sum(0) + 11)
