@@ -98,7 +98,7 @@ fused_rows_cta_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size
     }
 }
 
-/* Short rows: one warp per row. */
+/* Short rows: a warp takes two rows at a time, four columns-of-32 each: eight loads in flight per lane. */
 template <int RED, typename A, typename S, typename Load>
 __global__ void __launch_bounds__(kFusedThreads)
 fused_rows_warp_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, A identity,
@@ -106,17 +106,34 @@ fused_rows_warp_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, siz
     const unsigned lane = threadIdx.x & 31;
     const size_t warps_per_grid = size_t(gridDim.x) * (kFusedThreads / 32);
     const op<RED, A> f;
-    for (size_t row = size_t(blockIdx.x) * (kFusedThreads / 32) + (threadIdx.x >> 5); row < rows; row += warps_per_grid) {
-        A a0 = neutral<RED, A>(), a1 = neutral<RED, A>();
+    for (size_t row = 2 * (size_t(blockIdx.x) * (kFusedThreads / 32) + (threadIdx.x >> 5)); row < rows;
+         row += 2 * warps_per_grid) {
+        const bool two = row + 1 < rows;
+        const size_t row1 = two ? row + 1 : row;
+        A a[4], b[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { a[u] = neutral<RED, A>(); b[u] = neutral<RED, A>(); }
         size_t j = lane;
-        for (; j + 32 < n; j += 64) {
-            const A v0 = (A)load(row, j), v1 = (A)load(row, j + 32);
-            a0 = f(a0, v0);
-            a1 = f(a1, v1);
+        for (; j + 96 < n; j += 128) {
+            A va[4], vb[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) va[u] = (A)load(row, j + 32 * u);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) vb[u] = (A)load(row1, j + 32 * u);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { a[u] = f(a[u], va[u]); b[u] = f(b[u], vb[u]); }
         }
-        if (j < n) a0 = f(a0, (A)load(row, j));
-        const A r = warp_allreduce(f(a0, a1), f);
-        if (lane == 0) fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
+        for (; j < n; j += 32) {
+            const A va = (A)load(row, j), vb = (A)load(row1, j);
+            a[0] = f(a[0], va);
+            b[0] = f(b[0], vb);
+        }
+        const A ra = warp_allreduce(f(f(a[0], a[1]), f(a[2], a[3])), f);
+        const A rb = warp_allreduce(f(f(b[0], b[1]), f(b[2], b[3])), f);
+        if (lane == 0) {
+            fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, ra, identity, has_identity);
+            if (two) fused_store<RED, A, S>(out + (ptrdiff_t)row1 * out_stride, rb, identity, has_identity);
+        }
     }
 }
 
@@ -172,6 +189,27 @@ fused_cols_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t r
     }
 }
 
+/* Few rows, many columns: a thread per column, all rows of the slice in registers' reach. */
+template <int RED, typename A, typename S, typename Load>
+__global__ void __launch_bounds__(kFusedThreads)
+fused_cols_thread_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, A identity,
+                         int has_identity) {
+    const size_t col = size_t(blockIdx.x) * kFusedThreads + threadIdx.x;
+    if (col >= n) return;
+    const op<RED, A> f;
+    A acc = neutral<RED, A>();
+    size_t r = 0;
+    for (; r + kFusedColUnroll <= rows; r += kFusedColUnroll) {
+        A v[kFusedColUnroll];
+#pragma unroll
+        for (int u = 0; u < kFusedColUnroll; ++u) v[u] = (A)load(r + u, col);
+#pragma unroll
+        for (int u = 0; u < kFusedColUnroll; ++u) acc = f(acc, v[u]);
+    }
+    for (; r < rows; ++r) acc = f(acc, (A)load(r, col));
+    fused_store<RED, A, S>(out + (ptrdiff_t)col * out_stride, acc, identity, has_identity);
+}
+
 template <int RED, typename A, typename S>
 __global__ void fused_cols_finish_kernel(const A* __restrict__ partials, S* __restrict__ out, ptrdiff_t out_stride, size_t n,
                                          unsigned splits, A identity, int has_identity) {
@@ -212,7 +250,7 @@ inline cudaError_t fused_rows(Load load, S* out, ptrdiff_t out_stride, size_t ro
     const int has = identity ? 1 : 0;
     const size_t sms = (size_t)fused_sm_count();
     if (n < 2048 && rows >= 2 * sms) {
-        size_t grid = (rows + kFusedThreads / 32 - 1) / (kFusedThreads / 32);
+        size_t grid = ((rows + 1) / 2 + kFusedThreads / 32 - 1) / (kFusedThreads / 32);
         if (grid > sms * 8) grid = sms * 8;
         fused_rows_warp_kernel<RED, A, S, Load><<<(unsigned)grid, kFusedThreads, 0, stream>>>(load, out, out_stride, rows, n,
                                                                                           ident, has);
@@ -256,6 +294,11 @@ inline cudaError_t fused_cols(Load load, S* out, ptrdiff_t out_stride, size_t ro
     const A ident = identity ? *identity : A(0);
     const int has = identity ? 1 : 0;
     const size_t sms = (size_t)fused_sm_count();
+    if (rows <= 64 && n >= sms * kFusedThreads * 4) {
+        fused_cols_thread_kernel<RED, A, S, Load><<<(unsigned)((n + kFusedThreads - 1) / kFusedThreads), kFusedThreads, 0,
+                                                    stream>>>(load, out, out_stride, rows, n, ident, has);
+        return cudaGetLastError();
+    }
     const size_t col_tiles = (n + 31) / 32;
     size_t splits = 1;
     if (col_tiles < 8 * sms) {
