@@ -224,6 +224,12 @@ def _generate(state, sdfg, m: _Match):
             out_name, out_ctype, final = '__b200_value', acc, True
         else:
             out_name, out_ctype, final = out_edge.dst.data, sdfg.arrays[out_edge.dst.data].dtype.ctype, False
+        # map parameters / program symbols used inside the tasklet code itself (`tmp[i, j] = A[i, j] * i / N`)
+        for fs in map(str, t.free_symbols):
+            if fs in params:
+                need_params = True
+            elif fs in sdfg.symbols:
+                symbols.add(fs)
         lines = []
         defined = {out_conn: tdesc.dtype if final else sdfg.arrays[out_edge.dst.data].dtype}
         for e in state.in_edges(t):

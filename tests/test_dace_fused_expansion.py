@@ -60,6 +60,41 @@ def test_map_body_becomes_a_load_functor(dace):
 
 def test_things_that_must_not_be_fused(dace):
     from dace_b200 import fused_expansion as FE
-    assert FE.fuse_maps_into_reductions(_den(dace, 'fused_axis0', axis=0)) == 0     # only last-axis / all-axes folds
+    col = _den(dace, 'fused_axis0', axis=0)                                         # column fold: fused_cols
+    assert FE.fuse_maps_into_reductions(col) == 1
+    assert 'dace_b200::fused_cols<3, float, float>' in ''.join(c.clean_code for c in col.generate_code())
+    N, M, K = (dace.symbol(x, dace.int64) for x in 'NMK')
+
+    @dace.program
+    def mid(A: dace.float32[N, M, K], s: dace.float32[N, K]):
+        tmp = np.ndarray([N, M, K], dace.float32)
+        for i, j, k in dace.map[0:N, 0:M, 0:K]:
+            tmp[i, j, k] = A[i, j, k] * 2
+        s[:] = np.sum(tmp, axis=1)
+
+    sd = mid.to_sdfg(simplify=True)
+    sd.apply_gpu_transformations()
+    assert FE.fuse_maps_into_reductions(sd) == 0                                    # a middle axis: left to the 'B200' Reduce
     assert FE.fuse_maps_into_reductions(_den(dace, 'fused_host', gpu=False)) == 0   # host storage: untouched
     assert FE.fuse_maps_into_reductions(_den(dace, 'fused_reuse', reuse_tmp=True)) == 0   # the transient has another reader
+
+
+def test_tasklet_code_may_use_map_parameters_and_symbols(dace):
+    from dace_b200 import fused_expansion as FE
+    N, M = dace.symbol('N', dace.int64), dace.symbol('M', dace.int64)
+
+    @dace.program
+    def prog(A: dace.float64[N, M], s: dace.float64[N]):
+        tmp = np.ndarray([N, M], dace.float64)
+        for i, j in dace.map[0:N, 0:M]:
+            tmp[i, j] = A[i, j] * i / N + j
+        s[:] = np.sum(tmp, axis=1)
+
+    sdfg = prog.to_sdfg(simplify=True)
+    sdfg.name = 'fused_params'
+    sdfg.apply_gpu_transformations()
+    if FE.fuse_maps_into_reductions(sdfg) == 0:
+        pytest.skip('the frontend did not produce a plain tasklet body for this program')
+    cu = ''.join(c.clean_code for c in sdfg.generate_code() if c.language == 'cu')
+    assert 'const long long i = (long long)__row;' in cu and 'const long long j = (long long)__col;' in cu
+    assert 'int64_t N;' in cu or 'long long N;' in cu
