@@ -250,8 +250,10 @@ def _fold_scalar_after(sdfg, state, acc, rt: ReductionType, value):
 
 
 def propagate_sharding(sdfg, sharded: Dict[str, int]) -> Dict[str, int]:
-    """Arrays that are whole-array copies of a sharded array (host -> device copies inserted by
-    ``apply_gpu_transformations``) are shards along the same axis."""
+    """Which other arrays are shards, and along which axis:
+    * whole-array copies of a sharded array (the host -> device copies of ``apply_gpu_transformations``);
+    * outputs of elementwise maps: a map that reads ``X[..., p, ...]`` with parameter ``p`` on X's sharded
+      axis and writes ``T[..., p, ...]`` makes T a shard along the axis indexed by ``p``."""
     out = dict(sharded)
     changed = True
     while changed:
@@ -263,6 +265,28 @@ def propagate_sharding(sdfg, sharded: Dict[str, int]) -> Dict[str, int]:
                     if a in out and b not in out and len(sdfg.arrays[a].shape) == len(sdfg.arrays[b].shape):
                         out[b] = out[a]
                         changed = True
+            for entry in state.nodes():
+                if not isinstance(entry, nodes.MapEntry) or state.entry_node(entry) is not None:
+                    continue
+                params = set(entry.map.params)
+                shard_params = set()
+                for e in state.out_edges(entry):
+                    name = e.data.data
+                    if name in out and e.data.subset is not None and out[name] < len(e.data.subset):
+                        b, en, _ = e.data.subset.ranges[out[name]]
+                        if str(b) in params and str(b) == str(en):
+                            shard_params.add(str(b))
+                if not shard_params:
+                    continue
+                for e in state.in_edges(state.exit_node(entry)):
+                    name = e.data.data
+                    if name is None or name in out or e.data.subset is None:
+                        continue
+                    for d, (b, en, _) in enumerate(e.data.subset.ranges):
+                        if str(b) in shard_params and str(b) == str(en):
+                            out[name] = d
+                            changed = True
+                            break
     return out
 
 
@@ -367,6 +391,16 @@ def shard_reductions(sdfg, sharded: Dict[str, int]) -> Dict[str, int]:
     from .scatter_node import ScatterReduce
     sh = propagate_sharding(sdfg, sharded)
     counts = {'reduce': 0, 'scatter': 0, 'local': 0}
+    # Reductions that were already fused into generated kernels / single-pass nodes no longer show their axes:
+    # refuse instead of silently leaving a partial result uncombined.
+    for state in sdfg.states():
+        for node in state.nodes():
+            fused = (isinstance(node, nodes.Tasklet) and node.label == 'fused_map_reduce_b200') or \
+                type(node).__name__ == 'RowsMaxSum'
+            if fused and any(e.data.data in sh for e in state.in_edges(node)):
+                raise NotImplementedError('%s reads the sharded array(s) %s: call shard_reductions() BEFORE the fusing '
+                                          'rewrites (dace_b200.auto.apply_b200(sdfg, fuse=False), then shard, then fuse)' %
+                                          (node.label, sorted(e.data.data for e in state.in_edges(node) if e.data.data in sh)))
     for state in list(sdfg.states()):
         for node in list(state.nodes()):
             if isinstance(node, Reduce) and state.in_edges(node)[0].data.data in sh:

@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 12
+VERSION = 13
 
 
 def up_to_date() -> bool:
@@ -220,6 +220,22 @@ def _programs(dace):
     counts = CN.shard_reductions(sdfg, {'A': 0, 'keys': 0})
     if counts != {'reduce': 2, 'scatter': 1, 'local': 1}:
         raise RuntimeError('b200_sharded: unexpected sharding result %s' % counts)
+    progs.append(sdfg)
+
+    # (8b) Sharding + fusion in the right order: select (no fusing) -> shard -> fuse.  The local partial of the column
+    #      sum of squares is computed by the generated fused kernel, then combined across the ranks.
+    @dace.program
+    def b200_sharded_fused(A: dace.float32[N, M], sq: dace.float32[M]):
+        tmp = np.ndarray([N, M], dace.float32)
+        for i, j in dace.map[0:N, 0:M]:
+            tmp[i, j] = A[i, j] * A[i, j]
+        sq[:] = np.sum(tmp, axis=0)
+
+    sdfg = _to_sdfg(b200_sharded_fused, simplify=True)
+    sdfg.apply_gpu_transformations()
+    AUTO.apply_b200(sdfg, fuse=False)
+    if CN.shard_reductions(sdfg, {'A': 0})['reduce'] != 1 or AUTO.apply_b200(sdfg)['fused'] != 1:
+        raise RuntimeError('b200_sharded_fused: expected one combined and fused reduction')
     progs.append(sdfg)
 
     # (9) np.argmax / np.argmin: the frontend's struct-WCR map -> ArgReduce library node -> dace_b200_reduce_arg

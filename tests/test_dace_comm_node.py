@@ -106,3 +106,30 @@ def test_rejections(dace):
     assert C.shard_reductions(host, {'A': 0})['reduce'] == 1
     with pytest.raises(ValueError, match='GPU_Global'):     # the B200 combine has no CPU fallback
         host.expand_library_nodes()
+
+
+def test_fusing_before_sharding_is_refused(dace):
+    """A map -> reduce chain fused into one kernel hides the reduction from shard_reductions(): it must say so."""
+    from dace_b200 import auto as AUTO, comm_node as C
+    N, M = dace.symbol('N', dace.int64), dace.symbol('M', dace.int64)
+
+    @dace.program
+    def prog(A: dace.float32[N, M], s: dace.float32[M]):
+        tmp = np.ndarray([N, M], dace.float32)
+        for i, j in dace.map[0:N, 0:M]:
+            tmp[i, j] = A[i, j] * A[i, j]
+        s[:] = np.sum(tmp, axis=0)
+
+    fused_first = prog.to_sdfg(simplify=True)
+    fused_first.apply_gpu_transformations()
+    assert AUTO.apply_b200(fused_first)['fused'] == 1
+    with pytest.raises(NotImplementedError, match='BEFORE the fusing'):
+        C.shard_reductions(fused_first, {'A': 0})
+    right_order = prog.to_sdfg(simplify=True)
+    right_order.name = 'comm_then_fuse'
+    right_order.apply_gpu_transformations()
+    AUTO.apply_b200(right_order, fuse=False)
+    assert C.shard_reductions(right_order, {'A': 0})['reduce'] == 1
+    assert AUTO.apply_b200(right_order)['fused'] == 1            # the local partial is still computed by the fused kernel
+    code = ''.join(c.clean_code for c in right_order.generate_code())
+    assert 'dace_b200::fused_cols<3, float, float>' in code and code.count('dace_b200_comm_allreduce(') == 1

@@ -375,3 +375,11 @@ def test_fused_map_reduce_column_fold(cuda):
     prog('b200_fused_colstats')(A=a, mean=mean, out=out, N=37, M=301, K=96)
     ref = ((a.astype(np.float64) - mean.astype(np.float64)) ** 2).sum((0, 1))
     np.testing.assert_allclose(out, ref, rtol=2e-5)
+
+
+def test_sharded_fused_program_single_rank(cuda):
+    a = np.random.default_rng(71).standard_normal((2001, 333)).astype(np.float32)
+    sq = np.zeros(333, np.float32)
+    prog('b200_sharded_fused')(A=a, sq=sq, N=2001, M=333)
+    ref = (a.astype(np.float64) ** 2).sum(0)
+    assert np.all(np.abs(sq - ref) <= 1e-5 * ref)

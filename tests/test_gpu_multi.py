@@ -238,6 +238,12 @@ assert np.all(np.abs(cs - full.astype(np.float64).sum(0)) <= 1e-5 * scale)
 assert tot[0] == max(full.max(), np.float32(0.25))
 assert np.array_equal(bins, np.bincount(keys, minlength=M))
 assert np.allclose(rs, a.astype(np.float64).sum(1), rtol=1e-5, atol=1e-4)
+sq = np.zeros(M, np.float32)
+pf = ref_loader.RefProgram("b200_sharded_fused", built)       # shard -> fuse: fused kernel for the partial, then the combine
+pf(A=a, sq=sq, N=hi - lo, M=M)
+ref_sq = (full.astype(np.float64) ** 2).sum(0)
+assert np.all(np.abs(sq - ref_sq) <= 1e-5 * ref_sq), "sharded + fused column sum of squares"
+del pf
 lib = _lib.load()
 c = ctypes.c_void_p()
 _lib.check(lib.dace_b200_comm_default(ctypes.byref(c)), "comm_default")
