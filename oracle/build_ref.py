@@ -192,6 +192,37 @@ def _gpu_programs(dace):
     return progs
 
 
+_TODO = []
+
+
+def _compile_one(i):
+    """Compile _TODO[i] (inherited through fork); returns (name, manifest entry, failure text or None)."""
+    sdfg, meta = _TODO[i]
+    name = sdfg.name
+    try:
+        csdfg = sdfg.compile()
+    except Exception as ex:   # only tolerated for the GPU comparison programs
+        if not meta['kind'].endswith('_gpu'):
+            raise
+        return name, None, (str(ex).splitlines()[0][:300] if str(ex) else type(ex).__name__)
+    lib = 'lib%s.so' % name
+    shutil.copyfile(csdfg.filename, os.path.join(REF_DIR, lib))
+    # Signatures are only final after library-node expansion: read them
+    # from the SDFG the reference actually generated code for.
+    sdfg = csdfg.sdfg
+    args = []
+    for aname in sdfg.signature_arglist(with_types=False, for_call=True):
+        if aname in sdfg.arrays:
+            args.append({'name': aname, 'kind': 'array', 'dtype': sdfg.arrays[aname].dtype.to_string()})
+        else:
+            args.append({'name': aname, 'kind': 'symbol', 'ctype': sdfg.symbols[aname].ctype})
+    init_names = [n.strip() for n in sdfg.init_signature(for_call=True).split(',') if n.strip()]
+    entry = dict(meta)
+    entry.update({'lib': lib, 'args': args, 'init_symbols': [{'name': s, 'ctype': sdfg.symbols[s].ctype} for s in init_names]})
+    del csdfg
+    return name, entry, None
+
+
 def build_all(verbose: bool = True, only=None) -> dict:
     tmp = tempfile.mkdtemp(prefix='dace_b200_refbuild_')
     cwd = os.getcwd()
@@ -212,38 +243,27 @@ def build_all(verbose: bool = True, only=None) -> dict:
                 manifest['failed'] = old.get('failed', {})
             except Exception:
                 pass
-        for sdfg, meta in _programs(dace) + _gpu_programs(dace):
-            name = sdfg.name
-            if only and name not in only:
-                continue
-            try:
-                csdfg = sdfg.compile()
-            except Exception as ex:   # only tolerated for the GPU comparison programs
-                if not meta['kind'].endswith('_gpu'):
-                    raise
-                manifest['failed'][name] = str(ex).splitlines()[0][:300] if str(ex) else type(ex).__name__
+        todo = [(g, meta) for g, meta in _programs(dace) + _gpu_programs(dace) if not only or g.name in only]
+        global _TODO
+        _TODO = todo
+        # compiles run in forked workers (each program has its own build folder)
+        import concurrent.futures
+        import multiprocessing
+        jobs = max(1, min(len(todo), int(os.environ.get('DACE_B200_BUILD_JOBS', os.cpu_count() or 1))))
+        if jobs > 1:
+            with concurrent.futures.ProcessPoolExecutor(jobs, mp_context=multiprocessing.get_context('fork')) as pool:
+                results = list(pool.map(_compile_one, range(len(todo))))
+        else:
+            results = [_compile_one(i) for i in range(len(todo))]
+        for name, entry, failure in results:
+            if failure is not None:
+                manifest['failed'][name] = failure
                 if verbose:
-                    print('FAILED', name, manifest['failed'][name], file=sys.stderr)
+                    print('FAILED', name, failure, file=sys.stderr)
                 continue
-            lib = 'lib%s.so' % name
-            shutil.copyfile(csdfg.filename, os.path.join(REF_DIR, lib))
-            # Signatures are only final after library-node expansion: read them
-            # from the SDFG the reference actually generated code for.
-            sdfg = csdfg.sdfg
-            args = []
-            for aname in sdfg.signature_arglist(with_types=False, for_call=True):
-                if aname in sdfg.arrays:
-                    desc = sdfg.arrays[aname]
-                    args.append({'name': aname, 'kind': 'array', 'dtype': desc.dtype.to_string()})
-                else:
-                    args.append({'name': aname, 'kind': 'symbol', 'ctype': sdfg.symbols[aname].ctype})
-            init_names = [n.strip() for n in sdfg.init_signature(for_call=True).split(',') if n.strip()]
-            init_syms = [{'name': s, 'ctype': sdfg.symbols[s].ctype} for s in init_names]
-            entry = dict(meta)
-            entry.update({'lib': lib, 'args': args, 'init_symbols': init_syms})
             manifest['programs'][name] = entry
             if verbose:
-                print('built', name, [a['name'] for a in args], file=sys.stderr)
+                print('built', name, [a['name'] for a in entry['args']], file=sys.stderr)
         with open(MANIFEST, 'w') as f:
             json.dump(manifest, f, indent=1)
         return manifest

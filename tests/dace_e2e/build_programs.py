@@ -425,6 +425,41 @@ def _blockreduce_sdfg(dace, name, wcr, dt, nblocks, nthreads, items):
     return sdfg
 
 
+_TODO = []
+
+
+def _compile_one(i):
+    """Compile _TODO[i] (inherited through fork) and describe it for the manifest."""
+    sdfg = _TODO[i]
+    name = sdfg.name
+    csdfg = sdfg.compile()
+    lib = 'lib%s.so' % name
+    shutil.copyfile(csdfg.filename, os.path.join(OUT, lib))
+    g = csdfg.sdfg
+    args = []
+    for aname in g.signature_arglist(with_types=False, for_call=True):
+        if aname in g.arrays:
+            args.append({'name': aname, 'kind': 'array', 'dtype': g.arrays[aname].dtype.to_string(),
+                         'storage': str(g.arrays[aname].storage)})
+        else:
+            args.append({'name': aname, 'kind': 'symbol', 'ctype': g.symbols[aname].ctype})
+    init_names = [n.strip() for n in g.init_signature(for_call=True).split(',') if n.strip()]
+    srcdir = os.path.join(os.path.dirname(os.path.dirname(csdfg.filename)), 'src')
+    src = open(os.path.join(srcdir, 'cpu', name + '.cpp')).read()
+    cu = os.path.join(srcdir, 'cuda', name + '_cuda.cu')
+    cu = open(cu).read() if os.path.exists(cu) else ''
+    entry = {
+        'lib': lib, 'args': args,
+        'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
+        'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') +
+        src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') + src.count('__b200_fused_') // 2 +
+        cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
+        'comm_calls': src.count('dace_b200_comm_allreduce('),
+    }
+    del csdfg
+    return name, entry
+
+
 def build_all(verbose=True, only=None):
     from oracle.refenv import import_reference
     tmp = tempfile.mkdtemp(prefix='dace_b200_e2e_')
@@ -443,36 +478,23 @@ def build_all(verbose=True, only=None):
                                         if os.path.exists(os.path.join(OUT, v['lib']))}
             except Exception:
                 pass
-        for sdfg in _programs(dace):
-            name = sdfg.name
-            if only and name not in only:
-                continue
-            csdfg = sdfg.compile()
-            lib = 'lib%s.so' % name
-            shutil.copyfile(csdfg.filename, os.path.join(OUT, lib))
-            g = csdfg.sdfg
-            args = []
-            for aname in g.signature_arglist(with_types=False, for_call=True):
-                if aname in g.arrays:
-                    args.append({'name': aname, 'kind': 'array', 'dtype': g.arrays[aname].dtype.to_string(),
-                                 'storage': str(g.arrays[aname].storage)})
-                else:
-                    args.append({'name': aname, 'kind': 'symbol', 'ctype': g.symbols[aname].ctype})
-            init_names = [n.strip() for n in g.init_signature(for_call=True).split(',') if n.strip()]
-            srcdir = os.path.join(os.path.dirname(os.path.dirname(csdfg.filename)), 'src')
-            src = open(os.path.join(srcdir, 'cpu', name + '.cpp')).read()
-            cu = os.path.join(srcdir, 'cuda', name + '_cuda.cu')
-            cu = open(cu).read() if os.path.exists(cu) else ''
-            manifest['programs'][name] = {
-                'lib': lib, 'args': args,
-                'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
-                'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') + src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') + src.count('__b200_fused_') // 2 +
-                cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
-                'comm_calls': src.count('dace_b200_comm_allreduce('),
-            }
+        todo = [g for g in _programs(dace) if not only or g.name in only]
+        global _TODO
+        _TODO = todo
+        # The SDFGs are generated here; the compiles (CMake + nvcc + g++, ~10 s each) run in forked workers,
+        # every program in its own build folder.
+        import concurrent.futures
+        import multiprocessing
+        jobs = max(1, min(len(todo), int(os.environ.get('DACE_B200_BUILD_JOBS', os.cpu_count() or 1))))
+        if jobs > 1:
+            with concurrent.futures.ProcessPoolExecutor(jobs, mp_context=multiprocessing.get_context('fork')) as pool:
+                results = list(pool.map(_compile_one, range(len(todo))))
+        else:
+            results = [_compile_one(i) for i in range(len(todo))]
+        for name, entry in results:
+            manifest['programs'][name] = entry
             if verbose:
-                print('built', name, [a['name'] for a in args], 'b200 calls:', manifest['programs'][name]['b200_calls'],
-                      file=sys.stderr)
+                print('built', name, [a['name'] for a in entry['args']], 'b200 calls:', entry['b200_calls'], file=sys.stderr)
         json.dump(manifest, open(os.path.join(OUT, 'manifest.json'), 'w'), indent=1)
         return manifest
     finally:
