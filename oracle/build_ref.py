@@ -27,7 +27,7 @@ from .refenv import import_reference, reference_available  # noqa: F401
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REF_DIR = os.path.join(_HERE, '_ref')
 MANIFEST = os.path.join(REF_DIR, 'manifest.json')
-VERSION = 5
+VERSION = 6
 
 
 def up_to_date() -> bool:
@@ -189,6 +189,31 @@ def _gpu_programs(dace):
         if isinstance(n, dace.nodes.MapEntry):
             n.map.schedule = dace.ScheduleType.GPU_Device
     progs.append((sdfg, {'kind': 'wcr_map_gpu', 'impl': 'wcr-gpu-atomic'}))
+
+    # The reference's answer to map -> reduce chains: MapReduceFusion (reference
+    # dace/transformation/dataflow/mapreduce.py:18-146) = a WCR map, atomics on the GPU.  Same program as
+    # tests/dace_e2e b200_fused_softmax_den, device-resident; comparison baseline of dace_b200/fused_expansion.py.
+    import numpy as np
+    from dace.transformation.dataflow import MapReduceFusion
+    M = dace.symbol('M', dace.int64)
+
+    @dace.program
+    def refgpu_softmax_den_mapreducefusion(A: dace.float32[N, M], mx: dace.float32[N], s: dace.float32[N]):
+        tmp = np.ndarray([N, M], dace.float32)
+        for i, j in dace.map[0:N, 0:M]:
+            tmp[i, j] = np.exp(A[i, j] - mx[i])
+        dace.reduce(lambda a, b: a + b, tmp, s, axis=1, identity=0)   # writes s directly (the fusion cannot handle views)
+
+    sdfg = refgpu_softmax_den_mapreducefusion.to_sdfg(simplify=True)
+    sdfg.name = 'refgpu_softmax_den_mapreducefusion'
+    for a in ('A', 'mx', 's'):
+        sdfg.arrays[a].storage = G
+    sdfg.apply_gpu_transformations()
+    applied = sdfg.apply_transformations_repeated(MapReduceFusion)
+    for n, _ in sdfg.all_nodes_recursive():
+        if isinstance(n, dace.nodes.MapEntry) and n.map.schedule == dace.ScheduleType.GPU_Device:
+            n.map.gpu_block_size = [256, 1, 1]
+    progs.append((sdfg, {'kind': 'map_reduce_fusion_gpu', 'impl': 'MapReduceFusion', 'applied': applied}))
     return progs
 
 

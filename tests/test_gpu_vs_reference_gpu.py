@@ -8,6 +8,8 @@ compiled for sm_100 in the container where /root/reference exists
 pointers.  Integers must agree bit for bit; floats must both be within 1e-5 of the fp64
 truth (SURVEY.md 8(c) parity rules).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -113,3 +115,25 @@ def test_histogram_bit_exact_with_reference_gpu_kernel(nbins, cuda):
     mine = db.histogram(keys, nbins)
     assert torch.equal(mine, r)
     assert int(mine.sum().item()) == keys.numel()
+
+
+def test_fused_map_reduce_vs_reference_mapreducefusion(cuda):
+    """s[i] = sum_j exp(A[i, j] - mx[i]): this backend's FuseMapIntoReduce program (tree reduction in one generated
+    kernel) and the reference's own MapReduceFusion program (WCR map, atomics) on the same device buffers; both
+    within fp32 tolerance of the fp64 truth, ours at least as close."""
+    import torch
+    built = os.path.join(os.path.dirname(__file__), 'dace_e2e', '_built')
+    if not ref_loader.available(built):
+        pytest.skip('tests/dace_e2e/_built not present')
+    a = torch.randn(2048, 8192, device=cuda)
+    mx = a.max(dim=1).values.contiguous()
+    truth = torch.exp(a.double() - mx.double()[:, None]).sum(1)
+    s_ref = torch.full((2048, ), 7.0, device=cuda)
+    s_mine = torch.full((2048, ), 7.0, device=cuda)
+    torch.cuda.synchronize()
+    ref('refgpu_softmax_den_mapreducefusion')(A=a.data_ptr(), mx=mx.data_ptr(), s=s_ref.data_ptr(), N=2048, M=8192)
+    ref_loader.RefProgram('b200_fused_softmax_den', built)(A=a.data_ptr(), mx=mx.data_ptr(), s=s_mine.data_ptr(), N=2048, M=8192)
+    torch.cuda.synchronize()
+    err_ref = ((s_ref.double() - truth).abs() / truth).max().item()
+    err_mine = ((s_mine.double() - truth).abs() / truth).max().item()
+    assert err_mine <= 2e-5 and err_ref <= 1e-3, (err_mine, err_ref)

@@ -1,5 +1,6 @@
 """Ad-hoc probe: s[i] = sum_j exp(A[i, j] - mx[i]) as a DaCe program, fused (one generated kernel with a load
-functor) vs unfused (the reference code generator's map kernel writing a transient + 'B200' Reduce).
+functor) vs unfused (the reference code generator's map kernel writing a transient + 'B200' Reduce) vs the
+reference's own MapReduceFusion of the same program (oracle/_ref, WCR map with atomics).
 Device-resident arguments; wall clock around the program call with the stream synchronised (the generated
 program synchronises at its end)."""
 import os, sys, time, torch
@@ -13,8 +14,10 @@ for rows, n in ((65536, 8192), (8192, 65536), (1 << 20, 512)):
     mx = a.max(dim=1).values.contiguous()
     s = torch.zeros(rows, device=dev)
     ref = None
-    for name in ('b200_fused_softmax_den', 'b200_unfused_softmax_den'):
-        p = ref_loader.RefProgram(name, built)
+    for name in ('b200_fused_softmax_den', 'b200_unfused_softmax_den', 'refgpu_softmax_den_mapreducefusion'):
+        if name.startswith('refgpu') and rows > 65535:
+            continue                      # the reference's map kernel cannot launch: grid.y = rows
+        p = ref_loader.RefProgram(name, built if name.startswith('b200') else ref_loader.REF_DIR)
         for _ in range(2):
             p(A=a.data_ptr(), mx=mx.data_ptr(), s=s.data_ptr(), N=rows, M=n)
         torch.cuda.synchronize()
