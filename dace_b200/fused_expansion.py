@@ -85,6 +85,51 @@ class _Match:
         self.all_axes = False
         self.cols = False           # fold the leading axes, keep the last one
         self.redtype = None
+        # what the code generator needs, independent of where the pattern came from
+        self.shape = None           # iteration space = extents of the map
+        self.acc_dtype = None       # accumulator type
+        self.out_edge = None        # edge whose destination / memlet receives the result
+        self.identity = None        # None: fold into the existing output
+        self.uid = ''
+
+
+def _collect_body(state, sdfg, entry, mexit):
+    """(tasklets in topological order, scalar access nodes) of a map body made of Python tasklets chained
+    through register scalars and reading single elements of device arrays; None if it is anything else."""
+    scope = state.scope_subgraph(entry, include_entry=False, include_exit=False)
+    tasklets, scalars = [], []
+    for n in sdutil.dfs_topological_sort(scope, [x for x in scope.nodes() if scope.in_degree(x) == 0]):
+        if isinstance(n, nodes.Tasklet):
+            if n.language != dtypes.Language.Python or n.side_effects or len(n.out_connectors) != 1:
+                return None
+            tasklets.append(n)
+        elif isinstance(n, nodes.AccessNode):
+            d = sdfg.arrays[n.data]
+            if not d.transient or not _is_true(d.total_size == 1) or state.in_degree(n) != 1:
+                return None
+            scalars.append(n)
+        else:
+            return None
+    if not tasklets:
+        return None
+    for t in tasklets:
+        for e in state.in_edges(t):
+            if e.data.is_empty():
+                continue
+            if e.src is entry:
+                d = sdfg.arrays[e.data.data]
+                if (d.storage not in _GPU or e.data.wcr is not None or e.data.dynamic
+                        or not _is_true(e.data.subset.num_elements() == 1) or isinstance(d.dtype, dtypes.struct)):
+                    return None
+            elif not isinstance(e.src, nodes.AccessNode):
+                return None
+        outs = state.out_edges(t)
+        if len(outs) != 1 or not (outs[0].dst is mexit or isinstance(outs[0].dst, nodes.AccessNode)):
+            return None
+    for e in state.in_edges(entry):
+        if e.data.is_empty() or not isinstance(e.src, nodes.AccessNode):
+            return None
+    return tasklets, scalars
 
 
 def _match(state, sdfg, red: Reduce):
@@ -147,44 +192,16 @@ def _match(state, sdfg, red: Reduce):
         return None
     if all_axes and not _is_true(oe.data.subset.num_elements() == 1):
         return None
-    # body: tasklets chained through register scalars
-    scope = state.scope_subgraph(entry, include_entry=False, include_exit=False)
-    tasklets, scalars = [], []
-    for n in sdutil.dfs_topological_sort(scope, [x for x in scope.nodes() if scope.in_degree(x) == 0]):
-        if isinstance(n, nodes.Tasklet):
-            if n.language != dtypes.Language.Python or n.side_effects or len(n.out_connectors) != 1:
-                return None
-            tasklets.append(n)
-        elif isinstance(n, nodes.AccessNode):
-            d = sdfg.arrays[n.data]
-            if not d.transient or not _is_true(d.total_size == 1) or state.in_degree(n) != 1:
-                return None
-            scalars.append(n)
-        else:
-            return None
-    if not tasklets:
+    body = _collect_body(state, sdfg, entry, mexit)
+    if body is None:
         return None
-    for t in tasklets:
-        for e in state.in_edges(t):
-            if e.data.is_empty():
-                continue
-            if e.src is entry:
-                d = sdfg.arrays[e.data.data]
-                if (d.storage not in _GPU or e.data.wcr is not None or e.data.dynamic
-                        or not _is_true(e.data.subset.num_elements() == 1) or isinstance(d.dtype, dtypes.struct)):
-                    return None
-            elif not isinstance(e.src, nodes.AccessNode):
-                return None
-        outs = state.out_edges(t)
-        if len(outs) != 1 or not (outs[0].dst is mexit or isinstance(outs[0].dst, nodes.AccessNode)):
-            return None
-    for e in state.in_edges(entry):
-        if e.data.is_empty() or not isinstance(e.src, nodes.AccessNode):
-            return None
+    tasklets, scalars = body
     m = _Match()
     m.entry, m.exit, m.trans, m.reduce = entry, mexit, tnode, red
     m.tasklets, m.scalars, m.all_axes, m.redtype = tasklets, scalars, all_axes, rt
     m.cols = cols
+    m.shape, m.acc_dtype, m.out_edge, m.identity = list(tdesc.shape), tdesc.dtype, oe, red.identity
+    m.uid = '%s_%d_%d' % (sdfg.name, sdfg.node_id(state), state.node_id(red))
     return m
 
 
@@ -195,15 +212,14 @@ def _unparse(code: str, defined: dict) -> str:
 
 def _generate(state, sdfg, m: _Match):
     """(cuda global code, frame declaration, tasklet call code, [input array names])."""
-    entry, red = m.entry, m.reduce
-    tdesc = sdfg.arrays[m.trans.data]
-    oe = state.out_edges(red)[0]
+    entry = m.entry
+    oe = m.out_edge
     odesc = sdfg.arrays[oe.data.data]
-    acc, out_t = tdesc.dtype.ctype, odesc.dtype.ctype
-    shape = list(tdesc.shape)
+    acc, out_t = m.acc_dtype.ctype, odesc.dtype.ctype
+    shape = list(m.shape)
     nd = len(shape)
     params = list(entry.map.params)
-    ident = '%s_%d_%d' % (sdfg.name, sdfg.node_id(state), state.node_id(red))
+    ident = m.uid
 
     packed = [1] * nd
     for d in range(nd - 2, -1, -1):
@@ -231,7 +247,7 @@ def _generate(state, sdfg, m: _Match):
             elif fs in sdfg.symbols:
                 symbols.add(fs)
         lines = []
-        defined = {out_conn: tdesc.dtype if final else sdfg.arrays[out_edge.dst.data].dtype}
+        defined = {out_conn: m.acc_dtype if final else sdfg.arrays[out_edge.dst.data].dtype}
         for e in state.in_edges(t):
             if e.data.is_empty():
                 continue
@@ -295,10 +311,10 @@ def _generate(state, sdfg, m: _Match):
               ['%s %s;' % (sym_types[s], s) for s in syms]
     sig = ['const %s* %s' % (sdfg.arrays[a].dtype.ctype, a) for a in arrays] + ['%s* __out' % out_t] + \
           ['%s %s' % (sym_types[s], s) for s in syms] + ['void* __workspace', 'size_t __workspace_bytes', 'cudaStream_t __stream']
-    if red.identity is None:
+    if m.identity is None:
         ident_decl, ident_arg = '', '(const %s*)nullptr' % acc
     else:
-        ident_decl = 'const %s __identity = %s;' % (acc, symstr(red.identity, cpp_mode=True))
+        ident_decl = 'const %s __identity = %s;' % (acc, symstr(m.identity, cpp_mode=True))
         ident_arg = '&__identity'
     cuda_code = """
 struct __b200_load_{id} {{
@@ -328,10 +344,106 @@ cudaError_t __b200_fused_{id}({sig}) {{
     return cuda_code, frame_decl, call, arrays
 
 
+def _apply(graph, sdfg, m: _Match):
+    """Replace the matched subgraph by one host tasklet that launches the generated kernel."""
+    cuda_code, frame_decl, call, arrays = _generate(graph, sdfg, m)
+    entry, oe = m.entry, m.out_edge
+    out_desc = sdfg.arrays[oe.data.data]
+    in_conns = {'_in_' + a: dace.pointer(sdfg.arrays[a].dtype) for a in arrays}
+    tasklet = nodes.Tasklet('fused_map_reduce_b200', in_conns, {'_out': dace.pointer(out_desc.dtype)}, call,
+                            language=dace.Language.CPP)
+    tasklet.environments = {B200FusedReduce.full_class_path(), B200Reduce.full_class_path()}
+    graph.add_node(tasklet)
+    seen = set()
+    for e in graph.in_edges(entry):
+        a = e.data.data
+        if a in seen or a not in arrays:
+            continue
+        seen.add(a)
+        graph.add_edge(e.src, e.src_conn, tasklet, '_in_' + a, dace.Memlet.from_array(a, sdfg.arrays[a]))
+    out_memlet = copy.deepcopy(oe.data)
+    out_memlet.wcr = None          # the kernel folds into the output itself
+    graph.add_edge(tasklet, '_out', oe.dst, oe.dst_conn, out_memlet)
+    inner = [n.data for n in m.scalars]
+    graph.remove_nodes_from(list(graph.scope_subgraph(entry).nodes()) + [n for n in (m.trans, m.reduce) if n is not None])
+    for name in inner + ([m.trans.data] if m.trans is not None else []):
+        if not any(n.data == name for st in sdfg.states() for n in st.data_nodes()):
+            sdfg.remove_data(name, validate=False)
+    sdfg.append_global_code(cuda_code, 'cuda')
+    sdfg.append_global_code(frame_decl)
+    return tasklet
+
+
+def _match_wcr(state, sdfg, entry: nodes.MapEntry):
+    """A reduction written as a WCR map - ``for i, j in dace.map[...]: s[i] += f(A[i, j])`` after the frontend's
+    AugAssignToWCR, an explicit ``o >> s(1, lambda x, y: x + y)[i]`` tasklet output, or what the reference's
+    MapReduceFusion leaves behind: the output index uses only some of the map parameters, the others are folded
+    with the WCR operator.  Supported index forms: the leading parameters in order (row fold), only the last
+    parameter (column fold), a constant (everything folded)."""
+    if state.entry_node(entry) is not None:
+        return None
+    mexit = state.exit_node(entry)
+    if state.in_degree(mexit) != 1 or state.out_degree(mexit) != 1:
+        return None
+    w, outer = state.in_edges(mexit)[0], state.out_edges(mexit)[0]
+    if w.data.wcr is None or outer.data.wcr is None or w.data.dynamic or not isinstance(outer.dst, nodes.AccessNode):
+        return None
+    rt = detect_reduction_type(w.data.wcr)
+    if rt == ReductionType.Custom:
+        rt = lower_custom(w.data.wcr)
+    odesc = sdfg.arrays[w.data.data]
+    if (rt not in _OPS or odesc.storage not in _GPU or odesc.dtype not in _ACC_TYPES or isinstance(odesc, data.View)
+            or (rt in _INT_ONLY and odesc.dtype in (dace.float32, dace.float64))):
+        return None
+    params = list(entry.map.params)
+    nd = len(params)
+    shape = []
+    for b, e, st in entry.map.range.ranges:
+        if not (_is_true(b == 0) and _is_true(st == 1)):
+            return None
+        shape.append(e + 1)
+    idx = []
+    for b, e, _ in w.data.subset.ranges:
+        if str(b) != str(e):
+            return None
+        idx.append(str(b))
+    from .comm_node import _full_contiguous
+    all_axes = cols = False
+    uses_params = any(set(map(str, getattr(b, 'free_symbols', []))) & set(params) for b, _, _ in w.data.subset.ranges)
+    if not uses_params:
+        all_axes = True                                       # s[const] (+)= ...
+        if not _is_true(outer.data.subset.num_elements() == 1):
+            return None
+    elif nd >= 2 and idx == params[:-1]:
+        pass                                                  # rows: s[i...] (+)= f(..., j)
+    elif nd >= 2 and idx == [params[-1]]:
+        cols = True                                           # cols: s[j] (+)= f(i..., j)
+    else:
+        return None
+    if not all_axes:
+        kept = shape[:-1] if not cols else shape[-1:]
+        if len(odesc.shape) != len(kept) or not all(_is_true(a == b) for a, b in zip(odesc.shape, kept)):
+            return None
+        if not _full_contiguous(outer.data, odesc):
+            return None
+    body = _collect_body(state, sdfg, entry, mexit)
+    if body is None:
+        return None
+    tasklets, scalars = body
+    if any(e.data.data == w.data.data for t in tasklets for e in state.in_edges(t) if e.src is entry):
+        return None                                           # the map also reads what it accumulates into
+    m = _Match()
+    m.entry, m.exit, m.trans, m.reduce = entry, mexit, None, None
+    m.tasklets, m.scalars, m.all_axes, m.cols, m.redtype = tasklets, scalars, all_axes, cols, rt
+    m.shape, m.acc_dtype, m.out_edge, m.identity = shape, odesc.dtype, outer, None      # WCR: fold into the output
+    m.uid = '%s_%d_%d' % (sdfg.name, sdfg.node_id(state), state.node_id(entry))
+    return m
+
+
 @properties.make_properties
 class FuseMapIntoReduce(xf.SingleStateTransformation):
-    """Map -> transient -> Reduce  =>  one host tasklet that launches ``dace_b200::fused_rows`` with a
-    load functor generated from the map body."""
+    """Map -> transient -> Reduce  =>  one host tasklet that launches ``dace_b200::fused_rows`` /
+    ``fused_cols`` with a load functor generated from the map body."""
 
     reduce = xf.PatternNode(Reduce)
 
@@ -343,35 +455,34 @@ class FuseMapIntoReduce(xf.SingleStateTransformation):
         return _match(graph, sdfg, self.reduce) is not None
 
     def apply(self, graph, sdfg):
-        m = _match(graph, sdfg, self.reduce)
-        cuda_code, frame_decl, call, arrays = _generate(graph, sdfg, m)
-        red, entry = m.reduce, m.entry
-        oe = graph.out_edges(red)[0]
-        out_desc = sdfg.arrays[oe.data.data]
-        in_conns = {'_in_' + a: dace.pointer(sdfg.arrays[a].dtype) for a in arrays}
-        tasklet = nodes.Tasklet('fused_map_reduce_b200', in_conns, {'_out': dace.pointer(out_desc.dtype)}, call,
-                                language=dace.Language.CPP)
-        tasklet.environments = {B200FusedReduce.full_class_path(), B200Reduce.full_class_path()}
-        graph.add_node(tasklet)
-        seen = set()
-        for e in graph.in_edges(entry):
-            a = e.data.data
-            if a in seen or a not in arrays:
-                continue
-            seen.add(a)
-            graph.add_edge(e.src, e.src_conn, tasklet, '_in_' + a, dace.Memlet.from_array(a, sdfg.arrays[a]))
-        graph.add_edge(tasklet, '_out', oe.dst, oe.dst_conn, copy.deepcopy(oe.data))
-        inner = [n.data for n in m.scalars]
-        graph.remove_nodes_from(list(graph.scope_subgraph(entry).nodes()) + [m.trans, red])
-        for name in inner + [m.trans.data]:
-            if not any(n.data == name for st in sdfg.states() for n in st.data_nodes()):
-                sdfg.remove_data(name, validate=False)
-        sdfg.append_global_code(cuda_code, 'cuda')
-        sdfg.append_global_code(frame_decl)
-        return tasklet
+        return _apply(graph, sdfg, _match(graph, sdfg, self.reduce))
+
+
+@properties.make_properties
+class WCRMapToFusedReduce(xf.SingleStateTransformation):
+    """A reduction written as a WCR map  =>  one ``dace_b200::fused_rows`` / ``fused_cols`` launch (a tree
+    reduction folded into the existing output) instead of one atomic per element - the WCR lowering hook
+    for maps without indirection (indirect WCR maps go to ``ScatterReduce``, dace_b200/scatter_node.py)."""
+
+    map_entry = xf.PatternNode(nodes.MapEntry)
+
+    @classmethod
+    def expressions(cls):
+        return [sdutil.node_path_graph(cls.map_entry)]
+
+    def can_be_applied(self, graph, expr_index, sdfg, permissive=False):
+        return _match_wcr(graph, sdfg, self.map_entry) is not None
+
+    def apply(self, graph, sdfg):
+        return _apply(graph, sdfg, _match_wcr(graph, sdfg, self.map_entry))
 
 
 def fuse_maps_into_reductions(sdfg) -> int:
     """Apply :class:`FuseMapIntoReduce` wherever it matches (call after ``apply_gpu_transformations``);
     returns the number of fused pairs."""
     return sdfg.apply_transformations_repeated(FuseMapIntoReduce, validate=True)
+
+
+def lower_wcr_maps(sdfg) -> int:
+    """Apply :class:`WCRMapToFusedReduce` wherever it matches; returns the number of rewritten maps."""
+    return sdfg.apply_transformations_repeated(WCRMapToFusedReduce, validate=True)
