@@ -486,10 +486,10 @@ def build_all(verbose=True, only=None):
         import concurrent.futures
         import multiprocessing
         jobs = max(1, min(len(todo), int(os.environ.get('DACE_B200_BUILD_JOBS', os.cpu_count() or 1))))
-        if jobs > 1:
+        if jobs > 1 and sys.modules.get(__name__) is not None and getattr(sys.modules[__name__], '_compile_one', None) is _compile_one:
             with concurrent.futures.ProcessPoolExecutor(jobs, mp_context=multiprocessing.get_context('fork')) as pool:
                 results = list(pool.map(_compile_one, range(len(todo))))
-        else:
+        else:   # loaded under a name the workers could not import: compile one after the other
             results = [_compile_one(i) for i in range(len(todo))]
         for name, entry in results:
             manifest['programs'][name] = entry
