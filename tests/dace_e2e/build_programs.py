@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 13
+VERSION = 14
 
 
 def up_to_date() -> bool:
@@ -389,6 +389,39 @@ def _programs(dace):
         for n, _ in sdfg.all_nodes_recursive():       # a sensible block size for the unfused twin's map kernel
             if isinstance(n, dace.nodes.MapEntry) and n.map.schedule == dace.ScheduleType.GPU_Device:
                 n.map.gpu_block_size = [256, 1, 1]
+        progs.append(sdfg)
+
+    # (13) Reductions written as WCR maps (no indirection): `s[i] += f(A[i, j])` through the frontend's AugAssignToWCR,
+    #      an explicit WCR tasklet output folding everything into one element, and a column fold.  The reference emits
+    #      one atomic per element for these (reference codegen/targets/cpu.py:965-1013); WCRMapToFusedReduce
+    #      (dace_b200/fused_expansion.py) turns each into one tree-reduction kernel that folds into the output.
+    @dace.program
+    def b200_wcr_rows(A: dace.float32[N, M], mx: dace.float32[N], s: dace.float32[N]):
+        for i, j in dace.map[0:N, 0:M]:
+            s[i] += np.exp(A[i, j] - mx[i])
+
+    @dace.program
+    def b200_wcr_all_f64(A: dace.float64[N, M], s: dace.float64[1]):
+        for i, j in dace.map[0:N, 0:M]:
+            with dace.tasklet:
+                xin << A[i, j]                      # (names that do not shadow locals of this function)
+                res >> s(1, lambda x, y: x + y)[0]
+                res = xin * xin
+
+    @dace.program
+    def b200_wcr_cols_max_i32(A: dace.int32[N, M], B: dace.int32[N, M], out: dace.int32[M]):
+        for i, j in dace.map[0:N, 0:M]:
+            with dace.tasklet:
+                xin << A[i, j]
+                yin << B[i, j]
+                res >> out(1, lambda x, y: max(x, y))[j]
+                res = xin - yin
+
+    for p in (b200_wcr_rows, b200_wcr_all_f64, b200_wcr_cols_max_i32):
+        sdfg = _to_sdfg(p, simplify=True)
+        sdfg.apply_gpu_transformations()
+        if FE.lower_wcr_maps(sdfg) != 1:
+            raise RuntimeError('%s: WCRMapToFusedReduce did not apply' % sdfg.name)
         progs.append(sdfg)
     return progs
 

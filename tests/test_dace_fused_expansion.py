@@ -98,3 +98,49 @@ def test_tasklet_code_may_use_map_parameters_and_symbols(dace):
     cu = ''.join(c.clean_code for c in sdfg.generate_code() if c.language == 'cu')
     assert 'const long long i = (long long)__row;' in cu and 'const long long j = (long long)__col;' in cu
     assert 'int64_t N;' in cu or 'long long N;' in cu
+
+
+def test_wcr_maps_lower_to_the_fused_kernels(dace):
+    """`s[i] += f(A[i, j])` (AugAssignToWCR) and explicit WCR outputs: rows / cols / all forms; indirect WCR maps
+    (histograms) and maps that read their own output are not touched."""
+    from dace_b200 import fused_expansion as FE
+    N, M = dace.symbol('N', dace.int64), dace.symbol('M', dace.int64)
+
+    @dace.program
+    def rows(A: dace.float32[N, M], s: dace.float32[N]):
+        for i, j in dace.map[0:N, 0:M]:
+            s[i] += A[i, j] * A[i, j]
+
+    @dace.program
+    def cols(A: dace.float64[N, M], s: dace.float64[M]):
+        for i, j in dace.map[0:N, 0:M]:
+            with dace.tasklet:
+                xin << A[i, j]
+                res >> s(1, lambda x, y: min(x, y))[j]
+                res = xin + 1
+
+    @dace.program
+    def hist(keys: dace.int32[N], bins: dace.int32[M]):
+        for i in dace.map[0:N]:
+            bins[keys[i]] += 1
+
+    @dace.program
+    def middle(A: dace.float32[N, M, N], s: dace.float32[N, N]):
+        for i, j, k in dace.map[0:N, 0:M, 0:N]:
+            s[i, k] += A[i, j, k]
+
+    def lowered(p, name):
+        sdfg = p.to_sdfg(simplify=True)
+        sdfg.name = name
+        sdfg.apply_gpu_transformations()
+        return FE.lower_wcr_maps(sdfg), sdfg
+
+    n, sd = lowered(rows, 'wcr_cg_rows')
+    assert n == 1
+    code = ''.join(c.clean_code for c in sd.generate_code())
+    assert 'dace_b200::fused_rows<3, float, float>(__load, __out, (ptrdiff_t)1, (size_t)(N), (size_t)(M), (const float*)nullptr' in code
+    assert 'reduce_atomic' not in code and 'atomicAdd' not in code
+    n, sd = lowered(cols, 'wcr_cg_cols')
+    assert n == 1 and 'dace_b200::fused_cols<1, double, double>' in ''.join(c.clean_code for c in sd.generate_code())
+    assert lowered(hist, 'wcr_cg_hist')[0] == 0          # indirection: ScatterReduce's job
+    assert lowered(middle, 'wcr_cg_middle')[0] == 0      # a middle axis folded: left to the code generator

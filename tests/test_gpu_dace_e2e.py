@@ -383,3 +383,30 @@ def test_sharded_fused_program_single_rank(cuda):
     prog('b200_sharded_fused')(A=a, sq=sq, N=2001, M=333)
     ref = (a.astype(np.float64) ** 2).sum(0)
     assert np.all(np.abs(sq - ref) <= 1e-5 * ref)
+
+
+# ---- reductions written as WCR maps (no indirection) -> fused tree-reduction kernels ----
+
+def test_wcr_map_reductions(cuda):
+    rng = np.random.default_rng(81)
+    a = rng.standard_normal((513, 3001)).astype(np.float32)
+    mx = a.max(1)
+    s = np.full(513, 2.5, np.float32)                        # WCR accumulates into what is there
+    prog('b200_wcr_rows')(A=a, mx=mx, s=s, N=513, M=3001)
+    ref = 2.5 + np.exp(a.astype(np.float64) - mx.astype(np.float64)[:, None]).sum(1)
+    np.testing.assert_allclose(s, ref, rtol=2e-5)
+    f = rng.standard_normal((1111, 777))
+    tot = np.array([10.0])
+    p = prog('b200_wcr_all_f64')
+    p(A=f, s=tot, N=1111, M=777)
+    np.testing.assert_allclose(tot[0], 10.0 + (f * f).sum(), rtol=1e-12)
+    p(A=f, s=tot, N=1111, M=777)                             # accumulates again
+    np.testing.assert_allclose(tot[0], 10.0 + 2 * (f * f).sum(), rtol=1e-12)
+    x = rng.integers(-10**6, 10**6, (4099, 333)).astype(np.int32)
+    y = rng.integers(-10**6, 10**6, (4099, 333)).astype(np.int32)
+    out = np.full(333, -5, np.int32)
+    out[7] = 2**31 - 1                                       # an existing value that must survive the max
+    prog('b200_wcr_cols_max_i32')(A=x, B=y, out=out, N=4099, M=333)
+    exp = np.maximum((x - y).max(0), -5)
+    exp[7] = 2**31 - 1
+    np.testing.assert_array_equal(out, exp)
