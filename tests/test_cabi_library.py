@@ -61,3 +61,32 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
         assert 'no CPU fallback' in str(e)
     else:
         raise AssertionError('load() must raise when the CUDA library is missing')
+
+
+def test_single_process_communicator_needs_neither_nccl_nor_a_gpu():
+    """world == 1: dace_b200_comm_* is pure host logic (what a generated program gets when it is not launched
+    under a multi-rank launcher): create / query / no-op all-reduce / default / destroy."""
+    import ctypes
+    import os
+    from dace_b200 import _lib
+    lib = _lib.load()
+    c = ctypes.c_void_p()
+    assert lib.dace_b200_comm_create(0, 1, None, ctypes.byref(c)) == 0 and c.value
+    assert lib.dace_b200_comm_rank(c) == 0 and lib.dace_b200_comm_world(c) == 1
+    assert lib.dace_b200_comm_uses_peer_memory(c) == 0
+    buf = (ctypes.c_float * 4)(1, 2, 3, 4)
+    assert lib.dace_b200_comm_allreduce(c, 3, 0, buf, 4, None) == 0 and list(buf) == [1, 2, 3, 4]
+    assert lib.dace_b200_comm_allreduce(c, 3, 99, buf, 4, None) == 801          # unknown dtype: cudaErrorNotSupported
+    assert lib.dace_b200_comm_create(2, 2, None, ctypes.byref(ctypes.c_void_p())) == 1   # rank out of range
+    assert lib.dace_b200_comm_destroy(c) == 0
+    saved = {k: os.environ.pop(k, None) for k in ('WORLD_SIZE', 'RANK')}
+    try:
+        d = ctypes.c_void_p()
+        assert lib.dace_b200_comm_default(ctypes.byref(d)) == 0 and lib.dace_b200_comm_world(d) == 1
+        d2 = ctypes.c_void_p()
+        assert lib.dace_b200_comm_default(ctypes.byref(d2)) == 0 and d2.value == d.value     # process-wide
+        assert lib.dace_b200_comm_destroy(d) == 0
+    finally:
+        for k, v in saved.items():
+            if v is not None:
+                os.environ[k] = v
