@@ -38,6 +38,12 @@ from .expansion import B200Reduce
 from .redtypes import ReductionType, detect_reduction_type, lower_custom
 
 _ACC_TYPES = (dace.float32, dace.float64, dace.int32, dace.int64, dace.uint32, dace.uint64)
+# 16-bit floats are produced / stored as they are but ACCUMULATED in fp32 (north_star: "bf16 accumulated in fp32")
+_HALF_TYPES = tuple(t for t in (dace.float16, getattr(dace, 'bfloat16', None)) if t is not None)
+
+
+def _acc_of(dtype):
+    return dace.float32 if dtype in _HALF_TYPES else dtype
 _OPS = {ReductionType.Min, ReductionType.Max, ReductionType.Sum, ReductionType.Product,
         ReductionType.Logical_And, ReductionType.Bitwise_And, ReductionType.Logical_Or,
         ReductionType.Bitwise_Or, ReductionType.Logical_Xor, ReductionType.Bitwise_Xor}
@@ -88,6 +94,7 @@ class _Match:
         # what the code generator needs, independent of where the pattern came from
         self.shape = None           # iteration space = extents of the map
         self.acc_dtype = None       # accumulator type
+        self.value_dtype = None     # type of the value the map body produces (16-bit floats widen to the accumulator)
         self.out_edge = None        # edge whose destination / memlet receives the result
         self.identity = None        # None: fold into the existing output
         self.uid = ''
@@ -142,9 +149,9 @@ def _match(state, sdfg, red: Reduce):
         return None
     tdesc = sdfg.arrays[tnode.data]
     if (not tdesc.transient or isinstance(tdesc, data.View) or not isinstance(tdesc, data.Array)
-            or tdesc.storage not in _GPU or tdesc.dtype not in _ACC_TYPES):
+            or tdesc.storage not in _GPU or tdesc.dtype not in _ACC_TYPES + _HALF_TYPES):
         return None
-    if rt in _INT_ONLY and tdesc.dtype in (dace.float32, dace.float64):
+    if rt in _INT_ONLY and tdesc.dtype in (dace.float32, dace.float64) + _HALF_TYPES:
         return None
     if state.in_degree(tnode) != 1 or state.out_degree(tnode) != 1:
         return None
@@ -185,7 +192,7 @@ def _match(state, sdfg, red: Reduce):
     else:
         return None
     odesc = sdfg.arrays[oe.data.data]
-    if odesc.storage not in _GPU or odesc.dtype not in _ACC_TYPES or oe.data.wcr is not None:
+    if odesc.storage not in _GPU or odesc.dtype not in _ACC_TYPES + _HALF_TYPES or oe.data.wcr is not None:
         return None
     from .comm_node import _full_contiguous
     if not all_axes and not _full_contiguous(oe.data, odesc):
@@ -200,7 +207,8 @@ def _match(state, sdfg, red: Reduce):
     m.entry, m.exit, m.trans, m.reduce = entry, mexit, tnode, red
     m.tasklets, m.scalars, m.all_axes, m.redtype = tasklets, scalars, all_axes, rt
     m.cols = cols
-    m.shape, m.acc_dtype, m.out_edge, m.identity = list(tdesc.shape), tdesc.dtype, oe, red.identity
+    m.shape, m.acc_dtype, m.out_edge, m.identity = list(tdesc.shape), _acc_of(tdesc.dtype), oe, red.identity
+    m.value_dtype = tdesc.dtype
     m.uid = '%s_%d_%d' % (sdfg.name, sdfg.node_id(state), state.node_id(red))
     return m
 
@@ -237,7 +245,7 @@ def _generate(state, sdfg, m: _Match):
         out_edge = state.out_edges(t)[0]
         out_conn = next(iter(t.out_connectors))
         if out_edge.dst is m.exit:
-            out_name, out_ctype, final = '__b200_value', acc, True
+            out_name, out_ctype, final = '__b200_value', m.value_dtype.ctype, True
         else:
             out_name, out_ctype, final = out_edge.dst.data, sdfg.arrays[out_edge.dst.data].dtype.ctype, False
         # map parameters / program symbols used inside the tasklet code itself (`tmp[i, j] = A[i, j] * i / N`)
@@ -247,7 +255,7 @@ def _generate(state, sdfg, m: _Match):
             elif fs in sdfg.symbols:
                 symbols.add(fs)
         lines = []
-        defined = {out_conn: m.acc_dtype if final else sdfg.arrays[out_edge.dst.data].dtype}
+        defined = {out_conn: m.value_dtype if final else sdfg.arrays[out_edge.dst.data].dtype}
         for e in state.in_edges(t):
             if e.data.is_empty():
                 continue
@@ -322,9 +330,9 @@ struct __b200_load_{id} {{
     __device__ __forceinline__ {acc} operator()(size_t __row, size_t __col) const {{
         const size_t __flat = {flat}; (void)__flat;
         {pcode}
-        {acc} __b200_value;
+        {val} __b200_value;
         {body}
-        return __b200_value;
+        return ({acc})__b200_value;
     }}
 }};
 DACE_EXPORTED cudaError_t __b200_fused_{id}({sig});
@@ -335,7 +343,7 @@ cudaError_t __b200_fused_{id}({sig}) {{
                                                       __workspace, __workspace_bytes, __stream);
 }}
 """.format(id=ident, members='\n    '.join(members), acc=acc, out_t=out_t, flat=flat_expr, pcode='\n        '.join(pcode),
-           body='\n        '.join(body), sig=', '.join(sig), init=', '.join(arrays + syms), ident_decl=ident_decl,
+           val=m.value_dtype.ctype, body='\n        '.join(body), sig=', '.join(sig), init=', '.join(arrays + syms), ident_decl=ident_decl,
            fn='fused_cols' if m.cols else 'fused_rows', red=int(m.redtype), rows=symstr(rows_expr, cpp_mode=True), n=symstr(n_expr, cpp_mode=True), ident_arg=ident_arg)
     frame_decl = 'DACE_EXPORTED cudaError_t __b200_fused_%s(%s);\n' % (ident, ', '.join(sig))
     call = ('DACE_GPU_CHECK(__b200_fused_%s(%s));' %
@@ -392,8 +400,8 @@ def _match_wcr(state, sdfg, entry: nodes.MapEntry):
     if rt == ReductionType.Custom:
         rt = lower_custom(w.data.wcr)
     odesc = sdfg.arrays[w.data.data]
-    if (rt not in _OPS or odesc.storage not in _GPU or odesc.dtype not in _ACC_TYPES or isinstance(odesc, data.View)
-            or (rt in _INT_ONLY and odesc.dtype in (dace.float32, dace.float64))):
+    if (rt not in _OPS or odesc.storage not in _GPU or odesc.dtype not in _ACC_TYPES + _HALF_TYPES
+            or isinstance(odesc, data.View) or (rt in _INT_ONLY and odesc.dtype in (dace.float32, dace.float64) + _HALF_TYPES)):
         return None
     params = list(entry.map.params)
     nd = len(params)
@@ -435,7 +443,8 @@ def _match_wcr(state, sdfg, entry: nodes.MapEntry):
     m = _Match()
     m.entry, m.exit, m.trans, m.reduce = entry, mexit, None, None
     m.tasklets, m.scalars, m.all_axes, m.cols, m.redtype = tasklets, scalars, all_axes, cols, rt
-    m.shape, m.acc_dtype, m.out_edge, m.identity = shape, odesc.dtype, outer, None      # WCR: fold into the output
+    m.shape, m.acc_dtype, m.out_edge, m.identity = shape, _acc_of(odesc.dtype), outer, None   # WCR: fold into the output
+    m.value_dtype = odesc.dtype
     m.uid = '%s_%d_%d' % (sdfg.name, sdfg.node_id(state), state.node_id(entry))
     return m
 

@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 14
+VERSION = 15
 
 
 def up_to_date() -> bool:
@@ -416,6 +416,19 @@ def _programs(dace):
                 yin << B[i, j]
                 res >> out(1, lambda x, y: max(x, y))[j]
                 res = xin - yin
+
+    @dace.program
+    def b200_fused_f16_rows(A: dace.float16[N, M], s: dace.float16[N]):
+        tmp = np.ndarray([N, M], dace.float16)
+        for i, j in dace.map[0:N, 0:M]:
+            tmp[i, j] = A[i, j] * A[i, j]
+        s[:] = np.sum(tmp, axis=1)
+
+    sdfg = _to_sdfg(b200_fused_f16_rows, simplify=True)
+    sdfg.apply_gpu_transformations()
+    if FE.fuse_maps_into_reductions(sdfg) != 1:
+        raise RuntimeError('b200_fused_f16_rows: not fused')
+    progs.append(sdfg)
 
     for p in (b200_wcr_rows, b200_wcr_all_f64, b200_wcr_cols_max_i32):
         sdfg = _to_sdfg(p, simplify=True)

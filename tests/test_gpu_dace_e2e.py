@@ -410,3 +410,16 @@ def test_wcr_map_reductions(cuda):
     exp = np.maximum((x - y).max(0), -5)
     exp[7] = 2**31 - 1
     np.testing.assert_array_equal(out, exp)
+
+
+def test_fused_map_reduce_fp16_accumulates_in_fp32(cuda):
+    """fp16 producer and fp16 output, fp32 accumulator: the result is the fp32 sum rounded once to fp16."""
+    rng = np.random.default_rng(91)
+    a = (rng.random((257, 5000)) * 0.5).astype(np.float16)
+    s = np.zeros(257, np.float16)
+    prog('b200_fused_f16_rows')(A=a, s=s, N=257, M=5000)
+    sq = (a * a)                                             # the producer rounds each product to fp16
+    ref = sq.astype(np.float64).sum(1)
+    assert np.all(np.abs(s.astype(np.float64) - ref) <= 2.0 ** -10 * ref + 1e-3)    # one fp16 rounding of the sum
+    naive16 = sq.cumsum(axis=1, dtype=np.float16)[:, -1].astype(np.float64)          # fp16 accumulation drifts far more
+    assert np.abs(s.astype(np.float64) - ref).max() <= np.abs(naive16 - ref).max()
