@@ -50,7 +50,8 @@ def scalar_bytes(value, dt: int) -> bytes:
     if dt == BF16:
         return torch.tensor(float(value), dtype=torch.bfloat16).view(torch.int16).numpy().tobytes()
     if dt == F16:
-        return np.float16(value).tobytes()
+        with np.errstate(over='ignore'):      # e.g. -3e38 as "minus infinity" for a max
+            return np.float16(value).tobytes()
     npdt = _NP_OF_DT[dt]
     if np.issubdtype(npdt, np.integer):
         if isinstance(value, (bool, np.bool_)):

@@ -146,10 +146,14 @@ static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, v
                                  size_t R2, size_t row_stride, ptrdiff_t out_stride_k, const void* identity,
                                  const Launch& l) {
     const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
+    // 16-bit output: the second pass stays in fp32 (K values behind mid), a third tiny launch folds the
+    // identity and rounds once.
+    const bool half_out = dtmid == DT_F32 && (dtout == DT_BF16 || dtout == DT_F16);
     unsigned char neutral[8];
-    if (!supported_pair(dtin, dtmid) || !supported_pair(dtmid, dtout) || !neutral_bytes(red, dtmid, neutral))
+    if (!supported_pair(dtin, dtmid) || !(half_out || supported_pair(dtmid, dtout)) || !neutral_bytes(red, dtmid, neutral))
         return cudaErrorNotSupported;
-    const size_t need = R1 * K * dtype_size(dtmid);
+    const size_t mid_bytes = (R1 * K * dtype_size(dtmid) + 255) & ~size_t(255);
+    const size_t need = mid_bytes + (half_out ? K * sizeof(float) : 0);
     if (need > kMidMaxBytes) return cudaErrorNotSupported;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -178,8 +182,16 @@ static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, v
     }
     e = plan_rows(red, dtin, dtmid, in, ms.buf, R1 * K, R2, row_stride, 1, neutral, l);
     if (e != cudaSuccess) return e;
-    ColsArgs a{ms.buf, out, 1, R1, K, 0, K, 0, out_stride_k, identity};
-    e = launch_cols(red, dtmid, dtout, a, l);
+    if (half_out) {
+        float* tmp = reinterpret_cast<float*>(static_cast<char*>(ms.buf) + mid_bytes);
+        ColsArgs a{ms.buf, tmp, 1, R1, K, 0, K, 0, 1, neutral};
+        e = launch_cols(red, DT_F32, DT_F32, a, l);
+        if (e != cudaSuccess) return e;
+        e = launch_finish_convert(red, dtout, tmp, out, K, out_stride_k, identity, l);
+    } else {
+        ColsArgs a{ms.buf, out, 1, R1, K, 0, K, 0, out_stride_k, identity};
+        e = launch_cols(red, dtmid, dtout, a, l);
+    }
     if (e != cudaSuccess) return e;
     return cudaEventRecord(ms.last, l.stream);
 }

@@ -75,6 +75,9 @@ struct ScatterArgs {
     // (written by the key sampler of wcr_partition.cu earlier on the same stream).
     const int* gate = nullptr; int gate_run_if = 0;
 };
+// reduce_generic.cu: fp32 vector -> bf16 / f16 output with the identity fold (end of a two-pass plan).
+cudaError_t launch_finish_convert(int red, int dtout, const float* tmp, void* out, size_t n, ptrdiff_t out_stride,
+                                  const void* identity, const Launch& l);
 cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l);
 // Partition + shared-memory histogram path for large bin arrays (wcr_partition.cu);
 // cudaErrorNotSupported = does not apply, use the global-atomic kernel.

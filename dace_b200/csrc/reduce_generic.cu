@@ -177,6 +177,36 @@ static cudaError_t launch_fill_t(void* out, int nk, const long long* kshape, con
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------
+// Last step of a two-pass plan whose output is a 16-bit float: the fp32 result of the second pass
+// is folded with the caller's identity (or with what `out` holds) and rounded ONCE to bf16 / f16.
+// ---------------------------------------------------------------------------
+template <class Op, class S>
+__global__ void finish_convert_kernel(const float* __restrict__ tmp, S* __restrict__ out, size_t n, ptrdiff_t out_stride,
+                                      Finish<float> fin) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) write_result<Op, float, S>(out + (ptrdiff_t)i * out_stride, tmp[i], fin);
+}
+
+template <class S>
+static cudaError_t launch_finish_convert_t(int red, const float* tmp, void* out, size_t n, ptrdiff_t out_stride,
+                                           const void* identity, const Launch& l) {
+    return dispatch_op<float>(red, [&](auto op) -> cudaError_t {
+        using Op = decltype(op);
+        if (n == 0) return cudaSuccess;
+        finish_convert_kernel<Op, S><<<(unsigned)((n + 255) / 256), 256, 0, l.stream>>>(
+            tmp, static_cast<S*>(out), n, out_stride, make_finish<float, S>(identity));
+        return cudaGetLastError();
+    });
+}
+
+cudaError_t launch_finish_convert(int red, int dtout, const float* tmp, void* out, size_t n, ptrdiff_t out_stride,
+                                  const void* identity, const Launch& l) {
+    if (dtout == DT_BF16) return launch_finish_convert_t<__nv_bfloat16>(red, tmp, out, n, out_stride, identity, l);
+    if (dtout == DT_F16) return launch_finish_convert_t<__half>(red, tmp, out, n, out_stride, identity, l);
+    return cudaErrorNotSupported;
+}
+
 cudaError_t launch_fill(int dtout, void* out, int nk, const long long* kshape, const long long* kout,
                         const void* identity, const Launch& l) {
     switch (dtype_size(dtout)) {

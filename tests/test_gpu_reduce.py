@@ -467,3 +467,24 @@ def test_permuted_views_match_the_contiguous_result(dtype, perm, axes, cuda):
         out = torch.zeros(host.shape[2], host.shape[0], dtype=view.dtype, device=cuda).t()
         db.reduce('lambda a, b: a + b', view, out, axis=axes, identity=0)
         _check(out.cpu().numpy(), O.reduce(O.SUM, host, axes, identity=0, wide=True), dtype, host, axes, 'sum')
+
+
+@pytest.mark.parametrize('tdt', ['bfloat16', 'float16'])
+def test_two_pass_sixteen_bit_outputs(tdt, cuda):
+    """[R1, K, R2] with a 16-bit float output: fp32 between the passes, one rounding at the end, identity folded
+    once (given, or the value already in the output)."""
+    dt = getattr(torch, tdt)
+    eps = 2.0 ** -8 if tdt == 'bfloat16' else 2.0 ** -11
+    x = (torch.rand(12, 40, 3000, device=cuda) - 0.3).to(dt)
+    truth = x.double().sum((0, 2))
+    scale = x.double().abs().sum((0, 2))
+    got = db.reduce('lambda a, b: a + b', x, axis=(0, 2), identity=0)
+    assert got.dtype == dt
+    assert bool(((got.double() - truth).abs() <= eps * truth.abs() + 1e-5 * scale).all())
+    out = torch.full((40, ), 2.0, device=cuda, dtype=dt)
+    db.reduce('lambda a, b: a + b', x, out, axis=(0, 2), identity=None)
+    assert bool(((out.double() - (truth + 2.0)).abs() <= eps * (truth + 2.0).abs() + 1e-5 * scale).all())
+    mx = db.reduce('lambda a, b: max(a, b)', x, axis=(0, 2), identity=-3e38)
+    assert torch.equal(mx, x.amax((0, 2)))
+    mn = db.reduce('lambda a, b: min(a, b)', x, axis=(0, 2), identity=0.25)
+    assert torch.equal(mn.float(), torch.clamp(x.amin((0, 2)).float(), max=0.25))
