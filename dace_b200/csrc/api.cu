@@ -76,8 +76,24 @@ static cudaError_t plan_split(int red, int dtin, int dtout, const void* in, void
     const int big = row_bytes * rows >= (size_t(256) << 20) && row_bytes >= (size_t(8) << 20);
     const size_t tile = big ? (size_t(256) << 10) : (size_t(64) << 10);
     size_t want = ceil_div(row_bytes, tile);
-    size_t cap = ceil_div((big ? 1 : 2) * sms, rows);
-    if (want > cap) want = cap;
+    const size_t slots = (big ? 1 : 2) * sms;            // CTAs resident at a time
+    size_t cap = ceil_div(slots, rows);
+    if (rows > 1 && want > 1) {
+        // Several rows: rows x splits CTAs run in waves of `slots`; pick the split count whose last wave is
+        // the fullest (3 rows x 50 splits = 150 CTAs would leave 2 CTAs alone in a second wave: measured 0.78
+        // of the one-row bandwidth; 3 x 49 = 147 fills one wave).  Even counts only (clusters of 2).
+        const size_t smax = std::min(want, std::max<size_t>(cap, 64));
+        size_t best = 1;
+        double best_eff = 0.0;
+        for (size_t sp = 1; sp <= smax; sp = (sp == 1 ? 2 : sp + 2)) {
+            const size_t ctas = rows * sp;
+            const double eff = double(ctas) / double(ceil_div(ctas, slots) * slots);
+            if (eff > best_eff + 1e-9) { best_eff = eff; best = sp; }
+        }
+        want = best;
+    } else if (want > cap) {
+        want = cap;
+    }
     if (want < 1) want = 1;
     unsigned cluster = 1;
     if (want >= 2) { cluster = 2; want = (want / 2) * 2; }
@@ -301,7 +317,7 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
     }
     // [R1, K, R2] with contiguous R2 and dense (R1, K): two streaming passes through a small scratch.
     if (nr > 0 && nc == 3 && c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 &&
-        c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 32 &&
+        c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 2 &&
         getenv("DACE_B200_NO_TWO_PASS") == nullptr) {
         cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape,
                                        (size_t)c[2].shape, (size_t)c[1].in_stride, (ptrdiff_t)c[1].out_stride,
