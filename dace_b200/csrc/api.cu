@@ -73,7 +73,7 @@ static cudaError_t plan_split(int red, int dtin, int dtout, const void* in, void
     const size_t row_bytes = n * dtype_size(dtin);
     const size_t sms = sm_count();
     // Large rows: 1 CTA of 1024 threads per SM, 256 KiB tiles; otherwise 2 x 512 threads, 64 KiB tiles.
-    const int big = row_bytes * rows >= (size_t(256) << 20) && row_bytes >= (size_t(8) << 20);
+    const int big = row_bytes * rows >= (size_t(256) << 20) && row_bytes >= (size_t(2) << 20);
     const size_t tile = big ? (size_t(256) << 10) : (size_t(64) << 10);
     size_t want = ceil_div(row_bytes, tile);
     const size_t slots = (big ? 1 : 2) * sms;            // CTAs resident at a time
@@ -212,6 +212,44 @@ static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, v
     return cudaEventRecord(ms.last, l.stream);
 }
 
+// The canonical forms that have a streaming kernel; cudaErrorNotSupported = none of them.
+static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void* out, const Dim* c, int nc, int nr,
+                             const void* identity, const Launch& l) {
+    if (nr > 0) {
+        // [R] contiguous -> full reduction.
+        if (nc == 1 && c[0].in_stride == 1)
+            return plan_split(red, dtin, dtout, in, out, 1, (size_t)c[0].shape, 0, 0, identity, l);
+        // [K, R] with contiguous R -> rows.
+        if (nc == 2 && !c[0].reduced && c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
+            return plan_rows(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[0].in_stride,
+                             (ptrdiff_t)c[0].out_stride, identity, l);
+        }
+        // [R, K] / [K1, R, K2] with contiguous trailing K -> cols.
+        if (nc == 2 && c[0].reduced && !c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
+            ColsArgs a{in, out, 1, (size_t)c[0].shape, (size_t)c[1].shape, 0, (size_t)c[0].in_stride,
+                       0, (ptrdiff_t)c[1].out_stride, identity};
+            return launch_cols(red, dtin, dtout, a, l);
+        }
+        if (nc == 3 && !c[0].reduced && c[1].reduced && !c[2].reduced && c[2].in_stride == 1 &&
+            c[0].in_stride >= 0 && c[1].in_stride >= 0) {
+            ColsArgs a{in, out, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[2].shape,
+                       (size_t)c[0].in_stride, (size_t)c[1].in_stride,
+                       (ptrdiff_t)c[0].out_stride, (ptrdiff_t)c[2].out_stride, identity};
+            return launch_cols(red, dtin, dtout, a, l);
+        }
+    }
+    // [R1, K, R2] with contiguous R2 and dense (R1, K): two streaming passes through a small scratch.
+    if (nr > 0 && nc == 3 && c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 &&
+        c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 2 &&
+        getenv("DACE_B200_NO_TWO_PASS") == nullptr) {
+        cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape,
+                                       (size_t)c[2].shape, (size_t)c[1].in_stride, (ptrdiff_t)c[1].out_stride,
+                                       identity, l);
+        if (e2 != cudaErrorNotSupported) return e2;
+    }
+    return cudaErrorNotSupported;
+}
+
 static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, void* out, int ndim,
                                   const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,
                                   uint32_t mask, const void* identity, void* workspace, size_t workspace_bytes,
@@ -291,38 +329,27 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
     int nk = 0, nr = 0;
     for (int i = 0; i < nc; ++i) (c[i].reduced ? nr : nk)++;
 
-    const size_t esz = dtype_size(dtin);
-    if (nr > 0) {
-        // [R] contiguous -> full reduction.
-        if (nc == 1 && c[0].in_stride == 1)
-            return plan_split(red, dtin, dtout, in, out, 1, (size_t)c[0].shape, 0, 0, identity, l);
-        // [K, R] with contiguous R -> rows.
-        if (nc == 2 && !c[0].reduced && c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
-            return plan_rows(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[0].in_stride,
-                             (ptrdiff_t)c[0].out_stride, identity, l);
-        }
-        // [R, K] / [K1, R, K2] with contiguous trailing K -> cols.
-        if (nc == 2 && c[0].reduced && !c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
-            ColsArgs a{in, out, 1, (size_t)c[0].shape, (size_t)c[1].shape, 0, (size_t)c[0].in_stride,
-                       0, (ptrdiff_t)c[1].out_stride, identity};
-            return launch_cols(red, dtin, dtout, a, l);
-        }
-        if (nc == 3 && !c[0].reduced && c[1].reduced && !c[2].reduced && c[2].in_stride == 1 &&
-            c[0].in_stride >= 0 && c[1].in_stride >= 0) {
-            ColsArgs a{in, out, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[2].shape,
-                       (size_t)c[0].in_stride, (size_t)c[1].in_stride,
-                       (ptrdiff_t)c[0].out_stride, (ptrdiff_t)c[2].out_stride, identity};
-            return launch_cols(red, dtin, dtout, a, l);
-        }
+    {
+        cudaError_t ef = plan_fast(red, dtin, dtout, in, out, c, nc, nr, identity, l);
+        if (ef != cudaErrorNotSupported) return ef;
     }
-    // [R1, K, R2] with contiguous R2 and dense (R1, K): two streaming passes through a small scratch.
-    if (nr > 0 && nc == 3 && c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 &&
-        c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 2 &&
-        getenv("DACE_B200_NO_TWO_PASS") == nullptr) {
-        cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape,
-                                       (size_t)c[2].shape, (size_t)c[1].in_stride, (ptrdiff_t)c[1].out_stride,
-                                       identity, l);
-        if (e2 != cudaErrorNotSupported) return e2;
+    // Interleaved kept / reduced axes ([R1, K1, R2, K2], [K1, R1, K2, R2], ...): peel the outermost axis on the host
+    // when it is short and what remains has a streaming kernel - a reduced axis folds slice after slice into the
+    // output (identity for the first slice, "fold into existing" for the rest), a kept axis writes slice by slice.
+    if (nr > 0 && nc >= 3 && c[0].shape <= 64 && c[0].in_stride >= 0 && getenv("DACE_B200_NO_PEEL") == nullptr) {
+        int sub_nr = 0;
+        for (int i = 1; i < nc; ++i) sub_nr += c[i].reduced ? 1 : 0;
+        const size_t isz = dtype_size(dtin), osz = dtype_size(dtout);
+        bool ok = sub_nr > 0;
+        for (long long i = 0; ok && i < c[0].shape; ++i) {
+            const char* sin = static_cast<const char*>(in) + size_t(i) * size_t(c[0].in_stride) * isz;
+            char* sout = static_cast<char*>(out) + (c[0].reduced ? 0 : ptrdiff_t(i) * c[0].out_stride * ptrdiff_t(osz));
+            const void* sid = (c[0].reduced && i > 0) ? nullptr : identity;
+            cudaError_t ep = plan_fast(red, dtin, dtout, sin, sout, c + 1, nc - 1, sub_nr, sid, l);
+            if (ep == cudaErrorNotSupported && i == 0) { ok = false; break; }   // nothing launched yet: generic kernel
+            if (ep != cudaSuccess) return ep;
+        }
+        if (ok) return cudaSuccess;
     }
     // Everything else: generic strided kernel.
     if (nk > kMaxDims || nr > kMaxDims) return cudaErrorNotSupported;

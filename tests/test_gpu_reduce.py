@@ -488,3 +488,22 @@ def test_two_pass_sixteen_bit_outputs(tdt, cuda):
     assert torch.equal(mx, x.amax((0, 2)))
     mn = db.reduce('lambda a, b: min(a, b)', x, axis=(0, 2), identity=0.25)
     assert torch.equal(mn.float(), torch.clamp(x.amin((0, 2)).float(), max=0.25))
+
+
+@pytest.mark.parametrize('dtype', [np.float32, np.int64])
+@pytest.mark.parametrize('shape,axes', [([5, 7, 9, 130], (0, 2)), ([6, 5, 8, 300], (1, 3)), ([3, 4, 5, 6, 64], (1, 3)),
+                                        ([2, 3, 4, 5, 6, 40], (0, 2, 4)), ([64, 3, 50, 33], (0, 2)), ([65, 3, 50, 33], (0, 2))])
+def test_interleaved_axes_host_peel(dtype, shape, axes, cuda):
+    """[R1, K1, R2, K2], [K1, R1, K2, R2], ...: the outermost axis is peeled on the host (<= 64 slices) and each slice
+    goes to a streaming kernel; a reduced outer axis folds slice after slice, so the identity must count once."""
+    rng = np.random.default_rng(8)
+    a = _data(rng, shape, dtype, 'sum')
+    for op in ('sum', 'max'):
+        got, ref = _run(a, axes, op, cuda)
+        _check(got, ref, dtype, a, axes, op)
+    kept = [s for i, s in enumerate(shape) if i not in axes]
+    init = _data(rng, kept, dtype, 'sum')
+    got, ref = _run(a, axes, 'sum', cuda, identity=None, out_init=init)       # fold into the existing output
+    _check(got, ref, dtype, a, axes, 'sum')
+    got, ref = _run(a, axes, 'sum', cuda, identity=3)                          # a non-neutral identity, once
+    _check(got, ref, dtype, a, axes, 'sum')
