@@ -158,9 +158,9 @@ constexpr size_t kMidMaxBytes = size_t(256) << 20;
 // pass 1 folds every contiguous R2 run with the row kernels into mid[R1, K] (neutral seed),
 // pass 2 folds mid over R1 with the column kernel and applies the caller's identity.  Both passes
 // are the streaming kernels; the generic strided kernel it replaces ran one warp per output.
-static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, void* out, size_t R1, size_t K,
-                                 size_t R2, size_t row_stride, ptrdiff_t out_stride_k, const void* identity,
-                                 const Launch& l) {
+static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, void* out, size_t O, size_t R1, size_t K,
+                                 size_t R2, size_t row_stride, ptrdiff_t out_stride_o, ptrdiff_t out_stride_k,
+                                 const void* identity, const Launch& l) {
     const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
     // 16-bit output: the second pass stays in fp32 (K values behind mid), a third tiny launch folds the
     // identity and rounds once.
@@ -168,8 +168,10 @@ static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, v
     unsigned char neutral[8];
     if (!supported_pair(dtin, dtmid) || !(half_out || supported_pair(dtmid, dtout)) || !neutral_bytes(red, dtmid, neutral))
         return cudaErrorNotSupported;
-    const size_t mid_bytes = (R1 * K * dtype_size(dtmid) + 255) & ~size_t(255);
-    const size_t need = mid_bytes + (half_out ? K * sizeof(float) : 0);
+    // O > 1: an outer kept axis ([O, R1, K, R2] dense, e.g. per-sample per-channel statistics): the rows pass
+    // covers O * R1 * K runs, the column pass folds R1 for every (o, k).
+    const size_t mid_bytes = (O * R1 * K * dtype_size(dtmid) + 255) & ~size_t(255);
+    const size_t need = mid_bytes + (half_out ? O * K * sizeof(float) : 0);
     if (need > kMidMaxBytes) return cudaErrorNotSupported;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -196,16 +198,17 @@ static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, v
         if (e != cudaSuccess) { ms.buf = nullptr; return e; }
         ms.bytes = alloc;
     }
-    e = plan_rows(red, dtin, dtmid, in, ms.buf, R1 * K, R2, row_stride, 1, neutral, l);
+    e = plan_rows(red, dtin, dtmid, in, ms.buf, O * R1 * K, R2, row_stride, 1, neutral, l);
     if (e != cudaSuccess) return e;
     if (half_out) {
         float* tmp = reinterpret_cast<float*>(static_cast<char*>(ms.buf) + mid_bytes);
+        if (O != 1) return cudaErrorNotSupported;
         ColsArgs a{ms.buf, tmp, 1, R1, K, 0, K, 0, 1, neutral};
         e = launch_cols(red, DT_F32, DT_F32, a, l);
         if (e != cudaSuccess) return e;
         e = launch_finish_convert(red, dtout, tmp, out, K, out_stride_k, identity, l);
     } else {
-        ColsArgs a{ms.buf, out, 1, R1, K, 0, K, 0, out_stride_k, identity};
+        ColsArgs a{ms.buf, out, O, R1, K, R1 * K, K, out_stride_o, out_stride_k, identity};
         e = launch_cols(red, dtmid, dtout, a, l);
     }
     if (e != cudaSuccess) return e;
@@ -242,9 +245,19 @@ static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void*
     if (nr > 0 && nc == 3 && c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 &&
         c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 2 &&
         getenv("DACE_B200_NO_TWO_PASS") == nullptr) {
-        cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape,
-                                       (size_t)c[2].shape, (size_t)c[1].in_stride, (ptrdiff_t)c[1].out_stride,
+        cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, 1, (size_t)c[0].shape, (size_t)c[1].shape,
+                                       (size_t)c[2].shape, (size_t)c[1].in_stride, 0, (ptrdiff_t)c[1].out_stride,
                                        identity, l);
+        if (e2 != cudaErrorNotSupported) return e2;
+    }
+    // [O, R1, K, R2]: the same with an outer kept axis.
+    if (nr > 0 && nc == 4 && !c[0].reduced && c[1].reduced && !c[2].reduced && c[3].reduced && c[3].in_stride == 1 &&
+        c[2].in_stride >= c[3].shape && c[1].in_stride == c[2].in_stride * c[2].shape &&
+        c[0].in_stride == c[1].in_stride * c[1].shape && c[3].shape >= 2 && dtype_size(dtout) >= 4 &&
+        getenv("DACE_B200_NO_TWO_PASS") == nullptr) {
+        cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape,
+                                       (size_t)c[2].shape, (size_t)c[3].shape, (size_t)c[2].in_stride,
+                                       (ptrdiff_t)c[0].out_stride, (ptrdiff_t)c[2].out_stride, identity, l);
         if (e2 != cudaErrorNotSupported) return e2;
     }
     return cudaErrorNotSupported;
@@ -340,7 +353,11 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
         int sub_nr = 0;
         for (int i = 1; i < nc; ++i) sub_nr += c[i].reduced ? 1 : 0;
         const size_t isz = dtype_size(dtin), osz = dtype_size(dtout);
-        bool ok = sub_nr > 0;
+        size_t slice_elems = 1;
+        for (int i = 1; i < nc; ++i) slice_elems *= (size_t)c[i].shape;
+        // a reduced outer axis is where the strided kernel is weakest (one thread folds everything for its output);
+        // with a kept outer axis it keeps its warp-per-output mapping, so small slices are not worth their launches
+        bool ok = sub_nr > 0 && slice_elems * isz >= (c[0].reduced ? (size_t(1) << 20) : (size_t(32) << 20));
         for (long long i = 0; ok && i < c[0].shape; ++i) {
             const char* sin = static_cast<const char*>(in) + size_t(i) * size_t(c[0].in_stride) * isz;
             char* sout = static_cast<char*>(out) + (c[0].reduced ? 0 : ptrdiff_t(i) * c[0].out_stride * ptrdiff_t(osz));

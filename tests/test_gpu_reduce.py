@@ -507,3 +507,23 @@ def test_interleaved_axes_host_peel(dtype, shape, axes, cuda):
     _check(got, ref, dtype, a, axes, 'sum')
     got, ref = _run(a, axes, 'sum', cuda, identity=3)                          # a non-neutral identity, once
     _check(got, ref, dtype, a, axes, 'sum')
+
+
+@pytest.mark.parametrize('dtype', [np.float32, np.int32, np.float64])
+@pytest.mark.parametrize('shape', [[6, 5, 8, 300], [3, 70, 4, 33], [2, 2, 2, 2], [40, 3, 100, 1000]])
+def test_outer_kept_two_pass(dtype, shape, cuda):
+    """[O, R1, K, R2] over axes (1, 3) (per-sample, per-channel statistics): one rows pass over O*R1*K runs and one
+    column pass with O as the outer dimension."""
+    rng = np.random.default_rng(9)
+    a = _data(rng, shape, dtype, 'sum')
+    for op in ('sum', 'min'):
+        got, ref = _run(a, (1, 3), op, cuda)
+        _check(got, ref, dtype, a, (1, 3), op)
+    init = _data(rng, [shape[0], shape[2]], dtype, 'sum')
+    got, ref = _run(a, (1, 3), 'sum', cuda, identity=None, out_init=init)
+    _check(got, ref, dtype, a, (1, 3), 'sum')
+    # strided output (a transposed destination)
+    ta = torch.from_numpy(a).to(cuda)
+    out = torch.zeros(shape[2], shape[0], dtype=ta.dtype, device=cuda).t()
+    db.reduce('lambda a, b: a + b', ta, out, axis=(1, 3), identity=0)
+    _check(out.cpu().numpy(), O.reduce(O.SUM, a, (1, 3), identity=0, wide=True), dtype, a, (1, 3), 'sum')
