@@ -527,3 +527,22 @@ def test_outer_kept_two_pass(dtype, shape, cuda):
     out = torch.zeros(shape[2], shape[0], dtype=ta.dtype, device=cuda).t()
     db.reduce('lambda a, b: a + b', ta, out, axis=(1, 3), identity=0)
     _check(out.cpu().numpy(), O.reduce(O.SUM, a, (1, 3), identity=0, wide=True), dtype, a, (1, 3), 'sum')
+
+
+@pytest.mark.parametrize('K', [2, 3, 17, 100, 255, 256])
+@pytest.mark.parametrize('dtype', [np.float32, np.int32, np.float64])
+def test_narrow_dense_column_folds(K, dtype, cuda):
+    """[R, K <= 256] dense, axis 0: the flat-stream kernel (a thread's column never changes); deterministic."""
+    rng = np.random.default_rng(K)
+    R = (1 << 22) // K + 37
+    a = _data(rng, [R, K], dtype, 'sum')
+    for op in ('sum', 'max'):
+        got, ref = _run(a, (0, ), op, cuda)
+        _check(got, ref, dtype, a, (0, ), op)
+    init = _data(rng, [K], dtype, 'sum')
+    got, ref = _run(a, (0, ), 'sum', cuda, identity=None, out_init=init)
+    _check(got, ref, dtype, a, (0, ), 'sum')
+    ta = torch.from_numpy(a).to(cuda)
+    o1 = db.reduce('lambda a, b: a + b', ta, axis=(0, ), identity=0)
+    o2 = db.reduce('lambda a, b: a + b', ta, axis=(0, ), identity=0)
+    assert torch.equal(o1, o2)
