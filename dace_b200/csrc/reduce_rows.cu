@@ -63,10 +63,83 @@ static inline int pick_group(size_t row_bytes) {
     return G;
 }
 
+// Tiny dense rows ([R, n <= 128], rows back to back in memory, e.g. [N, 33] feature rows): a row is shorter than
+// one coalesced warp request, so the CTA treats its rows as one flat tile - 256 threads load kTinyTile elements with
+// scalar coalesced loads, every one of them issued before the first use (16 loads in flight per thread), into
+// shared memory; then warps fold rows out of shared memory, WIDTH lanes per row (conflict-free: a row is read by
+// consecutive lanes).  The lanes-per-row kernel above reaches 0.4-0.5 of the peak on such rows.
+constexpr int kTinyTile = 4096;            // elements per CTA tile
+constexpr int kTinyMaxN = 128;
+
+template <class L, class A, class S, class Op, int WIDTH>
+__global__ void __launch_bounds__(kRowThreads)
+rows_tiny_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, unsigned n, unsigned rows_per_tile,
+                 ptrdiff_t out_stride, Finish<A> fin) {
+    __shared__ L tile[kTinyTile];
+    constexpr int kPer = kTinyTile / kRowThreads;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned seg = lane / WIDTH, pos = lane % WIDTH;
+    constexpr unsigned kSegs = 32 / WIDTH;
+    const size_t ntiles = (rows + rows_per_tile - 1) / rows_per_tile;
+    for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const size_t row0 = t * rows_per_tile;
+        const unsigned nrows = (rows - row0 < rows_per_tile) ? unsigned(rows - row0) : rows_per_tile;
+        const unsigned count = nrows * n;
+        const L* src = in + row0 * n;
+        L v[kPer];
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            const unsigned i = threadIdx.x + unsigned(u) * kRowThreads;
+            if (i < count) v[u] = ldg_scalar(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            const unsigned i = threadIdx.x + unsigned(u) * kRowThreads;
+            if (i < count) tile[i] = v[u];
+        }
+        __syncthreads();
+        for (unsigned r = warp * kSegs + seg; r < nrows; r += (kRowThreads / 32) * kSegs) {
+            A acc = Op::neutral();
+            for (unsigned c = pos; c < n; c += WIDTH) acc = Op::apply(acc, to_acc<A, L>(tile[r * n + c]));
+            acc = warp_reduce<Op, A, WIDTH>(acc);
+            if (pos == 0) write_result<Op, A, S>(out + ptrdiff_t(row0 + r) * out_stride, acc, fin);
+        }
+        __syncthreads();
+    }
+}
+
+template <class T, class Op>
+static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
+    using L = typename T::L; using A = typename T::A; using S = typename T::S;
+    if (a.n > size_t(kTinyMaxN) || a.n < 2 || a.row_stride != a.n || a.rows * a.n < (size_t(1) << 22) ||
+        getenv("DACE_B200_NO_TINY_ROWS"))
+        return cudaErrorNotSupported;
+    const unsigned n = unsigned(a.n);
+    const unsigned rows_per_tile = kTinyTile / n;
+    const size_t ntiles = (a.rows + rows_per_tile - 1) / rows_per_tile;
+    size_t grid = size_t(sm_count()) * 8;
+    if (grid > ntiles) grid = ntiles;
+    Finish<A> fin = make_finish<A, S>(a.identity);
+#define DB200_TINY(W)                                                                                                   \
+    rows_tiny_kernel<L, A, S, Op, W><<<(unsigned)grid, kRowThreads, 0, l.stream>>>((const L*)a.in, (S*)a.out, a.rows, n, \
+                                                                                  rows_per_tile, a.out_stride, fin)
+    if (n <= 2) DB200_TINY(2);
+    else if (n <= 4) DB200_TINY(4);
+    else if (n <= 8) DB200_TINY(8);
+    else if (n <= 16) DB200_TINY(16);
+    else DB200_TINY(32);
+#undef DB200_TINY
+    return cudaGetLastError();
+}
+
 template <class T, class Op>
 static cudaError_t launch_rows_t(const RowsArgs& a, const Launch& l) {
     using L = typename T::L; using A = typename T::A; using S = typename T::S;
     constexpr int VB = 32;
+    {
+        cudaError_t e = launch_rows_tiny<T, Op>(a, l);
+        if (e != cudaErrorNotSupported) return e;
+    }
     Finish<A> fin = make_finish<A, S>(a.identity);
     const size_t row_bytes = a.n * sizeof(L);
     const int sms = sm_count();

@@ -546,3 +546,29 @@ def test_narrow_dense_column_folds(K, dtype, cuda):
     o1 = db.reduce('lambda a, b: a + b', ta, axis=(0, ), identity=0)
     o2 = db.reduce('lambda a, b: a + b', ta, axis=(0, ), identity=0)
     assert torch.equal(o1, o2)
+
+
+@pytest.mark.parametrize('n', [2, 3, 5, 8, 16, 17, 33, 100, 128])
+@pytest.mark.parametrize('dtype', [np.float32, np.int64, np.uint8, np.float64])
+def test_tiny_dense_rows(n, dtype, cuda):
+    """[R, n <= 128] dense, axis 1: rows staged through shared memory as one flat tile per CTA."""
+    rng = np.random.default_rng(n)
+    R = (1 << 22) // n + 41
+    a = _data(rng, [R, n], dtype, 'sum')
+    for op in ('sum', 'max'):
+        got, ref = _run(a, (1, ), op, cuda)
+        _check(got, ref, dtype, a, (1, ), op)
+    init = _data(rng, [R], dtype, 'sum')
+    got, ref = _run(a, (1, ), 'sum', cuda, identity=None, out_init=init)
+    _check(got, ref, dtype, a, (1, ), 'sum')
+
+
+def test_tiny_rows_bf16_to_f32_and_strided_out(cuda):
+    x = torch.randn((1 << 22) // 48 + 3, 48, device=cuda).to(torch.bfloat16)
+    out = torch.zeros(x.shape[0] * 2, dtype=torch.float32, device=cuda)[::2]
+    db.reduce('lambda a, b: a + b', x, out, axis=1, identity=0)
+    ref = x.double().sum(1)
+    scale = x.double().abs().sum(1)
+    assert bool(((out.double() - ref).abs() <= 1e-5 * scale + 1e-12).all())
+    mx = db.reduce('lambda a, b: max(a, b)', x, axis=1, identity=-3e38)
+    assert torch.equal(mx, x.amax(1))
