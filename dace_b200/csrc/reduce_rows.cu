@@ -98,11 +98,16 @@ rows_tiny_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, uns
             if (i < count) tile[i] = v[u];
         }
         __syncthreads();
-        for (unsigned r = warp * kSegs + seg; r < nrows; r += (kRowThreads / 32) * kSegs) {
+        // warp-uniform trip count: the shuffles inside warp_reduce need all 32 lanes, also those whose row is
+        // past the end of the tile
+        for (unsigned rb = warp * kSegs; rb < nrows; rb += (kRowThreads / 32) * kSegs) {
+            const unsigned r = rb + seg;
+            const bool valid = r < nrows;
             A acc = Op::neutral();
-            for (unsigned c = pos; c < n; c += WIDTH) acc = Op::apply(acc, to_acc<A, L>(tile[r * n + c]));
+            if (valid)
+                for (unsigned c = pos; c < n; c += WIDTH) acc = Op::apply(acc, to_acc<A, L>(tile[r * n + c]));
             acc = warp_reduce<Op, A, WIDTH>(acc);
-            if (pos == 0) write_result<Op, A, S>(out + ptrdiff_t(row0 + r) * out_stride, acc, fin);
+            if (valid && pos == 0) write_result<Op, A, S>(out + ptrdiff_t(row0 + r) * out_stride, acc, fin);
         }
         __syncthreads();
     }
