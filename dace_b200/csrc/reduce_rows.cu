@@ -78,8 +78,10 @@ rows_tiny_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, uns
     __shared__ L tile[kTinyTile];
     constexpr int kPer = kTinyTile / kRowThreads;
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const unsigned seg = lane / WIDTH, pos = lane % WIDTH;
-    constexpr unsigned kSegs = 32 / WIDTH;
+    constexpr int W = WIDTH < 2 ? 2 : WIDTH;
+    const unsigned seg = lane / W, pos = lane % W;
+    constexpr unsigned kSegs = 32 / W;
+    (void)seg; (void)pos; (void)warp;
     const size_t ntiles = (rows + rows_per_tile - 1) / rows_per_tile;
     for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
         const size_t row0 = t * rows_per_tile;
@@ -98,16 +100,31 @@ rows_tiny_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, uns
             if (i < count) tile[i] = v[u];
         }
         __syncthreads();
-        // warp-uniform trip count: the shuffles inside warp_reduce need all 32 lanes, also those whose row is
-        // past the end of the tile
-        for (unsigned rb = warp * kSegs; rb < nrows; rb += (kRowThreads / 32) * kSegs) {
-            const unsigned r = rb + seg;
-            const bool valid = r < nrows;
-            A acc = Op::neutral();
-            if (valid)
-                for (unsigned c = pos; c < n; c += WIDTH) acc = Op::apply(acc, to_acc<A, L>(tile[r * n + c]));
-            acc = warp_reduce<Op, A, WIDTH>(acc);
-            if (valid && pos == 0) write_result<Op, A, S>(out + ptrdiff_t(row0 + r) * out_stride, acc, fin);
+        if constexpr (WIDTH == 1) {
+            // a thread per row: n shared-memory reads at stride n words (conflict-free for odd n, 2-way for n = 2 mod 4)
+            for (unsigned r = threadIdx.x; r < nrows; r += kRowThreads) {
+                A a0 = Op::neutral(), a1 = Op::neutral();
+                const L* p = tile + r * n;
+                unsigned c = 0;
+                for (; c + 1 < n; c += 2) {
+                    a0 = Op::apply(a0, to_acc<A, L>(p[c]));
+                    a1 = Op::apply(a1, to_acc<A, L>(p[c + 1]));
+                }
+                if (c < n) a0 = Op::apply(a0, to_acc<A, L>(p[c]));
+                write_result<Op, A, S>(out + ptrdiff_t(row0 + r) * out_stride, Op::apply(a0, a1), fin);
+            }
+        } else {
+            // warp-uniform trip count: the shuffles inside warp_reduce need all 32 lanes, also those whose row is
+            // past the end of the tile
+            for (unsigned rb = warp * kSegs; rb < nrows; rb += (kRowThreads / 32) * kSegs) {
+                const unsigned r = rb + seg;
+                const bool valid = r < nrows;
+                A acc = Op::neutral();
+                if (valid)
+                    for (unsigned c = pos; c < n; c += WIDTH) acc = Op::apply(acc, to_acc<A, L>(tile[r * n + c]));
+                acc = warp_reduce<Op, A, WIDTH>(acc);
+                if (valid && pos == 0) write_result<Op, A, S>(out + ptrdiff_t(row0 + r) * out_stride, acc, fin);
+            }
         }
         __syncthreads();
     }
@@ -119,6 +136,7 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
     if (a.n > size_t(kTinyMaxN) || a.n < 2 || a.row_stride != a.n || a.rows * a.n < (size_t(1) << 22) ||
         getenv("DACE_B200_NO_TINY_ROWS"))
         return cudaErrorNotSupported;
+    if ((a.n * sizeof(L) / 4) % 4 == 0 && sizeof(L) >= 4) return cudaErrorNotSupported;   // stride would be >= 4-way bank conflicted
     const unsigned n = unsigned(a.n);
     const unsigned rows_per_tile = kTinyTile / n;
     const size_t ntiles = (a.rows + rows_per_tile - 1) / rows_per_tile;
@@ -128,11 +146,7 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
 #define DB200_TINY(W)                                                                                                   \
     rows_tiny_kernel<L, A, S, Op, W><<<(unsigned)grid, kRowThreads, 0, l.stream>>>((const L*)a.in, (S*)a.out, a.rows, n, \
                                                                                   rows_per_tile, a.out_stride, fin)
-    if (n <= 2) DB200_TINY(2);
-    else if (n <= 4) DB200_TINY(4);
-    else if (n <= 8) DB200_TINY(8);
-    else if (n <= 16) DB200_TINY(16);
-    else DB200_TINY(32);
+    DB200_TINY(1);
 #undef DB200_TINY
     return cudaGetLastError();
 }
