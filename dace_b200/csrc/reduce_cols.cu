@@ -474,19 +474,19 @@ static cudaError_t launch_cols_few_rows(const ColsArgs& a, const Launch& l) {
     return cudaGetLastError();
 }
 
-// Narrow dense matrices ([R, K] with K <= 256 columns, e.g. [N, 3] coordinates): the array is a flat stream
-// in which element i belongs to column i % K.  CTAs of B = floor(256 / K) * K threads walk it with a grid stride
+// Narrow dense matrices ([R, K] with K <= 1024 columns, e.g. [N, 3] coordinates): the array is a flat stream
+// in which element i belongs to column i % K.  CTAs of B = floor(256 / K) * K threads (1024 for K > 256) walk it with a grid stride
 // that is a multiple of K, so a thread's column never changes (column = tid % K): fully coalesced scalar loads,
 // one accumulator chain per thread, 8 loads in flight.  In-CTA combine in shared memory (fixed order), one partial
 // row per CTA in the workspace, and a warp per column folds the CTA partials (fixed order): deterministic.
 // The general kernel spends most lanes on padding here (measured 0.35-0.45 of the peak for K = 3 ... 100).
-constexpr int kNarrowMaxK = 256;
+constexpr int kNarrowMaxK = 1024;
 constexpr int kNarrowUnroll = 8;
 
 template <class L, class A, class Op>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 cols_narrow_kernel(const L* __restrict__ in, size_t total, unsigned K, A* __restrict__ partials) {
-    __shared__ A sm[256];
+    __shared__ A sm[1024];
     const unsigned B = blockDim.x;
     const size_t stride = size_t(gridDim.x) * B;
     A acc = Op::neutral();
@@ -528,9 +528,10 @@ static cudaError_t launch_cols_narrow(const ColsArgs& a, const Launch& l) {
         a.reduced * a.inner < (size_t(1) << 22) || l.ws.partials == nullptr || getenv("DACE_B200_NO_NARROW_COLS"))
         return cudaErrorNotSupported;
     const unsigned K = unsigned(a.inner);
-    const unsigned B = (256 / K) * K;
+    const unsigned tmax = K <= 256 ? 256 : 1024;          // CTA size: the largest multiple of K that fits
+    const unsigned B = (tmax / K) * K;
     const size_t total = a.reduced * a.inner;
-    size_t grid = size_t(sm_count()) * 8;
+    size_t grid = size_t(sm_count()) * (2048 / tmax);
     const size_t need = ceil_div(total, size_t(B) * kNarrowUnroll);
     if (grid > need) grid = need;
     if (grid * K * sizeof(A) > kPartialBytes) return cudaErrorNotSupported;

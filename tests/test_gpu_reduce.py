@@ -529,10 +529,10 @@ def test_outer_kept_two_pass(dtype, shape, cuda):
     _check(out.cpu().numpy(), O.reduce(O.SUM, a, (1, 3), identity=0, wide=True), dtype, a, (1, 3), 'sum')
 
 
-@pytest.mark.parametrize('K', [2, 3, 17, 100, 255, 256])
+@pytest.mark.parametrize('K', [2, 3, 17, 100, 255, 256, 257, 1000, 1024])
 @pytest.mark.parametrize('dtype', [np.float32, np.int32, np.float64])
 def test_narrow_dense_column_folds(K, dtype, cuda):
-    """[R, K <= 256] dense, axis 0: the flat-stream kernel (a thread's column never changes); deterministic."""
+    """[R, K <= 1024] dense, axis 0: the flat-stream kernel (a thread's column never changes); deterministic."""
     rng = np.random.default_rng(K)
     R = (1 << 22) // K + 37
     a = _data(rng, [R, K], dtype, 'sum')
