@@ -34,6 +34,10 @@ _PROTOTYPES = {
         _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_size_t, _c.c_size_t,
         _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p
     ]),
+    'dace_b200_reduce_rows_noalloc': (_c.c_int, [
+        _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_size_t, _c.c_size_t,
+        _c.c_void_p, _c.c_void_p
+    ]),
     'dace_b200_reduce_cols': (_c.c_int, [
         _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_size_t, _c.c_size_t,
         _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p

@@ -425,6 +425,13 @@ int dace_b200_reduce_rows(int redtype, int dtype_in, int dtype_out, const void* 
                                workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+int dace_b200_reduce_rows_noalloc(int redtype, int dtype_in, int dtype_out, const void* in, void* out,
+                                  size_t num_segments, size_t segment_size, size_t segment_stride,
+                                  const void* identity, dace_b200_stream_t stream) {
+    return (int)reduce_rows_noalloc(redtype, dtype_in, dtype_out, in, out, num_segments, segment_size, segment_stride,
+                                    identity, (cudaStream_t)stream);
+}
+
 int dace_b200_reduce_cols(int redtype, int dtype_in, int dtype_out, const void* in, void* out, size_t outer,
                           size_t reduced, size_t inner, const void* identity, void* workspace,
                           size_t workspace_bytes, dace_b200_stream_t stream) {

@@ -14,6 +14,11 @@ struct SplitArgs {
 };
 cudaError_t launch_split(int red, int dtin, int dtout, const SplitArgs& a, const Launch& l);
 
+// reduce_full.cu: the split kernel with tickets / partials in a file-scope __device__ array (no allocation anywhere
+// on the call path); rows <= 256.
+cudaError_t reduce_rows_noalloc(int red, int dtin, int dtout, const void* in, void* out, size_t rows, size_t n,
+                                size_t row_stride, const void* identity, cudaStream_t stream);
+
 // Segmented (row) reduction, one sub-warp / warp / CTA per row.
 struct RowsArgs {
     const void* in; void* out;

@@ -16,6 +16,8 @@
 //     run-to-run deterministic (no float atomics).
 // gridDim.y indexes independent rows (row_stride apart), so the same kernel
 // serves segmented reductions with few long segments.
+#include <cstdio>
+#include <mutex>
 #include "common.cuh"
 #include "span.cuh"
 #include "kernels.h"
@@ -154,6 +156,85 @@ cudaError_t launch_split(int red, int dtin, int dtout, const SplitArgs& a, const
             return launch_split_cfg<T, Op, 32, 4, 512>(a, l);
         });
     });
+}
+
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant (dace_b200_reduce_rows_noalloc in include/dace_b200_reduce.h): the
+// split kernel above with its tickets and partials in a file-scope device array instead of a
+// caller / library workspace, for callers that may not call cudaMalloc (stream capture, serving
+// loops).  The array lives in every GPU that loads this library until the process exits.  In host
+// code `g_noalloc_scratch` is only a stand-in for the symbol: the device address is looked up
+// once per device with cudaGetSymbolAddress (that device current) and handed to the kernel.
+// ---------------------------------------------------------------------------
+constexpr size_t kNoAllocMaxRows = 256;                                   // ticket counters
+constexpr size_t kNoAllocMaxPartials = 8192;                              // rows x clusters, 8 bytes each
+constexpr size_t kNoAllocCounterBytes = kNoAllocMaxRows * sizeof(unsigned);               // 1 KiB
+constexpr size_t kNoAllocScratchBytes = kNoAllocCounterBytes + kNoAllocMaxPartials * 8;   // 65 KiB
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+static std::mutex g_noalloc_mutex;
+static void* g_noalloc_ptr[64] = {nullptr};
+
+static cudaError_t noalloc_scratch(void** out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);   // device `dev` is current
+        if (e != cudaSuccess) return e;
+        if (p == nullptr) return cudaErrorInvalidSymbol;
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return cudaSuccess;
+}
+
+cudaError_t reduce_rows_noalloc(int red, int dtin, int dtout, const void* in, void* out, size_t rows, size_t n,
+                                size_t row_stride, const void* identity, cudaStream_t stream) {
+    if (red < RT_Min || red > RT_BXor) return cudaErrorNotSupported;
+    if (dispatch_types(dtin, dtout, [](auto) -> cudaError_t { return cudaSuccess; }) != cudaSuccess)
+        return cudaErrorNotSupported;
+    if (rows == 0) return cudaSuccess;
+    if (rows > kNoAllocMaxRows) {
+        fprintf(stderr,
+                "dace_b200_reduce_rows_noalloc: %zu segments exceed the maximum of %zu that the static device "
+                "scratch (%zu bytes) serves; use dace_b200_reduce_rows with a workspace\n",
+                rows, kNoAllocMaxRows, kNoAllocScratchBytes);
+        return cudaErrorInvalidValue;
+    }
+    if (!out || (n != 0 && !in)) return cudaErrorInvalidValue;
+    void* scratch = nullptr;
+    cudaError_t e = noalloc_scratch(&scratch);
+    if (e != cudaSuccess) return e;
+    Launch l;
+    l.stream = stream;
+    l.ws.counters = reinterpret_cast<unsigned*>(scratch);
+    l.ws.partials = static_cast<unsigned char*>(scratch) + kNoAllocCounterBytes;
+    if (n == 0) {   // empty range: outputs become the identity, or stay as they are without one
+        if (!identity) return cudaSuccess;
+        const long long ks[1] = {(long long)rows}, ko[1] = {1};
+        return launch_fill(dtout, out, 1, ks, ko, identity, l);
+    }
+    // The array is shared by every call and keeps the last call's contents: the tickets must start at zero.
+    e = cudaMemsetAsync(scratch, 0, kNoAllocCounterBytes, stream);
+    if (e != cudaSuccess) return e;
+    const size_t row_bytes = n * size_t(dtype_size(dtin));
+    const size_t sms = size_t(sm_count());
+    const int big = row_bytes * rows >= (size_t(256) << 20) && row_bytes >= (size_t(2) << 20);
+    const size_t tile = big ? (size_t(256) << 10) : (size_t(64) << 10);
+    size_t want = (row_bytes + tile - 1) / tile;
+    const size_t cap = ((big ? 1 : 2) * sms + rows - 1) / rows;     // CTAs resident at a time, per row
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    unsigned cluster = 1;
+    if (want >= 2) { cluster = 2; want = (want / 2) * 2; }
+    while (want > cluster && rows * (want / cluster) > kNoAllocMaxPartials) want -= cluster;
+    SplitArgs a{in, out, n, rows, row_stride, 1, (unsigned)want, cluster, identity, big};
+    return launch_split(red, dtin, dtout, a, l);
 }
 
 }  // namespace db200

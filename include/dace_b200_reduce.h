@@ -136,6 +136,21 @@ DACE_B200_API int dace_b200_reduce_rows(int redtype, int dtype_in, int dtype_out
                                         const void* identity, void* workspace, size_t workspace_bytes,
                                         dace_b200_stream_t stream);
 
+/* Allocation-free variant of dace_b200_reduce_rows for few, long segments (num_segments = 1 is a
+ * full reduction).  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  Same semantics and kernel as dace_b200_reduce_rows, but the cross-CTA
+ * tickets and partials live in a file-scope `static __device__` array of 66,560 bytes that every GPU
+ * loading the library holds until exit; the call path contains no cudaMalloc / cudaFree / allocating
+ * library routine (one cudaMemsetAsync on `stream` clears the tickets).  Limits: num_segments <= 256
+ * (more returns cudaErrorInvalidValue and prints the reason to stderr); any segment_size.  Every
+ * call on a device shares the one array: calls that may overlap on the GPU (different streams
+ * without ordering between them) race - serialise them or use dace_b200_reduce_rows with separate
+ * workspaces. */
+DACE_B200_API int dace_b200_reduce_rows_noalloc(int redtype, int dtype_in, int dtype_out, const void* in, void* out,
+                                                size_t num_segments, size_t segment_size, size_t segment_stride,
+                                                const void* identity, dace_b200_stream_t stream);
+
 /* Middle/leading axis reduced: in[outer][reduced][inner] (dense, inner
  * contiguous) -> out[outer][inner].  Replaces the GPUAuto strided schedule
  * (reference reduce.py:1141-1332); the CUB expansion has no equivalent
