@@ -21,6 +21,9 @@ _PROTOTYPES = {
     'dace_b200_status_string': (_c.c_char_p, [_c.c_int]),
     'dace_b200_workspace_bytes': (_c.c_size_t, []),
     'dace_b200_workspace_init': (_c.c_int, [_c.c_void_p, _c.c_size_t, _c.c_void_p]),
+    'dace_b200_reduce_nd_workspace_bytes': (_c.c_size_t, [
+        _c.c_int, _c.c_int, _c.c_int, _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64), _c.c_uint32
+    ]),
     'dace_b200_reduce_nd': (_c.c_int, [
         _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_int,
         _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64), _c.c_uint32, _c.c_void_p,
@@ -49,9 +52,11 @@ _PROTOTYPES = {
         _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_size_t, _c.c_size_t,
         _c.c_int64, _c.c_int64, _c.c_int64, _c.c_size_t, _c.c_size_t, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p
     ]),
+    'dace_b200_wcr_scatter_workspace_bytes': (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_size_t,
+                                                            _c.c_size_t]),
     'dace_b200_wcr_scatter': (_c.c_int, [
         _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_size_t, _c.c_void_p,
-        _c.c_size_t, _c.c_void_p
+        _c.c_size_t, _c.c_void_p, _c.c_size_t, _c.c_void_p
     ]),
     'dace_b200_peer_buffer_bytes': (_c.c_size_t, [_c.c_int, _c.c_size_t]),
     'dace_b200_peer_alloc': (_c.c_int, [_c.c_size_t, _c.POINTER(_c.c_void_p)]),

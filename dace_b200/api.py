@@ -93,20 +93,42 @@ def _stream_ptr(stream) -> int:
 
 
 class Workspace:
-    """Device workspace for cross-CTA combining: allocated once, reused
-    (the protocol of the reference's CUB temp storage,
-    reference dace/libraries/standard/nodes/reduce.py:550-570)."""
+    """Device workspace for cross-CTA combining (tickets + partials, plus optional extra scratch for the
+    two-pass plans): allocated by the CALLER - here with torch - once, reused; the protocol of the
+    reference's CUB temp storage (reference dace/libraries/standard/nodes/reduce.py:550-570).  The C ABI never
+    allocates.  One workspace serves one stream at a time."""
 
-    def __init__(self, device=None, stream=None):
+    def __init__(self, device=None, stream=None, nbytes: Optional[int] = None, zero_init: bool = True):
         lib = _lib.load()
-        self.nbytes = int(lib.dace_b200_workspace_bytes())
+        base = int(lib.dace_b200_workspace_bytes())
+        self.nbytes = max(int(nbytes), base if zero_init else 256) if nbytes is not None else base
         self.buffer = torch.empty(self.nbytes, dtype=torch.uint8, device=device or 'cuda')
-        _lib.check(lib.dace_b200_workspace_init(self.buffer.data_ptr(), self.nbytes, _stream_ptr(stream)),
-                   'dace_b200_workspace_init')
+        if zero_init:
+            _lib.check(lib.dace_b200_workspace_init(self.buffer.data_ptr(), self.nbytes, _stream_ptr(stream)),
+                       'dace_b200_workspace_init')
 
     @property
     def ptr(self) -> int:
         return self.buffer.data_ptr()
+
+
+# Default workspaces of this host API: one per (device, stream), created on first use and grown on demand
+# (before the C call, never inside it).  Outgrown buffers stay alive: kernels enqueued earlier may still use them.
+_WORKSPACES = {}
+_SCRATCH = {}
+_RETIRED = []
+
+
+def _default_workspace(cache, device: torch.device, stream_ptr: int, need: int, zero_init: bool) -> Workspace:
+    key = (device.index if device.index is not None else torch.cuda.current_device(), stream_ptr)
+    ws = cache.get(key)
+    if ws is None or ws.nbytes < need:
+        if ws is not None:
+            _RETIRED.append(ws)
+        with _on_device(device):
+            ws = Workspace(device, stream_ptr, nbytes=need, zero_init=zero_init)
+        cache[key] = ws
+    return ws
 
 
 def _require_cuda(t: torch.Tensor, what: str):
@@ -178,10 +200,14 @@ def reduce(op, in_array: torch.Tensor, out_array: Optional[torch.Tensor] = None,
     ident_buf = None
     if identity is not None:
         ident_buf = ctypes.create_string_buffer(scalar_bytes(identity, dt_out), 8)
-    ws_ptr, ws_bytes = (workspace.ptr, workspace.nbytes) if workspace is not None else (None, 0)
+    sptr = _stream_ptr(stream)
+    if workspace is None:
+        # shapes with >= 3 axes may have a two-pass plan that wants scratch behind the base workspace
+        need = int(lib.dace_b200_reduce_nd_workspace_bytes(dt_in, dt_out, nd, shape, istr, mask)) if nd >= 3 else 0
+        workspace = _default_workspace(_WORKSPACES, in_array.device, sptr, need, True)
     with _on_device(in_array.device):
         status = lib.dace_b200_reduce_nd(int(rt), dt_in, dt_out, in_array.data_ptr(), out_array.data_ptr(), nd,
-                                         shape, istr, ostr, mask, ident_buf, ws_ptr, ws_bytes, _stream_ptr(stream))
+                                         shape, istr, ostr, mask, ident_buf, workspace.ptr, workspace.nbytes, sptr)
     _lib.check(status, 'dace_b200_reduce_nd')
     return out_array if created else None
 
@@ -258,11 +284,13 @@ def _arg_reduce(red: int, in_array: torch.Tensor, axis, out_idx, out_val, init, 
             init = (info.min if red == int(ReductionType.Max_Location) else info.max) if info else \
                 (0 if red == int(ReductionType.Max_Location) else 1)
     ibuf = ctypes.create_string_buffer(scalar_bytes(init, dt_in), 8) if init is not None else None
-    ws_ptr, ws_bytes = (workspace.ptr, workspace.nbytes) if workspace is not None else (None, 0)
+    sptr = _stream_ptr(stream)
+    if workspace is None:
+        workspace = _default_workspace(_WORKSPACES, a.device, sptr, 0, True)
     with _on_device(a.device):
         status = lib.dace_b200_reduce_arg(red, dt_in, dtype_code(out_idx.dtype), a.data_ptr(), out_idx.data_ptr(),
                                           out_val.data_ptr() if out_val is not None else None, outer, reduced, inner,
-                                          so, sr, si, 0, 0, ibuf, ws_ptr, ws_bytes, _stream_ptr(stream))
+                                          so, sr, si, 0, 0, ibuf, workspace.ptr, workspace.nbytes, sptr)
     _lib.check(status, 'dace_b200_reduce_arg')
     return out_idx if created else None
 
@@ -286,7 +314,8 @@ def argmin(in_array: torch.Tensor, axis: Optional[int] = None, out_idx: Optional
                        workspace)
 
 
-def wcr_scatter(op, bins: torch.Tensor, indices: torch.Tensor, values=None, stream=None) -> None:
+def wcr_scatter(op, bins: torch.Tensor, indices: torch.Tensor, values=None, stream=None,
+                workspace: Optional[Workspace] = None) -> None:
     """``bins[indices[i]] = op(bins[indices[i]], values[i])`` - the WCR map
     ``out >> bins(1, wcr)[:]; out[idx] = v`` of reference
     samples/explicit/histogram.py:13-26 and ``hist[bin] += w`` of reference
@@ -308,9 +337,19 @@ def wcr_scatter(op, bins: torch.Tensor, indices: torch.Tensor, values=None, stre
         vptr = values.data_ptr()
     elif values is not None:
         cbuf = ctypes.create_string_buffer(scalar_bytes(values, dt_val), 8)
+    sptr = _stream_ptr(stream)
+    ws_ptr, ws_bytes = None, 0
+    if workspace is None and indices.numel() >= (1 << 22):
+        # large bin arrays: scratch of the radix-partition path (0 = the path does not apply)
+        need = int(lib.dace_b200_wcr_scatter_workspace_bytes(int(rt), dt_idx, dt_val, 1 if vptr else 0,
+                                                             indices.numel(), bins.numel()))
+        if need:
+            workspace = _default_workspace(_SCRATCH, bins.device, sptr, need, False)
+    if workspace is not None:
+        ws_ptr, ws_bytes = workspace.ptr, workspace.nbytes
     with _on_device(bins.device):
         status = lib.dace_b200_wcr_scatter(int(rt), dt_idx, dt_val, indices.data_ptr(), vptr, cbuf,
-                                           indices.numel(), bins.data_ptr(), bins.numel(), _stream_ptr(stream))
+                                           indices.numel(), bins.data_ptr(), bins.numel(), ws_ptr, ws_bytes, sptr)
     _lib.check(status, 'dace_b200_wcr_scatter')
 
 

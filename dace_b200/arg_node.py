@@ -26,7 +26,7 @@ from dace.symbolic import symstr
 from dace.transformation import transformation as xf
 from dace.transformation.transformation import ExpandTransformation
 
-from .expansion import B200Reduce, _DTYPE_CODES
+from .expansion import B200Reduce, _DTYPE_CODES, node_workspace
 from .redtypes import ReductionType
 
 _CODE_RE = re.compile(r'^\s*__out\s*=\s*_val_and_idx\(\s*idx\s*=\s*(\w+)\s*,\s*val\s*=\s*__in\s*\)\s*;?\s*$')
@@ -77,12 +77,13 @@ class ExpandArgReduceB200(ExpandTransformation):
         reduced = shape[axis]
         off_idx, off_val, size = _struct_layout(stype)
         red = int(ReductionType.Max_Location if node.func == 'max' else ReductionType.Min_Location)
+        ws, ws_bytes = node_workspace(sdfg, state, node)
         code = """
 DACE_GPU_CHECK((cudaError_t)dace_b200_reduce_arg({red}, {dtin}, {dtidx}, _in, (char *)_out + {off_idx}, (char *)_out + {off_val},
     (size_t)({outer}), (size_t)({reduced}), (size_t)({inner}), (int64_t)(({reduced}) * ({inner})), (int64_t)({inner}), (int64_t)1,
     (size_t){size}, (size_t){size}, nullptr /* fold into the pairs written by the init state */,
-    __state->dace_b200_workspace, dace_b200_workspace_bytes(), (dace_b200_stream_t)__dace_current_stream));
-""".format(red=red, dtin=_DTYPE_CODES[in_desc.dtype], dtidx=_IDX_CODES[idx_t], off_idx=off_idx, off_val=off_val,
+    {ws}, {ws_bytes}, (dace_b200_stream_t)__dace_current_stream));
+""".format(ws=ws, ws_bytes=ws_bytes, red=red, dtin=_DTYPE_CODES[in_desc.dtype], dtidx=_IDX_CODES[idx_t], off_idx=off_idx, off_val=off_val,
            outer=symstr(outer, cpp_mode=True), reduced=symstr(reduced, cpp_mode=True),
            inner=symstr(inner, cpp_mode=True), size=size)
         return nodes.Tasklet('arg_reduce_b200', {'_in': dace.pointer(in_desc.dtype)}, {'_out': dace.pointer(stype)}, code,

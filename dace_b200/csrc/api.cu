@@ -29,30 +29,34 @@ int sm_count() {
     return cached[dev];
 }
 
-static std::mutex g_ws_mutex;
-static void* g_default_ws[64] = {nullptr};
+static Tuning read_tuning() {
+    auto flag = [](const char* n) { return getenv(n) != nullptr; };
+    auto num = [](const char* n, int dflt) { const char* v = getenv(n); return v ? atoi(v) : dflt; };
+    Tuning t;
+    t.no_two_pass = flag("DACE_B200_NO_TWO_PASS");
+    t.no_axis_sort = flag("DACE_B200_NO_AXIS_SORT");
+    t.no_peel = flag("DACE_B200_NO_PEEL");
+    t.no_wide_cols = flag("DACE_B200_NO_WIDE_COLS");
+    t.no_few_rows = flag("DACE_B200_NO_FEW_ROWS");
+    t.no_narrow_cols = flag("DACE_B200_NO_NARROW_COLS");
+    t.no_partition = flag("DACE_B200_NO_PARTITION");
+    t.no_tiled = flag("DACE_B200_NO_TILED");
+    t.no_tiny_rows = flag("DACE_B200_NO_TINY_ROWS");
+    t.wide_wc = num("DACE_B200_WIDE_WC", 0);
+    t.part_chunk_log2 = num("DACE_B200_PART_CHUNK_LOG2", 0);
+    t.part_divert = num("DACE_B200_PART_DIVERT", -1);
+    return t;
+}
+static const Tuning g_tuning = read_tuning();   // at load time
+const Tuning& tuning() { return g_tuning; }
 
+// The workspace is the caller's (contract of include/dace_b200_reduce.h): nothing is allocated here.
 static cudaError_t resolve_workspace(void* workspace, size_t bytes, Launch& l) {
-    if (workspace != nullptr) {
-        if (bytes < kWorkspaceBytes) return cudaErrorInvalidValue;
-    } else {
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return e;
-        if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-        std::lock_guard<std::mutex> lock(g_ws_mutex);
-        if (g_default_ws[dev] == nullptr) {
-            void* p = nullptr;
-            e = cudaMalloc(&p, kWorkspaceBytes);
-            if (e != cudaSuccess) return e;
-            e = cudaMemset(p, 0, kCounterBytes);
-            if (e != cudaSuccess) { cudaFree(p); return e; }
-            g_default_ws[dev] = p;
-        }
-        workspace = g_default_ws[dev];
-    }
+    if (workspace == nullptr || bytes < kWorkspaceBytes) return cudaErrorInvalidValue;
     l.ws.counters = reinterpret_cast<unsigned*>(workspace);
     l.ws.partials = reinterpret_cast<char*>(workspace) + kCounterBytes;
+    l.extra = reinterpret_cast<char*>(workspace) + kWorkspaceBytes;
+    l.extra_bytes = bytes - kWorkspaceBytes;
     return cudaSuccess;
 }
 
@@ -143,16 +147,17 @@ static bool neutral_bytes(int red, int dt, unsigned char out[8]) {
     }
 }
 
-// Scratch between the passes of a two-pass plan: per device, grown on demand, kept; uses from
-// different streams are ordered by an event (same protocol as the partitioned scatter's scratch).
-struct MidScratch {
-    void* buf = nullptr;
-    size_t bytes = 0;
-    cudaEvent_t last = nullptr;
-};
-static std::mutex g_mid_mutex;
-static MidScratch g_mid[64];
+// Scratch between the passes of a two-pass plan: the part of the caller's workspace past the base
+// (dace_b200_reduce_nd_workspace_bytes() says how much a shape wants); a workspace without it sends
+// the shape to the slower scratch-free kernels.
 constexpr size_t kMidMaxBytes = size_t(256) << 20;
+
+static size_t two_pass_bytes(int dtin, int dtout, size_t O, size_t R1, size_t K) {
+    const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
+    const bool half_out = dtmid == DT_F32 && (dtout == DT_BF16 || dtout == DT_F16);
+    const size_t mid_bytes = (O * R1 * K * dtype_size(dtmid) + 255) & ~size_t(255);
+    return mid_bytes + (half_out ? ((O * K * sizeof(float) + 255) & ~size_t(255)) : 0);
+}
 
 // [R1, K, R2] with contiguous R2 (e.g. per-channel statistics of an [N, C, H*W] array: axes (0, 2)):
 // pass 1 folds every contiguous R2 run with the row kernels into mid[R1, K] (neutral seed),
@@ -171,48 +176,24 @@ static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, v
     // O > 1: an outer kept axis ([O, R1, K, R2] dense, e.g. per-sample per-channel statistics): the rows pass
     // covers O * R1 * K runs, the column pass folds R1 for every (o, k).
     const size_t mid_bytes = (O * R1 * K * dtype_size(dtmid) + 255) & ~size_t(255);
-    const size_t need = mid_bytes + (half_out ? O * K * sizeof(float) : 0);
-    if (need > kMidMaxBytes) return cudaErrorNotSupported;
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    if (dev < 0 || dev >= 64) return cudaErrorNotSupported;
-    std::lock_guard<std::mutex> lock(g_mid_mutex);
-    MidScratch& ms = g_mid[dev];
-    if (ms.last == nullptr) {
-        e = cudaEventCreateWithFlags(&ms.last, cudaEventDisableTiming);
-        if (e != cudaSuccess) return e;
-    } else {
-        e = cudaStreamWaitEvent(l.stream, ms.last, 0);
-        if (e != cudaSuccess) return e;
-    }
-    if (ms.bytes < need) {
-        if (ms.buf) {   // earlier users were ordered before this point by the event wait, but the free itself is immediate
-            e = cudaEventSynchronize(ms.last);
-            if (e != cudaSuccess) return e;
-            cudaFree(ms.buf);
-            ms.buf = nullptr; ms.bytes = 0;
-        }
-        const size_t alloc = std::max(need, size_t(4) << 20);
-        e = cudaMalloc(&ms.buf, alloc);
-        if (e != cudaSuccess) { ms.buf = nullptr; return e; }
-        ms.bytes = alloc;
-    }
-    e = plan_rows(red, dtin, dtmid, in, ms.buf, O * R1 * K, R2, row_stride, 1, neutral, l);
+    const size_t need = two_pass_bytes(dtin, dtout, O, R1, K);
+    if (need > kMidMaxBytes || need > l.extra_bytes) return cudaErrorNotSupported;
+    if (half_out && O != 1) return cudaErrorNotSupported;
+    void* mid = l.extra;
+    cudaError_t e;
+    e = plan_rows(red, dtin, dtmid, in, mid, O * R1 * K, R2, row_stride, 1, neutral, l);
     if (e != cudaSuccess) return e;
     if (half_out) {
-        float* tmp = reinterpret_cast<float*>(static_cast<char*>(ms.buf) + mid_bytes);
-        if (O != 1) return cudaErrorNotSupported;
-        ColsArgs a{ms.buf, tmp, 1, R1, K, 0, K, 0, 1, neutral};
+        float* tmp = reinterpret_cast<float*>(static_cast<char*>(mid) + mid_bytes);
+        ColsArgs a{mid, tmp, 1, R1, K, 0, K, 0, 1, neutral};
         e = launch_cols(red, DT_F32, DT_F32, a, l);
         if (e != cudaSuccess) return e;
         e = launch_finish_convert(red, dtout, tmp, out, K, out_stride_k, identity, l);
     } else {
-        ColsArgs a{ms.buf, out, O, R1, K, R1 * K, K, out_stride_o, out_stride_k, identity};
+        ColsArgs a{mid, out, O, R1, K, R1 * K, K, out_stride_o, out_stride_k, identity};
         e = launch_cols(red, dtmid, dtout, a, l);
     }
-    if (e != cudaSuccess) return e;
-    return cudaEventRecord(ms.last, l.stream);
+    return e;
 }
 
 // The canonical forms that have a streaming kernel; cudaErrorNotSupported = none of them.
@@ -244,7 +225,7 @@ static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void*
     // [R1, K, R2] with contiguous R2 and dense (R1, K): two streaming passes through a small scratch.
     if (nr > 0 && nc == 3 && c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 &&
         c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 2 &&
-        getenv("DACE_B200_NO_TWO_PASS") == nullptr) {
+        !tuning().no_two_pass) {
         cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, 1, (size_t)c[0].shape, (size_t)c[1].shape,
                                        (size_t)c[2].shape, (size_t)c[1].in_stride, 0, (ptrdiff_t)c[1].out_stride,
                                        identity, l);
@@ -254,7 +235,7 @@ static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void*
     if (nr > 0 && nc == 4 && !c[0].reduced && c[1].reduced && !c[2].reduced && c[3].reduced && c[3].in_stride == 1 &&
         c[2].in_stride >= c[3].shape && c[1].in_stride == c[2].in_stride * c[2].shape &&
         c[0].in_stride == c[1].in_stride * c[1].shape && c[3].shape >= 2 && dtype_size(dtout) >= 4 &&
-        getenv("DACE_B200_NO_TWO_PASS") == nullptr) {
+        !tuning().no_two_pass) {
         cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape,
                                        (size_t)c[2].shape, (size_t)c[3].shape, (size_t)c[2].in_stride,
                                        (ptrdiff_t)c[0].out_stride, (ptrdiff_t)c[2].out_stride, identity, l);
@@ -263,20 +244,16 @@ static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void*
     return cudaErrorNotSupported;
 }
 
-static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, void* out, int ndim,
-                                  const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,
-                                  uint32_t mask, const void* identity, void* workspace, size_t workspace_bytes,
-                                  cudaStream_t stream) {
+// Gather + canonicalise (shape, strides, axis mask): default output strides are C-contiguous over the kept axes;
+// unit dims are dropped, the axes put in memory order (largest input stride first, stable) and neighbours of
+// the same kind merged.  A fold does not care in which order the axes are walked and every kept axis carries
+// its own output stride, so transposed / permuted views (np.sum(A.T, axis=1), channels-last tensors)
+// canonicalise to the same [K, R] / [R, K] / [R1, K, R2] forms as their plain counterparts instead of
+// falling through to the strided kernel.
+static cudaError_t canonicalise(int ndim, const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,
+                                uint32_t mask, Dim* c, int& nc, size_t& nout, size_t& nred) {
     if (ndim < 0 || ndim > DACE_B200_MAX_DIMS) return cudaErrorInvalidValue;
     if (ndim > 0 && (!shape || !in_strides)) return cudaErrorInvalidValue;
-    if (red < RT_Min || red > RT_BXor) return cudaErrorNotSupported;
-    if (!supported_pair(dtin, dtout)) return cudaErrorNotSupported;
-    Launch l;
-    l.stream = stream;
-    cudaError_t e = resolve_workspace(workspace, workspace_bytes, l);
-    if (e != cudaSuccess) return e;
-
-    // Gather dims; default output strides are C-contiguous over the kept axes.
     Dim dims[DACE_B200_MAX_DIMS];
     long long kstride[DACE_B200_MAX_DIMS];
     {
@@ -286,7 +263,7 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
             if (!((mask >> i) & 1u)) { kstride[i] = s; s *= shape[i]; }
         }
     }
-    size_t nout = 1, nred = 1;
+    nout = 1; nred = 1;
     int kept_seen = 0;
     for (int i = 0; i < ndim; ++i) {
         if (shape[i] < 0) return cudaErrorInvalidValue;
@@ -300,23 +277,13 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
             nout *= (size_t)shape[i];
         }
     }
-    if (nout == 0) return cudaSuccess;
-    if (!out || (nred != 0 && !in)) return cudaErrorInvalidValue;  // empty tensors may carry null pointers
-
-    // Canonicalise: drop unit dims, merge mergeable neighbours of the same kind.
-    // A fold does not care in which order the axes are walked and every kept axis carries its own
-    // output stride, so the axes are first put in memory order (largest input stride first, stable):
-    // transposed / permuted views (np.sum(A.T, axis=1), channels-last tensors) then canonicalise to
-    // the same [K, R] / [R, K] / [R1, K, R2] forms as their plain counterparts instead of falling
-    // through to the strided kernel.
     Dim nz[DACE_B200_MAX_DIMS];
     int nnz = 0;
     for (int i = 0; i < ndim; ++i)
         if (dims[i].shape != 1) nz[nnz++] = dims[i];
-    if (getenv("DACE_B200_NO_AXIS_SORT") == nullptr)
+    if (!tuning().no_axis_sort)
         std::stable_sort(nz, nz + nnz, [](const Dim& a, const Dim& b) { return a.in_stride > b.in_stride; });
-    Dim c[DACE_B200_MAX_DIMS];
-    int nc = 0;
+    nc = 0;
     for (int i = 0; i < nnz; ++i) {
         if (nc > 0 && c[nc - 1].reduced == nz[i].reduced &&
             c[nc - 1].in_stride == nz[i].in_stride * nz[i].shape &&
@@ -328,6 +295,52 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
             c[nc++] = nz[i];
         }
     }
+    return cudaSuccess;
+}
+
+// Scratch a two-pass plan of the canonical form c[0..nc) would use (0 = the form has no two-pass plan).
+static size_t two_pass_need(int dtin, int dtout, const Dim* c, int nc) {
+    if (tuning().no_two_pass) return 0;
+    size_t need = 0;
+    if (nc == 3 && c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 &&
+        c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 2)
+        need = two_pass_bytes(dtin, dtout, 1, (size_t)c[0].shape, (size_t)c[1].shape);
+    if (nc == 4 && !c[0].reduced && c[1].reduced && !c[2].reduced && c[3].reduced && c[3].in_stride == 1 &&
+        c[2].in_stride >= c[3].shape && c[1].in_stride == c[2].in_stride * c[2].shape &&
+        c[0].in_stride == c[1].in_stride * c[1].shape && c[3].shape >= 2 && dtype_size(dtout) >= 4)
+        need = two_pass_bytes(dtin, dtout, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[2].shape);
+    return need <= kMidMaxBytes ? need : 0;
+}
+
+static size_t reduce_nd_workspace_bytes_impl(int dtin, int dtout, int ndim, const int64_t* shape,
+                                             const int64_t* in_strides, uint32_t mask) {
+    Dim c[DACE_B200_MAX_DIMS];
+    int nc = 0;
+    size_t nout = 0, nred = 0;
+    if (canonicalise(ndim, shape, in_strides, nullptr, mask, c, nc, nout, nred) != cudaSuccess || nout == 0 || nred == 0)
+        return kWorkspaceBytes;
+    size_t need = two_pass_need(dtin, dtout, c, nc);
+    if (need == 0 && nc >= 4) need = two_pass_need(dtin, dtout, c + 1, nc - 1);   // slices of a host-side peel
+    return kWorkspaceBytes + need;
+}
+
+static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, void* out, int ndim,
+                                  const int64_t* shape, const int64_t* in_strides, const int64_t* out_strides,
+                                  uint32_t mask, const void* identity, void* workspace, size_t workspace_bytes,
+                                  cudaStream_t stream) {
+    if (red < RT_Min || red > RT_BXor) return cudaErrorNotSupported;
+    if (!supported_pair(dtin, dtout)) return cudaErrorNotSupported;
+    Dim c[DACE_B200_MAX_DIMS];
+    int nc = 0;
+    size_t nout = 0, nred = 0;
+    cudaError_t e = canonicalise(ndim, shape, in_strides, out_strides, mask, c, nc, nout, nred);
+    if (e != cudaSuccess) return e;
+    if (nout == 0) return cudaSuccess;
+    if (!out || (nred != 0 && !in)) return cudaErrorInvalidValue;  // empty tensors may carry null pointers
+    Launch l;
+    l.stream = stream;
+    e = resolve_workspace(workspace, workspace_bytes, l);
+    if (e != cudaSuccess) return e;
 
     if (nred == 0) {
         // Empty range: outputs become the identity; without one they stay as they are.
@@ -349,7 +362,7 @@ static cudaError_t reduce_nd_impl(int red, int dtin, int dtout, const void* in, 
     // Interleaved kept / reduced axes ([R1, K1, R2, K2], [K1, R1, K2, R2], ...): peel the outermost axis on the host
     // when it is short and what remains has a streaming kernel - a reduced axis folds slice after slice into the
     // output (identity for the first slice, "fold into existing" for the rest), a kept axis writes slice by slice.
-    if (nr > 0 && nc >= 3 && c[0].shape <= 64 && c[0].in_stride >= 0 && getenv("DACE_B200_NO_PEEL") == nullptr) {
+    if (nr > 0 && nc >= 3 && c[0].shape <= 64 && c[0].in_stride >= 0 && !tuning().no_peel) {
         int sub_nr = 0;
         for (int i = 1; i < nc; ++i) sub_nr += c[i].reduced ? 1 : 0;
         const size_t isz = dtype_size(dtin), osz = dtype_size(dtout);
@@ -389,7 +402,7 @@ using namespace db200;
 
 extern "C" {
 
-int dace_b200_version(void) { return 1000; }
+int dace_b200_version(void) { return 2000; }
 
 const char* dace_b200_status_string(int status) { return cudaGetErrorString((cudaError_t)status); }
 
@@ -398,6 +411,11 @@ size_t dace_b200_workspace_bytes(void) { return kWorkspaceBytes; }
 int dace_b200_workspace_init(void* workspace, size_t workspace_bytes, dace_b200_stream_t stream) {
     if (!workspace || workspace_bytes < kWorkspaceBytes) return (int)cudaErrorInvalidValue;
     return (int)cudaMemsetAsync(workspace, 0, kCounterBytes, (cudaStream_t)stream);
+}
+
+size_t dace_b200_reduce_nd_workspace_bytes(int dtype_in, int dtype_out, int ndim, const int64_t* shape,
+                                           const int64_t* in_strides, uint32_t reduce_mask) {
+    return reduce_nd_workspace_bytes_impl(dtype_in, dtype_out, ndim, shape, in_strides, reduce_mask);
 }
 
 int dace_b200_reduce_nd(int redtype, int dtype_in, int dtype_out, const void* in, void* out, int ndim,
@@ -471,14 +489,22 @@ int dace_b200_reduce_arg(int redtype, int dtype_in, int dtype_idx, const void* i
     return (int)launch_arg(redtype, dtype_in, a, l);
 }
 
+size_t dace_b200_wcr_scatter_workspace_bytes(int redtype, int dtype_idx, int dtype_val, int has_values, size_t n,
+                                             size_t nbins) {
+    if (redtype != RT_Sum || tuning().no_partition) return 0;
+    return scatter_partition_bytes(dtype_idx, dtype_val, has_values != 0, n, nbins);
+}
+
 int dace_b200_wcr_scatter(int redtype, int dtype_idx, int dtype_val, const void* idx, const void* values,
-                          const void* const_value, size_t n, void* bins, size_t nbins,
-                          dace_b200_stream_t stream) {
+                          const void* const_value, size_t n, void* bins, size_t nbins, void* workspace,
+                          size_t workspace_bytes, dace_b200_stream_t stream) {
     if (n > 0 && (!idx || !bins)) return (int)cudaErrorInvalidValue;
     if (nbins == 0 || n == 0) return (int)cudaSuccess;
     Launch l;
     l.stream = (cudaStream_t)stream;
     l.ws.counters = nullptr; l.ws.partials = nullptr;
+    l.extra = workspace;                               // pure scratch for this entry point (may be NULL)
+    l.extra_bytes = workspace ? workspace_bytes : 0;
     ScatterArgs a{idx, values, const_value, n, bins, nbins};
     return (int)launch_scatter(redtype, dtype_idx, dtype_val, a, l);
 }

@@ -81,6 +81,14 @@ struct Comm {
     void* own = nullptr;
     void* bases[kMaxWorld] = {};
     unsigned long long epoch = 0;
+    // Collectives of one communicator are chained in issue order even when the caller enqueues them on
+    // different streams (independent AllReduceCombine nodes under DaCe's default stream assignment): the
+    // one-shot peer kernel relies on epochs arriving in order (two slots by parity, flags overwritten), and
+    // NCCL wants one order on every rank.
+    std::mutex order_mutex;
+    cudaEvent_t order = nullptr;
+    cudaStream_t last_stream = nullptr;
+    bool has_prev = false;
 };
 
 int fail(const char* what, int code) {
@@ -222,6 +230,7 @@ int dace_b200_comm_create(int rank, int world, const unsigned char* id128, void*
         memcpy(&id, id128, 128);
         int rc = nccl().CommInitRank(&c->nccl, world, id, rank);
         if (rc != 0) { delete c; return fail("ncclCommInitRank", rc); }
+        if (cudaEventCreateWithFlags(&c->order, cudaEventDisableTiming) != cudaSuccess) c->order = nullptr;
         setup_peer(c);
     }
     *comm = c;
@@ -290,6 +299,7 @@ int dace_b200_comm_destroy(void* comm) {
     }
     if (c->nccl) nccl().CommDestroy(c->nccl);   // collective: peers have unmapped before the buffer goes away
     if (c->own) cudaFree(c->own);
+    if (c->order) cudaEventDestroy(c->order);
     delete c;
     return 0;
 }
@@ -336,15 +346,30 @@ int dace_b200_comm_allreduce(void* comm, int redtype, int dtype, void* data, siz
                            dtype == DT_I64 || dtype == DT_U64;
     const bool peer_op = red == RT_Sum || red == RT_Product || red == RT_Min || red == RT_Max ||
                          ((red == RT_BAnd || red == RT_BOr || red == RT_BXor) && dtype != DT_F32 && dtype != DT_F64);
-    if (c->peer && peer_type && peer_op && nelem * esize <= kPeerCap) {
-        c->epoch += 1;
-        return (int)launch_peer_allreduce(red, dtype, data, nelem, c->bases, c->rank, c->world, c->epoch, kPeerCap,
-                                          (cudaStream_t)stream);
-    }
+    const bool use_peer = c->peer && peer_type && peer_op && nelem * esize <= kPeerCap;
     const int op = nccl_op(red), ty = nccl_type(dtype);
-    if (op < 0 || ty < 0) return (int)cudaErrorNotSupported;
-    int rc = nccl().AllReduce(data, data, nelem, ty, op, c->nccl, (cudaStream_t)stream);
-    return rc == 0 ? 0 : fail("ncclAllReduce", rc);
+    if (!use_peer && (op < 0 || ty < 0)) return (int)cudaErrorNotSupported;
+    std::lock_guard<std::mutex> lock(c->order_mutex);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (c->order && c->has_prev && s != c->last_stream) {
+        cudaError_t e = cudaStreamWaitEvent(s, c->order, 0);   // the previous collective, on whatever stream it ran
+        if (e != cudaSuccess) return (int)e;
+    }
+    int status;
+    if (use_peer) {
+        c->epoch += 1;
+        status = (int)launch_peer_allreduce(red, dtype, data, nelem, c->bases, c->rank, c->world, c->epoch, kPeerCap, s);
+    } else {
+        int rc = nccl().AllReduce(data, data, nelem, ty, op, c->nccl, s);
+        status = rc == 0 ? 0 : fail("ncclAllReduce", rc);
+    }
+    if (status == 0 && c->order) {
+        cudaError_t e = cudaEventRecord(c->order, s);
+        if (e != cudaSuccess) return (int)e;
+        c->last_stream = s;
+        c->has_prev = true;
+    }
+    return status;
 }
 
 }  // extern "C"

@@ -380,10 +380,32 @@ inline Finish<A> make_finish(const void* identity) {
 
 int sm_count();
 
-// Launch geometry shared by the kernels.
+// Launch context shared by the kernels: the stream and the caller's workspace (tickets + partials,
+// followed by whatever extra scratch the caller added on top of dace_b200_workspace_bytes()).
 struct Launch {
     cudaStream_t stream;
     Workspace ws;
+    void* extra = nullptr;       // scratch past the base workspace (two-pass `mid`, partition buffers)
+    size_t extra_bytes = 0;
+};
+
+// Experiment knobs (environment variables), read ONCE when the library is loaded - never on a call path.
+struct Tuning {
+    bool no_two_pass, no_axis_sort, no_peel, no_wide_cols, no_few_rows, no_narrow_cols, no_partition, no_tiled, no_tiny_rows;
+    int wide_wc;            // DACE_B200_WIDE_WC (0 = default)
+    int part_chunk_log2;    // DACE_B200_PART_CHUNK_LOG2 (0 = default)
+    int part_divert;        // DACE_B200_PART_DIVERT (-1 = default)
+};
+const Tuning& tuning();
+
+// Per-device "done once" flags for cudaFuncSetAttribute (function attributes are per device).
+struct PerDeviceOnce {
+    bool done[64] = {false};
+    bool* slot() {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+        return &done[dev];
+    }
 };
 
 }  // namespace db200

@@ -91,10 +91,10 @@ cudaError_t launch_peer_allreduce(int red, int dtype, void* data, size_t nelem, 
                                   unsigned long long epoch, size_t cap_bytes, cudaStream_t stream);
 size_t peer_buffer_bytes(int world, size_t cap_bytes);
 
-// On success *gate (may be null afterwards) is the device flag the partitioned kernel was gated on
-// (0 = it ran; 1 = the sampler found clustered keys and it returned at once): the caller then
-// launches the global-atomic kernel gated on 1 and calls scatter_partition_done().
+// On success *gate is the device flag the partitioned kernel was gated on (0 = it ran; 1 = the sampler
+// found clustered keys and it returned at once): the caller then launches the global-atomic kernel
+// gated on 1.  Scratch = l.extra (the caller's workspace, scatter_partition_bytes() large).
 cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l, const int** gate);
-cudaError_t scatter_partition_done(const Launch& l);
+size_t scatter_partition_bytes(int dtidx, int dtval, bool has_values, size_t n, size_t nbins);
 
 }  // namespace db200

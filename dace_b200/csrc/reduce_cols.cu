@@ -367,13 +367,13 @@ template <class T, class Op, int N>
 static cudaError_t launch_cols_wide(const ColsArgs& a, const Launch& l) {
     using L = typename T::L; using A = typename T::A; using S = typename T::S;
     constexpr int U = 8;
-    if (getenv("DACE_B200_NO_WIDE_COLS")) return cudaErrorNotSupported;
+    if (tuning().no_wide_cols) return cudaErrorNotSupported;
     const size_t colvecs = ceil_div(a.inner, N);
     if (colvecs < 128) return cudaErrorNotSupported;                 // rows narrower than 4 KiB
     // 4 warps (4 KiB) side by side measured best or within 1 % of best from 16 MiB to 8 GiB (tools/cols_sweep.py):
     // wider CTAs only make the partials bigger.
     int wc_max = 4;
-    if (const char* ev = getenv("DACE_B200_WIDE_WC")) wc_max = atoi(ev);   // tuning knob for experiments
+    if (tuning().wide_wc > 0) wc_max = tuning().wide_wc;   // tuning knob for experiments (read at load)
     int WC = 4;
     while (WC < wc_max && size_t(WC) * 32 < colvecs) WC <<= 1;
     const unsigned WR = kWideWarps / WC;
@@ -404,12 +404,12 @@ static cudaError_t launch_cols_wide(const ColsArgs& a, const Launch& l) {
     if (gz > 65535) return cudaErrorNotSupported;
     auto kern = cols_wide_kernel<L, A, S, Op, N, U>;
     const size_t smem = WR > 1 ? size_t(kWideThreads) * N * sizeof(A) : 0;
-    static bool attr_set = false;   // per instantiation
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;   // per instantiation and per device (function attributes are per device)
+    if (bool* done = attr_set.slot(); !*done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              int(size_t(kWideThreads) * N * sizeof(A)));
         if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }
-        attr_set = true;
+        *done = true;
     }
     Finish<A> fin = make_finish<A, S>(a.identity);
     kern<<<dim3((unsigned)splits, (unsigned)gy, (unsigned)gz), kWideThreads, smem, l.stream>>>(
@@ -463,7 +463,7 @@ template <class T, class Op>
 static cudaError_t launch_cols_few_rows(const ColsArgs& a, const Launch& l) {
     using L = typename T::L; using A = typename T::A; using S = typename T::S;
     if (a.reduced > size_t(kFewMaxRows) || a.outer > 65535 || a.inner < size_t(sm_count()) * kFewThreads * 2 ||
-        getenv("DACE_B200_NO_FEW_ROWS"))
+        tuning().no_few_rows)
         return cudaErrorNotSupported;
     size_t grid = ceil_div(a.inner, size_t(kFewThreads) * kFewCols);
     const size_t cap = size_t(sm_count()) * 8;
@@ -525,7 +525,7 @@ template <class T, class Op>
 static cudaError_t launch_cols_narrow(const ColsArgs& a, const Launch& l) {
     using L = typename T::L; using A = typename T::A; using S = typename T::S;
     if (a.outer != 1 || a.inner > size_t(kNarrowMaxK) || a.inner < 2 || a.in_stride_r != a.inner ||
-        a.reduced * a.inner < (size_t(1) << 22) || l.ws.partials == nullptr || getenv("DACE_B200_NO_NARROW_COLS"))
+        a.reduced * a.inner < (size_t(1) << 22) || l.ws.partials == nullptr || tuning().no_narrow_cols)
         return cudaErrorNotSupported;
     const unsigned K = unsigned(a.inner);
     const unsigned tmax = K <= 256 ? 256 : 1024;          // CTA size: the largest multiple of K that fits

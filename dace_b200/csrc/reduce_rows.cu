@@ -134,7 +134,7 @@ template <class T, class Op>
 static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
     using L = typename T::L; using A = typename T::A; using S = typename T::S;
     if (a.n > size_t(kTinyMaxN) || a.n < 2 || a.row_stride != a.n || a.rows * a.n < (size_t(1) << 22) ||
-        getenv("DACE_B200_NO_TINY_ROWS"))
+        tuning().no_tiny_rows)
         return cudaErrorNotSupported;
     if ((a.n * sizeof(L) / 4) % 4 == 0 && sizeof(L) >= 4) return cudaErrorNotSupported;   // stride would be >= 4-way bank conflicted
     const unsigned n = unsigned(a.n);

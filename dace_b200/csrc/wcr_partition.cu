@@ -32,7 +32,7 @@
 // fixed-slot staging with a warp-per-bucket copy-out, carrying phase-B loads through phase A.
 #include <algorithm>
 #include <cstdlib>
-#include <mutex>
+#include <cstring>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -275,46 +275,56 @@ __global__ void __launch_bounds__(1024) scatter_sample_kernel(const unsigned* __
     if (threadIdx.x == 0) *flag = (cnt >= 512) ? 1 : 0;
 }
 
-// Per-device scratch: the double-buffered partitioned keys and the per-chunk
-// bucket cursors.  Uses from different streams are serialised with an event.
-struct PartScratch {
-    unsigned* buf = nullptr;
-    unsigned* gcur = nullptr;
-    int* flag = nullptr;
-    size_t buf_words = 0;
-    cudaEvent_t last = nullptr;
-    int coop = -1;
+// Geometry + scratch layout of one partitioned call.  The scratch is the caller's
+// (dace_b200_wcr_scatter_workspace_bytes() / the `workspace` argument of dace_b200_wcr_scatter):
+//     [ flag: 256 B ][ per-chunk bucket cursors: nchunks x B words ][ double buffer: 2 x B x cap words ]
+struct PartPlan {
+    int B, S;
+    size_t chunk, nchunks;
+    unsigned cap;
+    size_t smem;
+    size_t gcur_off, buf_off, total;
 };
-static std::mutex g_part_mutex;
-static PartScratch g_part[64];
 
-template <class V>
-static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Launch& l, const int** gate_out) {
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    if (dev < 0 || dev >= 64) return cudaErrorNotSupported;
-    const int B = int((a.nbins + kBucketBins - 1) / kBucketBins);
+static bool part_plan(int dtidx, int dtval, bool has_values, size_t n, size_t nbins, PartPlan& p) {
+    if (has_values) return false;
+    if (dtidx != DT_I32 && dtidx != DT_U32) return false;
+    if (dtval != DT_I32 && dtval != DT_U32 && dtval != DT_F32) return false;
+    if (n < (size_t(1) << 22)) return false;
+    if (nbins * 4 <= (size_t(96) << 10) || nbins > size_t(kMaxBuckets) * kBucketBins) return false;
     const int sms = sm_count();
-    if (B > kMaxBuckets || B > sms) return cudaErrorNotSupported;
-    const int S = sms / B;
+    p.B = int((nbins + kBucketBins - 1) / kBucketBins);
+    if (p.B > kMaxBuckets || p.B > sms) return false;
+    p.S = sms / p.B;
     // every group of every CTA gets the same number of tiles per chunk (the grid barrier waits for the slowest)
     const size_t wave = size_t(sms) * kPartThreads * kKeysPerThread;
-    size_t chunk = wave * std::max<size_t>(1, (kChunkKeysDefault + wave / 2) / wave);
-    if (const char* ev = getenv("DACE_B200_PART_CHUNK_LOG2")) {   // tuning knob for experiments
-        const int lg = atoi(ev);
-        if (lg >= 20 && lg <= 26) chunk = wave * std::max<size_t>(1, ((size_t(1) << lg) + wave / 2) / wave);
-    }
-    const size_t nchunks = (a.n + chunk - 1) / chunk;
-    if (nchunks > kMaxChunks) return cudaErrorNotSupported;
+    p.chunk = wave * std::max<size_t>(1, (kChunkKeysDefault + wave / 2) / wave);
+    const int lg = tuning().part_chunk_log2;   // tuning knob for experiments (read at load)
+    if (lg >= 20 && lg <= 26) p.chunk = wave * std::max<size_t>(1, ((size_t(1) << lg) + wave / 2) / wave);
+    p.nchunks = (n + p.chunk - 1) / p.chunk;
+    if (p.nchunks > kMaxChunks) return false;
     // 1.5x the uniform share per bucket, multiple of 4 words so every bucket base stays 16-byte aligned
-    const unsigned cap = unsigned(((chunk * 3 / 2) / B + 3) & ~size_t(3));
-    const size_t smem = size_t(kBucketBins) * sizeof(V) + size_t(kGroups) * kTileKeys * sizeof(unsigned);
-    auto kern = scatter_partition_kernel<V>;
+    p.cap = unsigned(((p.chunk * 3 / 2) / p.B + 3) & ~size_t(3));
+    p.smem = size_t(kBucketBins) * 4 + size_t(kGroups) * kTileKeys * sizeof(unsigned);
+    p.gcur_off = 256;
+    p.buf_off = (p.gcur_off + p.nchunks * size_t(p.B) * sizeof(unsigned) + 255) & ~size_t(255);
+    p.total = p.buf_off + (2 * size_t(p.B) * p.cap + 8 * size_t(kMaxBuckets)) * sizeof(unsigned);
+    return true;
+}
 
-    std::lock_guard<std::mutex> lock(g_part_mutex);
-    PartScratch& ps = g_part[dev];
-    if (ps.coop < 0) {
+size_t scatter_partition_bytes(int dtidx, int dtval, bool has_values, size_t n, size_t nbins) {
+    PartPlan p;
+    return part_plan(dtidx, dtval, has_values, n, nbins, p) ? p.total : 0;
+}
+
+// Cooperative launch + 192 KiB of dynamic shared memory: checked once per device (-1 unknown, 0 no, 1 yes).
+static int g_part_coop[64];
+static bool g_part_coop_init = [] { for (int& v : g_part_coop) v = -1; return true; }();
+
+static bool partition_supported(size_t smem) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
+    if (g_part_coop[dev] < 0) {
         int coop = 0, occ = 0;
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
         if (coop) {
@@ -322,81 +332,55 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Laun
                 cudaFuncSetAttribute(scatter_partition_kernel<unsigned>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
                 cudaFuncSetAttribute(scatter_partition_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
                 coop = 0;
-            else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kPartThreads, smem) != cudaSuccess || occ < 1)
+            else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scatter_partition_kernel<int>, kPartThreads, smem) != cudaSuccess || occ < 1)
                 coop = 0;
         }
         cudaGetLastError();
-        ps.coop = coop;
+        g_part_coop[dev] = coop ? 1 : 0;
     }
-    if (!ps.coop) return cudaErrorNotSupported;
-    const size_t buf_words = 2 * size_t(B) * cap;
-    if (ps.buf == nullptr || ps.buf_words < buf_words) {
-        if (ps.buf) { cudaFree(ps.buf); ps.buf = nullptr; }
-        // 2 * 1.5 * chunk words (+ rounding slack for any B) = ~96 MiB
-        const size_t alloc_words = buf_words + 8 * size_t(kMaxBuckets);
-        e = cudaMalloc(&ps.buf, alloc_words * sizeof(unsigned));
-        if (e != cudaSuccess) { ps.buf = nullptr; return e; }
-        ps.buf_words = alloc_words;
-    }
-    if (ps.gcur == nullptr) {
-        e = cudaMalloc(&ps.gcur, kMaxChunks * size_t(kMaxBuckets) * sizeof(unsigned));
-        if (e != cudaSuccess) { ps.gcur = nullptr; return e; }
-    }
-    if (ps.flag == nullptr) {
-        e = cudaMalloc(&ps.flag, 256);
-        if (e != cudaSuccess) { ps.flag = nullptr; return e; }
-    }
-    if (ps.last == nullptr) {
-        e = cudaEventCreateWithFlags(&ps.last, cudaEventDisableTiming);
-        if (e != cudaSuccess) return e;
-    } else {
-        e = cudaStreamWaitEvent(l.stream, ps.last, 0);   // scratch is shared: order uses across streams
-        if (e != cudaSuccess) return e;
-    }
-    e = cudaMemsetAsync(ps.gcur, 0, nchunks * size_t(B) * sizeof(unsigned), l.stream);
-    if (e != cudaSuccess) return e;
+    return g_part_coop[dev] == 1;
+}
 
+template <class V>
+static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const PartPlan& p, const Launch& l,
+                                        const int** gate_out) {
+    unsigned char* base = static_cast<unsigned char*>(l.extra);
+    int* flag = reinterpret_cast<int*>(base);
+    unsigned* gcur = reinterpret_cast<unsigned*>(base + p.gcur_off);
+    unsigned* buf = reinterpret_cast<unsigned*>(base + p.buf_off);
+    cudaError_t e = cudaMemsetAsync(gcur, 0, p.nchunks * size_t(p.B) * sizeof(unsigned), l.stream);
+    if (e != cudaSuccess) return e;
     const unsigned* keys = reinterpret_cast<const unsigned*>(a.idx);
     size_t n = a.n;
-    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(keys, n, ps.flag);
-    const int* gate = ps.flag;
+    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(keys, n, flag);
+    const int* gate = flag;
     *gate_out = gate;
     V* bins = reinterpret_cast<V*>(a.bins);
     unsigned nbins = unsigned(a.nbins);
-    unsigned* buf = ps.buf;
-    unsigned* gcur = ps.gcur;
-    size_t chunk_arg = chunk;
-    unsigned cap_arg = cap;
-    int B_arg = B, S_arg = S;
+    size_t chunk_arg = p.chunk;
+    unsigned cap_arg = p.cap;
+    int B_arg = p.B, S_arg = p.S;
     int aligned = (reinterpret_cast<size_t>(a.idx) & 15) == 0;
-    int divert = kDivertDefault;
-    if (const char* ev = getenv("DACE_B200_PART_DIVERT")) divert = std::max(0, atoi(ev));   // tuning knob (0 = off)
+    int divert = tuning().part_divert >= 0 ? tuning().part_divert : kDivertDefault;   // tuning knob (0 = off)
     void* args[] = {&keys, &n, &bins, &nbins, &cval, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert};
-    e = cudaLaunchCooperativeKernel((void*)kern, dim3(sms), dim3(kPartThreads), args, smem, l.stream);
+    e = cudaLaunchCooperativeKernel((void*)scatter_partition_kernel<V>, dim3(sm_count()), dim3(kPartThreads), args,
+                                    p.smem, l.stream);
     if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }
-    return cudaSuccess;   // the event is recorded by scatter_partition_done(), after the gated global kernel
+    return cudaSuccess;
 }
 
-cudaError_t scatter_partition_done(const Launch& l) {
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    std::lock_guard<std::mutex> lock(g_part_mutex);
-    if (dev < 0 || dev >= 64 || g_part[dev].last == nullptr) return cudaErrorInvalidValue;
-    return cudaEventRecord(g_part[dev].last, l.stream);
-}
-
-// Returns cudaErrorNotSupported when the partitioned path does not apply (caller falls back
-// to the global-atomic kernel - still a GPU path).
+// Returns cudaErrorNotSupported when the partitioned path does not apply or the caller's scratch is too
+// small (caller falls back to the global-atomic kernel - still a GPU path).
 cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l, const int** gate) {
-    if (a.values != nullptr) return cudaErrorNotSupported;
-    if (dtidx != DT_I32 && dtidx != DT_U32) return cudaErrorNotSupported;
-    if (a.n < (size_t(1) << 22)) return cudaErrorNotSupported;
-    if (a.nbins * 4 <= (size_t(96) << 10) || a.nbins > size_t(kMaxBuckets) * kBucketBins) return cudaErrorNotSupported;
+    PartPlan p;
+    if (!part_plan(dtidx, dtval, a.values != nullptr, a.n, a.nbins, p)) return cudaErrorNotSupported;
+    if (l.extra == nullptr || l.extra_bytes < p.total || (reinterpret_cast<size_t>(l.extra) & 15) != 0)
+        return cudaErrorNotSupported;
+    if (!partition_supported(p.smem)) return cudaErrorNotSupported;
     switch (dtval) {
-        case DT_I32: { int c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<int>(a, c, l, gate); }
-        case DT_U32: { unsigned c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<unsigned>(a, c, l, gate); }
-        case DT_F32: { float c = 1.f; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<float>(a, c, l, gate); }
+        case DT_I32: { int c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<int>(a, c, p, l, gate); }
+        case DT_U32: { unsigned c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<unsigned>(a, c, p, l, gate); }
+        case DT_F32: { float c = 1.f; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<float>(a, c, p, l, gate); }
         default: return cudaErrorNotSupported;
     }
 }

@@ -308,7 +308,7 @@ static cudaError_t launch_scatter_val(int red, int dtval, const ScatterArgs& a, 
 }
 
 cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, const Launch& l) {
-    if (red == RT_Sum && getenv("DACE_B200_NO_PARTITION") == nullptr) {
+    if (red == RT_Sum && !tuning().no_partition) {
         const int* gate = nullptr;
         cudaError_t e = launch_scatter_partitioned(dtidx, dtval, a, l, &gate);
         if (e == cudaSuccess) {
@@ -318,9 +318,7 @@ cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, 
             ScatterArgs g = a;
             g.gate = gate;
             g.gate_run_if = 1;
-            e = (dtidx == DT_I32) ? launch_scatter_val<int>(red, dtval, g, l) : launch_scatter_val<unsigned>(red, dtval, g, l);
-            cudaError_t e2 = scatter_partition_done(l);
-            return e != cudaSuccess ? e : e2;
+            return (dtidx == DT_I32) ? launch_scatter_val<int>(red, dtval, g, l) : launch_scatter_val<unsigned>(red, dtval, g, l);
         }
         if (e != cudaErrorNotSupported) return e;
     }

@@ -34,7 +34,7 @@ from dace.sdfg import utils as sdutil
 from dace.symbolic import symstr
 from dace.transformation import transformation as xf
 
-from .expansion import B200Reduce
+from .expansion import B200FusedReduce, B200Reduce, node_workspace
 from .redtypes import ReductionType, detect_reduction_type, lower_custom
 
 _ACC_TYPES = (dace.float32, dace.float64, dace.int32, dace.int64, dace.uint32, dace.uint64)
@@ -49,25 +49,6 @@ _OPS = {ReductionType.Min, ReductionType.Max, ReductionType.Sum, ReductionType.P
         ReductionType.Bitwise_Or, ReductionType.Logical_Xor, ReductionType.Bitwise_Xor}
 _INT_ONLY = {ReductionType.Bitwise_And, ReductionType.Bitwise_Or, ReductionType.Bitwise_Xor}
 _GPU = (dtypes.StorageType.GPU_Global, dtypes.StorageType.CPU_Pinned)
-
-
-@dace.library.environment
-class B200FusedReduce:
-    """Header-only: puts ``dace_b200_fused_reduce.cuh`` into the generated .cu file; the workspace in the
-    state struct comes from ``B200Reduce``."""
-    cmake_minimum_version = None
-    cmake_packages = ["CUDA"]
-    cmake_variables = {}
-    cmake_includes = []
-    cmake_libraries = []
-    cmake_compile_flags = []
-    cmake_link_flags = []
-    cmake_files = []
-    headers = {'frame': [], 'cuda': ['dace_b200_fused_reduce.cuh']}
-    state_fields = []
-    init_code = ""
-    finalize_code = ""
-    dependencies = [B200Reduce]
 
 
 def _redtype(node: Reduce):
@@ -348,13 +329,15 @@ cudaError_t __b200_fused_{id}({sig}) {{
     frame_decl = 'DACE_EXPORTED cudaError_t __b200_fused_%s(%s);\n' % (ident, ', '.join(sig))
     call = ('DACE_GPU_CHECK(__b200_fused_%s(%s));' %
             (ident, ', '.join(['_in_' + a for a in arrays] + ['_out'] + syms +
-                              ['__state->dace_b200_workspace', 'dace_b200_workspace_bytes()', '__dace_current_stream'])))
+                              ['@B200_WS@', '@B200_WS_BYTES@', '__dace_current_stream'])))
     return cuda_code, frame_decl, call, arrays
 
 
 def _apply(graph, sdfg, m: _Match):
     """Replace the matched subgraph by one host tasklet that launches the generated kernel."""
     cuda_code, frame_decl, call, arrays = _generate(graph, sdfg, m)
+    ws, ws_bytes = node_workspace(sdfg, graph, m.entry)      # tickets + split partials of this kernel only
+    call = call.replace('@B200_WS@', ws).replace('@B200_WS_BYTES@', ws_bytes)
     entry, oe = m.entry, m.out_edge
     out_desc = sdfg.arrays[oe.data.data]
     in_conns = {'_in_' + a: dace.pointer(sdfg.arrays[a].dtype) for a in arrays}

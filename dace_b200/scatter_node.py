@@ -37,7 +37,11 @@ from dace.symbolic import symstr
 from dace.transformation import transformation as xf
 from dace.transformation.transformation import ExpandTransformation
 
-from .expansion import B200Reduce, _DTYPE_CODES, _resolve_redtype
+from .expansion import B200Reduce, _DTYPE_CODES, _resolve_redtype, node_workspace
+from .redtypes import ReductionType
+
+_SCATTER_OPS = {ReductionType.Sum, ReductionType.Min, ReductionType.Max, ReductionType.Product,
+                ReductionType.Bitwise_And, ReductionType.Bitwise_Or, ReductionType.Bitwise_Xor}
 
 _IDX_DTYPES = (dace.int32, dace.uint32, dace.int64, dace.uint8)
 _VAL_DTYPES = (dace.int32, dace.uint32, dace.int64, dace.uint64, dace.float32, dace.float64)
@@ -137,6 +141,9 @@ class ExpandScatterB200(ExpandTransformation):
             raise NotImplementedError('ScatterReduce expansion "B200": values (%s) and bins (%s) must have one dtype' %
                                       (sdfg.arrays[val_edge.data.data].dtype, bins_desc.dtype))
         redtype = _resolve_redtype(node.wcr)
+        if redtype not in _SCATTER_OPS:
+            # dace_b200_wcr_scatter has no logical operators: refuse here, not with cudaErrorNotSupported at run time
+            raise NotImplementedError('ScatterReduce expansion "B200": reduction type %s has no scatter kernel' % redtype.name)
         n, _, _ = _one_dim(idx_edge.data, 'index')
         nbins, _, _ = _one_dim(bins_edge.data, 'bins')
 
@@ -146,13 +153,21 @@ class ExpandScatterB200(ExpandTransformation):
             val_arg, const_arg = 'nullptr', '&__b200_const'
         else:
             const_decl, val_arg, const_arg = '', '_val', 'nullptr'
+        # Scratch of the radix-partition path (large bin arrays): sized in __dace_init from the SDFG's
+        # symbols, owned by this node; 0 bytes wanted = the path does not apply (a 256-byte stub is kept).
+        used = set(str(x) for v in (n, nbins) for x in getattr(v, 'free_symbols', ()))
+        ws, ws_bytes = node_workspace(
+            sdfg, state, node, symbols_used=used, zero_init=False,
+            bytes_code='__b200_need = dace_b200_wcr_scatter_workspace_bytes(%d, %d, %d, %d, (size_t)(%s), (size_t)(%s));'
+            % (int(redtype), _DTYPE_CODES[idx_desc.dtype], _DTYPE_CODES[bins_desc.dtype], 0 if val_edge is None else 1,
+               symstr(n, cpp_mode=True), symstr(nbins, cpp_mode=True)))
         code = """
 {const_decl}
 DACE_GPU_CHECK((cudaError_t)dace_b200_wcr_scatter({red}, {dtidx}, {dtval}, _idx, {val_arg}, {const_arg}, (size_t)({n}),
-    _bins, (size_t)({nbins}), (dace_b200_stream_t)__dace_current_stream));
+    _bins, (size_t)({nbins}), {ws}, {ws_bytes}, (dace_b200_stream_t)__dace_current_stream));
 """.format(const_decl=const_decl, red=int(redtype), dtidx=_DTYPE_CODES[idx_desc.dtype],
            dtval=_DTYPE_CODES[bins_desc.dtype], val_arg=val_arg, const_arg=const_arg,
-           n=symstr(n, cpp_mode=True), nbins=symstr(nbins, cpp_mode=True))
+           n=symstr(n, cpp_mode=True), nbins=symstr(nbins, cpp_mode=True), ws=ws, ws_bytes=ws_bytes)
         in_conns = {'_idx': dace.pointer(idx_desc.dtype)}
         if val_edge is not None:
             in_conns['_val'] = dace.pointer(bins_desc.dtype)

@@ -56,96 +56,137 @@ __host__ __device__ __forceinline__ A neutral() {
     }
 }
 
+/* What the kernels below need to know about an operator: the accumulator type, the functor, the seed of
+ * a thread's private accumulator, and the conversions at the two ends.  `builtin_ops` = the operators of
+ * dace::ReductionType with their neutral elements.  `custom_ops` = ANY associative + commutative functor
+ * `T f(const T&, const T&)` (custom WCR lambdas, reference dace/libraries/standard/nodes/reduce.py:453-463,
+ * dace/runtime/include/dace/reduction.h:56-164): such an operator has no known neutral element, so the
+ * accumulator carries a "holds a value" flag and empty accumulators are skipped when two are combined. */
+template <int RED, typename A_>
+struct builtin_ops {
+    using A = A_;
+    using functor = op<RED, A_>;
+    __host__ __device__ static __forceinline__ A seed() { return neutral<RED, A_>(); }
+    template <typename V> __device__ static __forceinline__ A from_value(const V& v) { return (A)v; }
+    template <typename S> __device__ static __forceinline__ S to_output(const A& a) { return (S)a; }
+    __host__ static A from_identity(const A_* identity) { return identity ? *identity : A_(0); }
+};
+
+template <typename T>
+struct maybe {   /* value + "holds a value" */
+    T v;
+    int has;
+};
+
+template <typename F, typename T>
+struct custom_ops {
+    using A = maybe<T>;
+    struct functor {
+        __device__ __forceinline__ A operator()(const A& a, const A& b) const {
+            if (!a.has) return b;
+            if (!b.has) return a;
+            return A{F()(a.v, b.v), 1};
+        }
+    };
+    __host__ __device__ static __forceinline__ A seed() { return A{T(), 0}; }
+    template <typename V> __device__ static __forceinline__ A from_value(const V& v) { return A{(T)v, 1}; }
+    template <typename S> __device__ static __forceinline__ S to_output(const A& a) { return (S)a.v; }
+    __host__ static A from_identity(const T* identity) { return identity ? A{*identity, 1} : A{T(), 0}; }
+};
+
 namespace detail {
 
 constexpr int kFusedThreads = 256;
 constexpr int kFusedUnroll = 4;
 
-template <int RED, typename A, typename S>
-__device__ __forceinline__ void fused_store(S* out, A v, A identity, int has_identity) {
-    const A base = has_identity ? identity : (A)(*out);
-    *out = (S)op<RED, A>()(base, v);
+template <typename P, typename S>
+__device__ __forceinline__ void fused_store(S* out, typename P::A v, typename P::A identity, int has_identity) {
+    const typename P::A base = has_identity ? identity : P::from_value(*out);
+    *out = P::template to_output<S>(typename P::functor()(base, v));
 }
 
 /* One CTA per (row, split): threads stride the columns of the split with kFusedUnroll independent
  * accumulators (that many loads in flight per thread), then a block tree. */
-template <int RED, typename A, typename S, typename Load>
+template <typename P, typename S, typename Load>
 __global__ void __launch_bounds__(kFusedThreads)
 fused_rows_cta_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t n, unsigned splits,
-                      A* __restrict__ partials, A identity, int has_identity) {
+                      typename P::A* __restrict__ partials, typename P::A identity, int has_identity) {
     const size_t row = blockIdx.y;
     const unsigned split = blockIdx.x;
     const size_t seg = (n + splits - 1) / splits;
     const size_t lo = size_t(split) * seg;
     const size_t hi = (lo + seg < n) ? lo + seg : n;
-    const op<RED, A> f;
+    using A = typename P::A;
+    const typename P::functor f;
     A acc[kFusedUnroll];
 #pragma unroll
-    for (int u = 0; u < kFusedUnroll; ++u) acc[u] = neutral<RED, A>();
+    for (int u = 0; u < kFusedUnroll; ++u) acc[u] = P::seed();
     size_t j = lo + threadIdx.x;
     for (; j + size_t(kFusedUnroll - 1) * kFusedThreads < hi; j += size_t(kFusedUnroll) * kFusedThreads) {
         A v[kFusedUnroll];
 #pragma unroll
-        for (int u = 0; u < kFusedUnroll; ++u) v[u] = (A)load(row, j + size_t(u) * kFusedThreads);
+        for (int u = 0; u < kFusedUnroll; ++u) v[u] = P::from_value(load(row, j + size_t(u) * kFusedThreads));
 #pragma unroll
         for (int u = 0; u < kFusedUnroll; ++u) acc[u] = f(acc[u], v[u]);
     }
-    for (; j < hi; j += kFusedThreads) acc[0] = f(acc[0], (A)load(row, j));
+    for (; j < hi; j += kFusedThreads) acc[0] = f(acc[0], P::from_value(load(row, j)));
     A r = block_reduce<A, kFusedThreads, 0x7f01>(acc, f);
     if (threadIdx.x == 0) {
-        if (splits == 1) fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
+        if (splits == 1) fused_store<P, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
         else partials[row * splits + split] = r;
     }
 }
 
 /* Short rows: a warp takes two rows at a time, four columns-of-32 each: eight loads in flight per lane. */
-template <int RED, typename A, typename S, typename Load>
+template <typename P, typename S, typename Load>
 __global__ void __launch_bounds__(kFusedThreads)
-fused_rows_warp_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, A identity,
+fused_rows_warp_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, typename P::A identity,
                        int has_identity) {
     const unsigned lane = threadIdx.x & 31;
     const size_t warps_per_grid = size_t(gridDim.x) * (kFusedThreads / 32);
-    const op<RED, A> f;
+    using A = typename P::A;
+    const typename P::functor f;
     for (size_t row = 2 * (size_t(blockIdx.x) * (kFusedThreads / 32) + (threadIdx.x >> 5)); row < rows;
          row += 2 * warps_per_grid) {
         const bool two = row + 1 < rows;
         const size_t row1 = two ? row + 1 : row;
         A a[4], b[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { a[u] = neutral<RED, A>(); b[u] = neutral<RED, A>(); }
+        for (int u = 0; u < 4; ++u) { a[u] = P::seed(); b[u] = P::seed(); }
         size_t j = lane;
         for (; j + 96 < n; j += 128) {
             A va[4], vb[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) va[u] = (A)load(row, j + 32 * u);
+            for (int u = 0; u < 4; ++u) va[u] = P::from_value(load(row, j + 32 * u));
 #pragma unroll
-            for (int u = 0; u < 4; ++u) vb[u] = (A)load(row1, j + 32 * u);
+            for (int u = 0; u < 4; ++u) vb[u] = P::from_value(load(row1, j + 32 * u));
 #pragma unroll
             for (int u = 0; u < 4; ++u) { a[u] = f(a[u], va[u]); b[u] = f(b[u], vb[u]); }
         }
         for (; j < n; j += 32) {
-            const A va = (A)load(row, j), vb = (A)load(row1, j);
+            const A va = P::from_value(load(row, j)), vb = P::from_value(load(row1, j));
             a[0] = f(a[0], va);
             b[0] = f(b[0], vb);
         }
         const A ra = warp_allreduce(f(f(a[0], a[1]), f(a[2], a[3])), f);
         const A rb = warp_allreduce(f(f(b[0], b[1]), f(b[2], b[3])), f);
         if (lane == 0) {
-            fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, ra, identity, has_identity);
-            if (two) fused_store<RED, A, S>(out + (ptrdiff_t)row1 * out_stride, rb, identity, has_identity);
+            fused_store<P, S>(out + (ptrdiff_t)row * out_stride, ra, identity, has_identity);
+            if (two) fused_store<P, S>(out + (ptrdiff_t)row1 * out_stride, rb, identity, has_identity);
         }
     }
 }
 
-template <int RED, typename A, typename S>
-__global__ void fused_finish_kernel(const A* __restrict__ partials, S* __restrict__ out, ptrdiff_t out_stride, size_t rows,
-                                    unsigned splits, A identity, int has_identity) {
+template <typename P, typename S>
+__global__ void fused_finish_kernel(const typename P::A* __restrict__ partials, S* __restrict__ out, ptrdiff_t out_stride, size_t rows,
+                                    unsigned splits, typename P::A identity, int has_identity) {
     const size_t row = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (row >= rows) return;
-    const op<RED, A> f;
+    using A = typename P::A;
+    const typename P::functor f;
     A r = partials[row * splits];
     for (unsigned s = 1; s < splits; ++s) r = f(r, partials[row * splits + s]);   /* fixed order */
-    fused_store<RED, A, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
+    fused_store<P, S>(out + (ptrdiff_t)row * out_stride, r, identity, has_identity);
 }
 
 /* Column fold: out[c] = fold over r of load(r, c).  A CTA owns 32 adjacent columns (one per lane, so the
@@ -153,10 +194,11 @@ __global__ void fused_finish_kernel(const A* __restrict__ partials, S* __restric
  * warp, warp + 8, ... with kFusedColUnroll rows in flight per warp. */
 constexpr int kFusedColUnroll = 8;
 
-template <int RED, typename A, typename S, typename Load>
+template <typename P, typename S, typename Load>
 __global__ void __launch_bounds__(kFusedThreads)
 fused_cols_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, unsigned splits,
-                  A* __restrict__ partials, A identity, int has_identity) {
+                  typename P::A* __restrict__ partials, typename P::A identity, int has_identity) {
+    using A = typename P::A;
     constexpr int kWarps = kFusedThreads / 32;
     __shared__ A tile[kWarps][33];
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -165,18 +207,18 @@ fused_cols_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t r
     const size_t seg = (rows + splits - 1) / splits;
     const size_t lo = size_t(split) * seg;
     const size_t hi = (lo + seg < rows) ? lo + seg : rows;
-    const op<RED, A> f;
-    A acc = neutral<RED, A>();
+    const typename P::functor f;
+    A acc = P::seed();
     if (col < n) {
         size_t r = lo + warp;
         for (; r + size_t(kFusedColUnroll - 1) * kWarps < hi; r += size_t(kFusedColUnroll) * kWarps) {
             A v[kFusedColUnroll];
 #pragma unroll
-            for (int u = 0; u < kFusedColUnroll; ++u) v[u] = (A)load(r + size_t(u) * kWarps, col);
+            for (int u = 0; u < kFusedColUnroll; ++u) v[u] = P::from_value(load(r + size_t(u) * kWarps, col));
 #pragma unroll
             for (int u = 0; u < kFusedColUnroll; ++u) acc = f(acc, v[u]);
         }
-        for (; r < hi; r += kWarps) acc = f(acc, (A)load(r, col));
+        for (; r < hi; r += kWarps) acc = f(acc, P::from_value(load(r, col)));
     }
     tile[warp][lane] = acc;
     __syncthreads();
@@ -184,41 +226,43 @@ fused_cols_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t r
         A r = tile[0][lane];
 #pragma unroll
         for (int w = 1; w < kWarps; ++w) r = f(r, tile[w][lane]);
-        if (splits == 1) fused_store<RED, A, S>(out + (ptrdiff_t)col * out_stride, r, identity, has_identity);
+        if (splits == 1) fused_store<P, S>(out + (ptrdiff_t)col * out_stride, r, identity, has_identity);
         else partials[size_t(split) * n + col] = r;
     }
 }
 
 /* Few rows, many columns: a thread per column, all rows of the slice in registers' reach. */
-template <int RED, typename A, typename S, typename Load>
+template <typename P, typename S, typename Load>
 __global__ void __launch_bounds__(kFusedThreads)
-fused_cols_thread_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, A identity,
+fused_cols_thread_kernel(Load load, S* __restrict__ out, ptrdiff_t out_stride, size_t rows, size_t n, typename P::A identity,
                          int has_identity) {
     const size_t col = size_t(blockIdx.x) * kFusedThreads + threadIdx.x;
     if (col >= n) return;
-    const op<RED, A> f;
-    A acc = neutral<RED, A>();
+    using A = typename P::A;
+    const typename P::functor f;
+    A acc = P::seed();
     size_t r = 0;
     for (; r + kFusedColUnroll <= rows; r += kFusedColUnroll) {
         A v[kFusedColUnroll];
 #pragma unroll
-        for (int u = 0; u < kFusedColUnroll; ++u) v[u] = (A)load(r + u, col);
+        for (int u = 0; u < kFusedColUnroll; ++u) v[u] = P::from_value(load(r + u, col));
 #pragma unroll
         for (int u = 0; u < kFusedColUnroll; ++u) acc = f(acc, v[u]);
     }
-    for (; r < rows; ++r) acc = f(acc, (A)load(r, col));
-    fused_store<RED, A, S>(out + (ptrdiff_t)col * out_stride, acc, identity, has_identity);
+    for (; r < rows; ++r) acc = f(acc, P::from_value(load(r, col)));
+    fused_store<P, S>(out + (ptrdiff_t)col * out_stride, acc, identity, has_identity);
 }
 
-template <int RED, typename A, typename S>
-__global__ void fused_cols_finish_kernel(const A* __restrict__ partials, S* __restrict__ out, ptrdiff_t out_stride, size_t n,
-                                         unsigned splits, A identity, int has_identity) {
+template <typename P, typename S>
+__global__ void fused_cols_finish_kernel(const typename P::A* __restrict__ partials, S* __restrict__ out, ptrdiff_t out_stride, size_t n,
+                                         unsigned splits, typename P::A identity, int has_identity) {
     const size_t col = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (col >= n) return;
-    const op<RED, A> f;
+    using A = typename P::A;
+    const typename P::functor f;
     A r = partials[col];
     for (unsigned s = 1; s < splits; ++s) r = f(r, partials[size_t(s) * n + col]);   /* fixed order, coalesced */
-    fused_store<RED, A, S>(out + (ptrdiff_t)col * out_stride, r, identity, has_identity);
+    fused_store<P, S>(out + (ptrdiff_t)col * out_stride, r, identity, has_identity);
 }
 
 inline int fused_sm_count() {
@@ -239,21 +283,20 @@ inline int fused_sm_count() {
  * (dace_b200/csrc/common.cuh kCounterBytes); the partials area behind them is free between calls. */
 constexpr size_t kWorkspaceCounterBytes = 16384;
 
-/* Host launcher.  `identity` is a HOST pointer (or nullptr: fold into `out`).  `workspace` /
- * `workspace_bytes`: the program's dace_b200 workspace; only needed when rows are split. */
-template <int RED, typename A, typename S, typename Load>
-inline cudaError_t fused_rows(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, const A* identity,
-                              void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+/* Host launchers.  `identity` is a HOST pointer (or nullptr: fold into `out`).  `workspace` /
+ * `workspace_bytes`: a dace_b200 workspace owned by the call site; only needed when rows are split. */
+template <typename P, typename S, typename Load>
+inline cudaError_t fused_rows_ops(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, typename P::A ident,
+                                  int has, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
     using namespace detail;
+    using A = typename P::A;
     if (rows == 0) return cudaSuccess;
-    const A ident = identity ? *identity : A(0);
-    const int has = identity ? 1 : 0;
     const size_t sms = (size_t)fused_sm_count();
     if (n < 2048 && rows >= 2 * sms) {
         size_t grid = ((rows + 1) / 2 + kFusedThreads / 32 - 1) / (kFusedThreads / 32);
         if (grid > sms * 8) grid = sms * 8;
-        fused_rows_warp_kernel<RED, A, S, Load><<<(unsigned)grid, kFusedThreads, 0, stream>>>(load, out, out_stride, rows, n,
-                                                                                          ident, has);
+        fused_rows_warp_kernel<P, S, Load><<<(unsigned)grid, kFusedThreads, 0, stream>>>(load, out, out_stride, rows, n,
+                                                                                      ident, has);
         return cudaGetLastError();
     }
     /* CTA per (row, split): aim at >= 4 CTAs per SM, at least 4096 elements per split */
@@ -272,31 +315,30 @@ inline cudaError_t fused_rows(Load load, S* out, ptrdiff_t out_stride, size_t ro
     }
     if (rows > 65535) {   /* gridDim.y limit: fall back to the warp kernel's row loop */
         size_t grid = sms * 8;
-        fused_rows_warp_kernel<RED, A, S, Load><<<(unsigned)grid, kFusedThreads, 0, stream>>>(load, out, out_stride, rows, n,
-                                                                                          ident, has);
+        fused_rows_warp_kernel<P, S, Load><<<(unsigned)grid, kFusedThreads, 0, stream>>>(load, out, out_stride, rows, n,
+                                                                                      ident, has);
         return cudaGetLastError();
     }
-    fused_rows_cta_kernel<RED, A, S, Load><<<dim3((unsigned)splits, (unsigned)rows), kFusedThreads, 0, stream>>>(
+    fused_rows_cta_kernel<P, S, Load><<<dim3((unsigned)splits, (unsigned)rows), kFusedThreads, 0, stream>>>(
         load, out, out_stride, n, (unsigned)splits, partials, ident, has);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess || splits == 1) return e;
-    fused_finish_kernel<RED, A, S><<<(unsigned)((rows + 127) / 128), 128, 0, stream>>>(partials, out, out_stride, rows,
-                                                                                    (unsigned)splits, ident, has);
+    fused_finish_kernel<P, S><<<(unsigned)((rows + 127) / 128), 128, 0, stream>>>(partials, out, out_stride, rows,
+                                                                               (unsigned)splits, ident, has);
     return cudaGetLastError();
 }
 
 /* out[c * out_stride] = fold(op, identity, load(0, c), ..., load(rows - 1, c))      c in [0, n) */
-template <int RED, typename A, typename S, typename Load>
-inline cudaError_t fused_cols(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, const A* identity,
-                              void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+template <typename P, typename S, typename Load>
+inline cudaError_t fused_cols_ops(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, typename P::A ident,
+                                  int has, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
     using namespace detail;
+    using A = typename P::A;
     if (n == 0) return cudaSuccess;
-    const A ident = identity ? *identity : A(0);
-    const int has = identity ? 1 : 0;
     const size_t sms = (size_t)fused_sm_count();
     if (rows <= 64 && n >= sms * kFusedThreads * 4) {
-        fused_cols_thread_kernel<RED, A, S, Load><<<(unsigned)((n + kFusedThreads - 1) / kFusedThreads), kFusedThreads, 0,
-                                                    stream>>>(load, out, out_stride, rows, n, ident, has);
+        fused_cols_thread_kernel<P, S, Load><<<(unsigned)((n + kFusedThreads - 1) / kFusedThreads), kFusedThreads, 0,
+                                               stream>>>(load, out, out_stride, rows, n, ident, has);
         return cudaGetLastError();
     }
     const size_t col_tiles = (n + 31) / 32;
@@ -315,13 +357,47 @@ inline cudaError_t fused_cols(Load load, S* out, ptrdiff_t out_stride, size_t ro
         if (splits > avail) splits = avail > 0 ? avail : 1;
         if (splits > 1) partials = reinterpret_cast<A*>(static_cast<char*>(workspace) + kWorkspaceCounterBytes);
     }
-    fused_cols_kernel<RED, A, S, Load><<<dim3((unsigned)col_tiles, (unsigned)splits), kFusedThreads, 0, stream>>>(
+    fused_cols_kernel<P, S, Load><<<dim3((unsigned)col_tiles, (unsigned)splits), kFusedThreads, 0, stream>>>(
         load, out, out_stride, rows, n, (unsigned)splits, partials, ident, has);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess || splits == 1) return e;
-    fused_cols_finish_kernel<RED, A, S><<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(partials, out, out_stride, n,
-                                                                                      (unsigned)splits, ident, has);
+    fused_cols_finish_kernel<P, S><<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(partials, out, out_stride, n,
+                                                                                 (unsigned)splits, ident, has);
     return cudaGetLastError();
+}
+
+/* Built-in operators (RED = dace::ReductionType value). */
+template <int RED, typename A, typename S, typename Load>
+inline cudaError_t fused_rows(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, const A* identity,
+                              void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    using P = builtin_ops<RED, A>;
+    return fused_rows_ops<P, S, Load>(load, out, out_stride, rows, n, P::from_identity(identity), identity ? 1 : 0,
+                                      workspace, workspace_bytes, stream);
+}
+template <int RED, typename A, typename S, typename Load>
+inline cudaError_t fused_cols(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, const A* identity,
+                              void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    using P = builtin_ops<RED, A>;
+    return fused_cols_ops<P, S, Load>(load, out, out_stride, rows, n, P::from_identity(identity), identity ? 1 : 0,
+                                      workspace, workspace_bytes, stream);
+}
+
+/* Custom WCR functor F (default-constructible, `T operator()(const T&, const T&) const`, associative and
+ * commutative like every DaCe WCR): what the `B200` expansion instantiates for ReductionType.Custom Reduce
+ * nodes, in place of cub::DeviceReduce::Reduce(..., __reduce_<id>(), identity) (reference reduce.py:453-468). */
+template <typename F, typename T, typename S, typename Load>
+inline cudaError_t fused_rows_custom(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, const T* identity,
+                                     void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    using P = custom_ops<F, T>;
+    return fused_rows_ops<P, S, Load>(load, out, out_stride, rows, n, P::from_identity(identity), identity ? 1 : 0,
+                                      workspace, workspace_bytes, stream);
+}
+template <typename F, typename T, typename S, typename Load>
+inline cudaError_t fused_cols_custom(Load load, S* out, ptrdiff_t out_stride, size_t rows, size_t n, const T* identity,
+                                     void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    using P = custom_ops<F, T>;
+    return fused_cols_ops<P, S, Load>(load, out, out_stride, rows, n, P::from_identity(identity), identity ? 1 : 0,
+                                      workspace, workspace_bytes, stream);
 }
 
 }  // namespace dace_b200

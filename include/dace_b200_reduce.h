@@ -16,7 +16,10 @@
  * Conventions (same as the reference's, reference dace/runtime/include/dace/cuda/cudacommon.cuh:28-83):
  *   - every entry point returns a cudaError_t value as int (0 = cudaSuccess), so
  *     the call site can stay wrapped in DACE_GPU_CHECK(...);
- *   - work is enqueued on `stream` and never synchronises the stream or device;
+ *   - work is enqueued on `stream`; the compute entry points never synchronise the stream or the
+ *     device and never allocate or free memory (no cudaMalloc / cudaFree / cudaEventSynchronize
+ *     and no getenv on any call path: they can be captured into a CUDA graph); every byte of
+ *     scratch they use is the caller's `workspace`;
  *   - `in`, `out`, `bins`... are device (or pinned, device-mapped) pointers owned
  *     by the caller, already offset to the memlet start; nothing is retained;
  *   - unsupported (op, dtype) combinations return cudaErrorNotSupported (801),
@@ -88,17 +91,24 @@ DACE_B200_API int dace_b200_version(void);
 DACE_B200_API const char* dace_b200_status_string(int status);
 
 /* ---- Workspace ---------------------------------------------------------
- * Cross-CTA combining uses a small device workspace (ticket counters +
- * partials).  Mirrors the reference's CUB temp-storage protocol: query the size,
+ * Cross-CTA combining uses a device workspace owned by the CALLER: ticket counters + partials
+ * (dace_b200_workspace_bytes() = 8 MiB, the "base"), optionally followed by more scratch for the
+ * plans that need it.  Mirrors the reference's CUB temp-storage protocol: query the size,
  * cudaMalloc once in __dace_init_cuda, cudaFree in __dace_exit_cuda
- * (reference dace/libraries/standard/nodes/reduce.py:550-570).  The workspace
- * must be zero-initialised once with dace_b200_workspace_init(); kernels leave
- * it clean.  Passing workspace == NULL selects a per-device default workspace the
- * library allocates on first use (not safe for concurrent use from several
- * streams; generated code passes its own).  One workspace serves one stream at
- * a time. */
+ * (reference dace/libraries/standard/nodes/reduce.py:550-570).  The base must be zero-initialised
+ * once with dace_b200_workspace_init(); kernels leave it clean.  One workspace serves one stream at
+ * a time: calls that may overlap on the GPU (independent nodes on different streams) need separate
+ * workspaces - the `B200` expansions allocate one per expanded node.  The library never allocates
+ * a workspace itself: workspace == NULL or workspace_bytes < the base is cudaErrorInvalidValue.
+ *
+ * dace_b200_reduce_nd_workspace_bytes(): bytes a workspace should have for dace_b200_reduce_nd to
+ * run this shape at full speed: the base, plus the intermediate of the two-pass plans ([R1, K, R2]
+ * and [O, R1, K, R2] forms).  With a smaller (base-only) workspace those shapes still work, through
+ * the slower scratch-free kernels.  Pure host arithmetic, no CUDA calls besides a cached device query. */
 DACE_B200_API size_t dace_b200_workspace_bytes(void);
 DACE_B200_API int dace_b200_workspace_init(void* workspace, size_t workspace_bytes, dace_b200_stream_t stream);
+DACE_B200_API size_t dace_b200_reduce_nd_workspace_bytes(int dtype_in, int dtype_out, int ndim, const int64_t* shape,
+                                                         const int64_t* in_strides, uint32_t reduce_mask);
 
 /* ---- Reduce library node -------------------------------------------------
  * General N-D entry, the call the `B200` expansion of
@@ -199,10 +209,18 @@ DACE_B200_API int dace_b200_reduce_arg(int redtype, int dtype_in, int dtype_idx,
  * place (WCR semantics: it is the caller's job to initialise it).  dtype_idx:
  * i32, u32, i64, u8; dtype_val (= bins type): i32, u32, i64, u64, f32, f64.
  * `values` may be NULL, then `const_value` (HOST pointer, dtype_val; NULL = 1) is
- * applied for every index.  Indices outside [0, nbins) are skipped. */
+ * applied for every index.  Indices outside [0, nbins) are skipped.
+ * `workspace` is pure scratch for this call (no initialisation needed, 16-byte aligned):
+ * dace_b200_wcr_scatter_workspace_bytes() says how much the radix-partition path wants for the given
+ * problem (0 = the path does not apply: small bin arrays, per-element values, 64-bit bins, < 2^22
+ * keys).  workspace == NULL or too small selects the global-atomic kernel instead (correct, slower
+ * for large bin arrays). */
+DACE_B200_API size_t dace_b200_wcr_scatter_workspace_bytes(int redtype, int dtype_idx, int dtype_val, int has_values,
+                                                           size_t n, size_t nbins);
 DACE_B200_API int dace_b200_wcr_scatter(int redtype, int dtype_idx, int dtype_val, const void* idx,
                                         const void* values, const void* const_value, size_t n, void* bins,
-                                        size_t nbins, dace_b200_stream_t stream);
+                                        size_t nbins, void* workspace, size_t workspace_bytes,
+                                        dace_b200_stream_t stream);
 
 /* ---- Multi-GPU combine of small partials over NVLink peer memory --------------
  * When the sharded axis is the reduced one, every GPU's local call above leaves a partial that

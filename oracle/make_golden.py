@@ -16,7 +16,10 @@ answers do: small seeded inputs + the outputs the reference produced for them.
 * arg_golden.npz - np.argmax / np.argmin through the frontend's struct-WCR lowering
   (reference tests/numpy/reductions_test.py:58-84), generated with one OpenMP thread.
 
-Usage (from a writable cwd):  PYTHONPATH=/root/repo python -m oracle.make_golden [--arg]
+* custom_golden.npz - custom WCR lambdas through the reference's `pure` expansion (reference
+  tests/custom_reduce_test.py and associative lambdas that are none of the built-in types).
+
+Usage (from a writable cwd):  PYTHONPATH=/root/repo python -m oracle.make_golden [--arg | --custom]
 """
 import json
 import os
@@ -292,6 +295,68 @@ def _arg_cases(dace):
     return out, meta
 
 
+# Custom WCR lambdas through the reference's `pure` expansion (the only CPU expansion that takes them,
+# reference reduce.py:27-154; CPU lowering = wcr_custom CAS loops, reduction.h:56-164).  The lambdas are
+# associative and commutative (every DaCe WCR must be), inputs avoid ties, so the results do not depend on the
+# thread interleaving.  Shared with tests/dace_e2e/build_programs.py, which builds the same SDFGs with 'B200'.
+CUSTOM_CASES = [
+    # tag, dtype, shape, axes, lambda, identity
+    ('app_i64_rows', 'int64', [33, 257], [1], 'lambda a, b: a + b + a * b', 0),
+    ('app_i64_cols', 'int64', [257, 33], [0], 'lambda a, b: a + b + a * b', 0),
+    ('app_i64_full', 'int64', [5001], None, 'lambda a, b: a + b + a * b', 0),
+    ('app_i64_lead2', 'int64', [9, 31, 40], [0, 1], 'lambda a, b: a + b + a * b', 7),
+    ('absmax_f32_rows', 'float32', [20, 300], [1], 'lambda a, b: a if abs(a) > abs(b) else b', 0),
+    ('absmax_f32_noident', 'float32', [300, 20], [0], 'lambda a, b: a if abs(a) > abs(b) else b', None),
+    ('refmin_f32_full', 'float32', [20], None, 'lambda a, b: a if a < b else b', 9999999),     # tests/custom_reduce_test.py:7-9
+]
+
+
+def custom_inputs(tag, dtype, shape):
+    rng = np.random.default_rng(sum(map(ord, tag)))
+    if dtype == 'int64':
+        return (rng.integers(-3, 4, shape) * 2).astype(np.int64)        # 1 + x is odd: prod(1 + x) never collapses to 0
+    return rng.uniform(-100, 100, shape).astype(np.float32)
+
+
+def _custom_cases(dace):
+    from oracle.build_ref import _reduce_sdfg
+    out, meta = {}, []
+    for tag, dtype, shape, axes, wcr, identity in CUSTOM_CASES:
+        dt = {'int64': dace.int64, 'float32': dace.float32}[dtype]
+        sdfg = _reduce_sdfg(dace, 'gc_' + tag, dt, dt, len(shape), axes, wcr, identity, 'pure')
+        data = custom_inputs(tag, dtype, shape)
+        kept = [s for i, s in enumerate(shape) if axes is not None and i not in axes] or [1]
+        init = None
+        if identity is None:
+            init = np.random.default_rng(1).uniform(-50, 50, kept).astype(data.dtype)
+        B = np.zeros(kept, data.dtype) if init is None else init.copy()
+        sdfg(A=data, B=B, **{'D%d' % i: s for i, s in enumerate(shape)})
+        out[tag + '__in'] = data
+        out[tag + '__out'] = B
+        if init is not None:
+            out[tag + '__init'] = init
+        meta.append({'tag': tag, 'dtype': dtype, 'shape': shape, 'axes': axes, 'wcr': wcr, 'identity': identity,
+                     'impl': 'pure'})
+    return out, meta
+
+
+def main_custom():
+    tmp = tempfile.mkdtemp(prefix='dace_b200_golden_')
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    try:
+        dace = import_reference(os.path.join(tmp, '.dacecache'))
+        assert dace is not None, 'reference checkout not available'
+        o, m = _custom_cases(dace)
+        np.savez_compressed(os.path.join(GOLDEN, 'custom_golden.npz'), **o)
+        with open(os.path.join(GOLDEN, 'custom_golden_meta.json'), 'w') as f:
+            json.dump({'reference_version': dace.__version__, 'custom': m}, f, indent=1)
+        print('wrote custom-lambda golden vectors to', GOLDEN)
+    finally:
+        os.chdir(cwd)
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
 def main_arg():
     os.environ['OMP_NUM_THREADS'] = '1'
     tmp = tempfile.mkdtemp(prefix='dace_b200_golden_')
@@ -343,6 +408,9 @@ if __name__ == '__main__':
     import sys
     if '--arg' in sys.argv:      # only the argmin/argmax vectors (the other files stay byte-identical)
         main_arg()
+    elif '--custom' in sys.argv:  # only the custom-lambda vectors
+        main_custom()
     else:
         main()
         main_arg()
+        main_custom()

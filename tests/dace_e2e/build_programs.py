@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 15
+VERSION = 17
 
 
 def up_to_date() -> bool:
@@ -81,7 +81,6 @@ def _programs(dace):
         ('b200_mid2_sum_f32', f32, f32, 4, [1, 2], add, 0),
         ('b200_outer_inner_sum_f64', f64, f64, 3, [0, 2], add, 0),
         ('b200_row_max_bf16_f32', bf16, f32, 2, [1], mx, -fmax),
-        ('b200_noident_col_max_f64', f64, f64, 2, [0], mx, None),
     ):
         sdfg = _reduce_sdfg(dace, name, din, dout, nd, axes, wcr, ident, 'B200')
         sdfg.apply_gpu_transformations()
@@ -111,6 +110,51 @@ def _programs(dace):
     r.implementation = 'B200'
     st.add_nedge(st.add_read('A'), r, dace.Memlet.from_array('A', sdfg.arrays['A']))
     st.add_nedge(r, st.add_write('B'), dace.Memlet.from_array('B', sdfg.arrays['B']))
+    progs.append(sdfg)
+
+    # (4b) identity=None folds into the output already on the device.  Device-resident on purpose: with host
+    #      arrays the reference's GPU transformation does not copy a write-only B in, so the fold would start
+    #      from whatever the fresh cudaMalloc holds.
+    sdfg = dace.SDFG('b200_noident_col_max_f64')
+    D1 = dace.symbol('D1', dace.int64)
+    sdfg.add_array('A', [D0, D1], f64, storage=dace.StorageType.GPU_Global)
+    sdfg.add_array('B', [D1], f64, storage=dace.StorageType.GPU_Global)
+    st = sdfg.add_state()
+    r = st.add_reduce(mx, [0], None)
+    r.implementation = 'B200'
+    st.add_nedge(st.add_read('A'), r, dace.Memlet.from_array('A', sdfg.arrays['A']))
+    st.add_nedge(r, st.add_write('B'), dace.Memlet.from_array('B', sdfg.arrays['B']))
+    progs.append(sdfg)
+
+    # (4c) Two independent large reductions in ONE state: DaCe's default stream assignment
+    #      (compiler.cuda.max_concurrent_streams = 0) puts them on different streams, so they may overlap on
+    #      the GPU - each expanded node owns its workspace (tickets + partials), nothing is shared.
+    sdfg = dace.SDFG('b200_two_reductions_one_state')
+    sdfg.add_array('A', [D0], f32, storage=dace.StorageType.GPU_Global)
+    sdfg.add_array('C', [D1, 4096], f32, storage=dace.StorageType.GPU_Global)
+    sdfg.add_array('s', [1], f32, storage=dace.StorageType.GPU_Global)
+    sdfg.add_array('cs', [4096], f32, storage=dace.StorageType.GPU_Global)
+    st = sdfg.add_state()
+    r1 = st.add_reduce(add, None, 0)
+    r2 = st.add_reduce(add, [0], 0)
+    r1.implementation = r2.implementation = 'B200'
+    st.add_nedge(st.add_read('A'), r1, dace.Memlet.from_array('A', sdfg.arrays['A']))
+    st.add_nedge(r1, st.add_write('s'), dace.Memlet.from_array('s', sdfg.arrays['s']))
+    st.add_nedge(st.add_read('C'), r2, dace.Memlet.from_array('C', sdfg.arrays['C']))
+    st.add_nedge(r2, st.add_write('cs'), dace.Memlet.from_array('cs', sdfg.arrays['cs']))
+    progs.append(sdfg)
+
+    # (4d) Host arrays with persistent device copies: the reference's make_transients_persistent
+    #      (reference dace/transformation/auto/auto_optimize.py:460-540) moves the cudaMalloc / cudaFree of gpu_A /
+    #      gpu_B from every call into __dace_init / __dace_exit; together with the per-node workspace nothing is
+    #      allocated on the call path.  This is the program bench.py times end to end.
+    from dace.transformation.auto.auto_optimize import make_transients_persistent
+    sdfg = _reduce_sdfg(dace, 'b200_full_sum_f32_persistent', f32, f32, 1, None, add, 0, 'B200')
+    sdfg.apply_gpu_transformations()
+    E.use_b200_reductions(sdfg)
+    made = make_transients_persistent(sdfg, dace.DeviceType.GPU)
+    if not any(made.values()):
+        raise RuntimeError('b200_full_sum_f32_persistent: no transient became persistent')
     progs.append(sdfg)
 
     # (5) WCR maps (scatter-add / histograms): unmodified @dace.programs; the map is rewritten into a
@@ -436,6 +480,18 @@ def _programs(dace):
         if FE.lower_wcr_maps(sdfg) != 1:
             raise RuntimeError('%s: WCRMapToFusedReduce did not apply' % sdfg.name)
         progs.append(sdfg)
+    # (14) Custom WCR lambdas on the device-level Reduce node (ReductionType.Custom): the lambda becomes a generated
+    #      functor instantiated with the header kernels (dace_b200/expansion.py:_expand_custom), as the reference's
+    #      CUB expansion does (reference reduce.py:453-468).  Same SDFGs as the golden vectors the reference's `pure`
+    #      expansion produced (oracle/make_golden.py CUSTOM_CASES), device-resident arrays.
+    from oracle.make_golden import CUSTOM_CASES
+    for tag, dtype, shape, axes, wcr, identity in CUSTOM_CASES:
+        dt = {'int64': dace.int64, 'float32': f32}[dtype]
+        sdfg = _reduce_sdfg(dace, 'b200_custom_' + tag, dt, dt, len(shape), axes, wcr, identity, 'B200')
+        for a in ('A', 'B'):
+            sdfg.arrays[a].storage = dace.StorageType.GPU_Global
+        progs.append(sdfg)
+
     return progs
 
 
@@ -498,7 +554,7 @@ def _compile_one(i):
         'lib': lib, 'args': args,
         'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
         'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') +
-        src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') + src.count('__b200_fused_') // 2 +
+        src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') + src.count('__b200_fused_') // 2 + src.count('DACE_GPU_CHECK(__b200_custom_') +
         cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
         'comm_calls': src.count('dace_b200_comm_allreduce('),
     }

@@ -23,6 +23,13 @@ struct MulLL {      // a[r, c] * w[c] on int64, sum-reduced (dot product with a 
     __device__ long long operator()(size_t r, size_t c) const { return a[r * ld + c] * w[c]; }
 };
 
+// Custom WCR functors (no known neutral element): the lambda of reference tests/custom_reduce_test.py:7-9
+// and an associative + commutative integer operator that is none of the built-ins (a + b + a * b).
+struct MinByCompare { template <typename T> __device__ T operator()(const T& a, const T& b) const { return a < b ? a : b; } };
+struct AddPlusProduct { template <typename T> __device__ T operator()(const T& a, const T& b) const { return a + b + a * b; } };
+struct PlainF { const float* x; size_t ld; __device__ float operator()(size_t r, size_t c) const { return x[r * ld + c]; } };
+struct PlainLL { const long long* x; size_t ld; __device__ long long operator()(size_t r, size_t c) const { return x[r * ld + c]; } };
+
 }  // namespace
 
 extern "C" __attribute__((visibility("default"))) int fused_reduce_harness_run(
@@ -46,6 +53,15 @@ extern "C" __attribute__((visibility("default"))) int fused_reduce_harness_run(
                    return fused_cols<kMax, int, int>(f, (int*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
         case 13: { const long long id = 11; MulLL f{(const long long*)in0, (const long long*)in1, (size_t)n};
                    return fused_cols<kSum, long long, long long>(f, (long long*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
+        /* custom functors: rows (20, 21) and columns (30, 31) */
+        case 20: { const float id = 9999999.f; PlainF f{(const float*)in0, (size_t)n};
+                   return fused_rows_custom<MinByCompare, float, float>(f, (float*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
+        case 21: { const long long id = 0; PlainLL f{(const long long*)in0, (size_t)n};
+                   return fused_rows_custom<AddPlusProduct, long long, long long>(f, (long long*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
+        case 30: { const float id = 9999999.f; PlainF f{(const float*)in0, (size_t)n};
+                   return fused_cols_custom<MinByCompare, float, float>(f, (float*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
+        case 31: { const long long id = 0; PlainLL f{(const long long*)in0, (size_t)n};
+                   return fused_cols_custom<AddPlusProduct, long long, long long>(f, (long long*)out, out_stride, rows, n, use_identity ? &id : nullptr, workspace, workspace_bytes, s); }
         default: return cudaErrorInvalidValue;
     }
 }

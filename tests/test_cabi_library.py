@@ -26,7 +26,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     for name in _declared():
         assert hasattr(lib, name), name
     lib = dace_b200.load()
-    assert lib.dace_b200_version() == 1000
+    assert lib.dace_b200_version() == 2000
     assert lib.dace_b200_workspace_bytes() == 8 << 20
     assert lib.dace_b200_status_string(801).decode() == 'operation not supported'
 
@@ -50,6 +50,33 @@ def test_no_product_code_touches_the_oracle():
             if f.endswith(('.py', '.cu', '.cuh', '.h')):
                 text = open(os.path.join(dirpath, f), errors='ignore').read()
                 assert 'oracle' not in text.lower(), os.path.join(dirpath, f)
+
+
+def test_compute_paths_neither_allocate_nor_synchronise_nor_read_the_environment():
+    """Contract of include/dace_b200_reduce.h: the kernel files and the planner contain no cudaMalloc / cudaFree /
+    synchronise / getenv.  Allowed exceptions: the peer-buffer setup entry points (dace_b200_peer_alloc / _free,
+    not compute calls) and the one-time read of the tuning knobs when the library is loaded (read_tuning)."""
+    csrc = os.path.join(ROOT, 'dace_b200', 'csrc')
+    banned = re.compile(r'\b(cudaMalloc\w*|cudaFree\w*|cudaEventSynchronize|cudaStreamSynchronize|cudaDeviceSynchronize|'
+                        r'cudaMemcpy|cudaMemset|getenv)\s*\(')
+    for f in sorted(os.listdir(csrc)):
+        if not f.endswith(('.cu', '.cuh', '.h')) or f == 'comm.cu':     # comm.cu = communicator set-up (NCCL, IPC)
+            continue
+        text = open(os.path.join(csrc, f)).read()
+        text = re.sub(r'//[^\n]*', '', text)
+        if f == 'api.cu':
+            a, b = text.index('static Tuning read_tuning()'), text.index('static const Tuning g_tuning')
+            text = text[:a] + text[b:]
+            a, b = text.index('int dace_b200_peer_alloc('), text.index('int dace_b200_peer_export(')
+            text = text[:a] + text[b:]
+        hits = banned.findall(text)
+        assert not hits, (f, hits)
+    # the shared library's compute entry points carry their scratch in the signature
+    src = open(HEADER).read()
+    for fn in ('dace_b200_reduce_nd', 'dace_b200_reduce_full', 'dace_b200_reduce_rows', 'dace_b200_reduce_cols',
+               'dace_b200_reduce_arg', 'dace_b200_wcr_scatter'):
+        proto = re.search(r'DACE_B200_API int %s\((.*?)\);' % fn, src, re.S).group(1)
+        assert 'void* workspace' in proto and 'size_t workspace_bytes' in proto, fn
 
 
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):

@@ -53,7 +53,7 @@ def test_map_body_becomes_a_load_functor(dace):
     assert 'struct __b200_load_fused_cg_' in cu and 'const float __in1 = gpu_A[__flat];' in cu
     assert 'const float __in2 = gpu_mx[i];' in cu and '__out = exp(__in1);' in cu
     assert 'dace_b200::fused_rows<3, float, float>(__load, __out, (ptrdiff_t)1, (size_t)(N), (size_t)(M), &__identity' in cu
-    assert 'DACE_GPU_CHECK(__b200_fused_fused_cg_' in frame and '__state->dace_b200_workspace' in frame
+    assert 'DACE_GPU_CHECK(__b200_fused_fused_cg_' in frame and ', __b200_ws_fused_cg_' in frame     # per-kernel workspace
     assert '__global__' not in cu.split('struct __b200_load_')[0] or 'reduce_atomic' not in cu   # no WCR map kernel
     assert FE.fuse_maps_into_reductions(sdfg) == 0
 

@@ -52,18 +52,24 @@ def test_generated_code_calls_the_c_abi(dace):
     import re
     istr = re.search(r'__b200_istr\[\] = \{(.*?)\};', frame).group(1).replace(' ', '')
     assert istr in ('(int64_t)(D1*D2),(int64_t)(D2),(int64_t)(1)', '(int64_t)((D1*D2)),(int64_t)(D2),(int64_t)(1)')
-    assert ', 2u, &__b200_identity, __state->dace_b200_workspace' in frame
+    import re
+    m = re.search(r', 2u, &__b200_identity, (__b200_ws_\w+), \1_bytes,', frame)
+    assert m, 'the call passes the workspace owned by this node'
+    ws = m.group(1)
     assert '__dace_current_stream' in frame
-    assert 'void *dace_b200_workspace = nullptr;' in frame            # state struct field
-    assert 'dace_b200_workspace_init(__state->dace_b200_workspace' in frame   # init once, like the CUB storage
-    assert 'cudaFree(__state->dace_b200_workspace)' in frame
+    assert 'void *%s = nullptr; size_t %s_bytes = 0;' % (ws, ws) in frame        # per-node storage, like CUB's
+    assert '__b200_need = dace_b200_reduce_nd_workspace_bytes(0, 0, 3, __b200_shape, __b200_istr, 2u);' in frame
+    assert 'cudaMalloc(&%s, %s_bytes)' % (ws, ws) in frame                       # allocated once in __dace_init
+    assert 'dace_b200_workspace_init(%s, %s_bytes, nullptr)' % (ws, ws) in frame
+    assert 'cudaFree(%s)' % ws in frame                                          # freed in __dace_exit
+    assert '__state->dace_b200_workspace' not in frame
     assert 'cub::' not in ''.join(code.values())
 
 
 def test_identity_none_passes_null(dace):
     sdfg = _sdfg(dace, 'b200_codegen_noident', [0], 'lambda a, b: max(a, b)', None)
     frame = ''.join(c.clean_code for c in sdfg.generate_code())
-    assert 'dace_b200_reduce_nd(2, 0, 0,' in frame and ', 1u, nullptr, __state->dace_b200_workspace' in frame
+    assert 'dace_b200_reduce_nd(2, 0, 0,' in frame and ', 1u, nullptr, __b200_ws_b200_codegen_noident_' in frame
 
 
 def test_environment_links_the_prebuilt_library(dace):

@@ -148,7 +148,12 @@ def test_b200_expansion_emits_the_c_abi_call(env):
     frame = next(v for k, v in code.items() if 'Frame' in k or k == 'b200_scatter_codegen')
     assert 'dace_b200_reduce.h' in frame
     assert 'DACE_GPU_CHECK((cudaError_t)dace_b200_wcr_scatter(3, 2, 0, _idx, _val, nullptr, (size_t)(N),' in frame
-    assert '_bins, (size_t)(M), (dace_b200_stream_t)__dace_current_stream));' in frame
+    import re
+    m = re.search(r'_bins, \(size_t\)\(M\), (__b200_ws_\w+), \1_bytes, \(dace_b200_stream_t\)__dace_current_stream\)\);', frame)
+    assert m, 'the call passes the scratch owned by this node'
+    # sized in __dace_init from the program's symbols (per-element values: the query answers 0, a stub is kept)
+    assert '__b200_need = dace_b200_wcr_scatter_workspace_bytes(3, 2, 0, 1, (size_t)(N), (size_t)(M));' in frame
+    assert 'cudaMalloc(&%s, %s_bytes)' % (m.group(1), m.group(1)) in frame and 'cudaFree(%s)' % m.group(1) in frame
     assert 'reduce_atomic' not in ''.join(code.values())      # the per-element atomic kernel is gone
     assert not any(k.endswith('cuda') and 'hist_weighted' in v and '__global__' in v for k, v in code.items())
 

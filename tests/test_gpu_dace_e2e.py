@@ -99,10 +99,53 @@ def test_bf16_rows_fp32_out(cuda):
 
 
 def test_identity_none_folds_into_output(cuda):
-    a = np.random.default_rng(5).uniform(-1, 1, (400, 60))
-    b = np.full(60, 0.5)
-    prog('b200_noident_col_max_f64')(A=a, B=b, D0=400, D1=60)
-    np.testing.assert_array_equal(b, np.maximum(0.5, a.max(0)))
+    """identity=None: the fold starts from what the output holds (reference operations.py:251).  Device-resident
+    arrays, so the starting values are really there (the reference's GPU transformation does not copy a
+    write-only host array in)."""
+    import torch
+    rng = np.random.default_rng(5)
+    a = rng.uniform(-1, 1, (400, 60))
+    b0 = rng.uniform(0.9, 1.1, 60)               # some above, some below the column maxima
+    ta, tb = torch.from_numpy(a).to(cuda), torch.from_numpy(b0).to(cuda)
+    prog('b200_noident_col_max_f64')(A=ta.data_ptr(), B=tb.data_ptr(), D0=400, D1=60)
+    torch.cuda.synchronize()
+    exp = np.maximum(b0, a.max(0))
+    assert (exp != a.max(0)).any() and (exp != b0).any()
+    np.testing.assert_array_equal(tb.cpu().numpy(), exp)
+
+
+def test_two_independent_reductions_in_one_state_do_not_share_a_workspace(cuda):
+    """Two large reductions that both combine through tickets + partials, in one state: DaCe's default stream
+    assignment runs them on different streams.  Each expanded node owns its workspace, so results stay exact
+    (integers-as-floats, sums < 2^24) call after call."""
+    import torch
+    n, rows = (1 << 24) + 4096, 1 << 13
+    g = torch.Generator(device=cuda)
+    g.manual_seed(11)
+    a = (torch.rand(n, device=cuda, generator=g) < 0.25).float()              # exact sum < 2^24
+    c = torch.randint(0, 3, (rows, 4096), device=cuda, generator=g).float()    # exact column sums
+    s = torch.zeros(1, device=cuda)
+    cs = torch.zeros(4096, device=cuda)
+    want_s, want_cs = a.double().sum().item(), c.double().sum(0)
+    p = prog('b200_two_reductions_one_state')
+    for _ in range(20):
+        s.fill_(-1)
+        cs.fill_(-1)
+        p(A=a.data_ptr(), C=c.data_ptr(), s=s.data_ptr(), cs=cs.data_ptr(), D0=n, D1=rows)
+        torch.cuda.synchronize()
+        assert s.item() == want_s
+        assert torch.equal(cs.double(), want_cs)
+
+
+def test_persistent_transients_program(cuda):
+    """make_transients_persistent: device copies of the host arrays are allocated in __dace_init."""
+    a = np.random.default_rng(8).random(3000017, dtype=np.float32)
+    b = np.zeros(1, np.float32)
+    p = prog('b200_full_sum_f32_persistent')
+    for _ in range(3):
+        b[0] = -1
+        p(A=a, B=b, D0=a.size)
+        assert abs(float(b[0]) - float(a.sum(dtype=np.float64))) <= 1e-5 * float(a.sum(dtype=np.float64))
 
 
 def test_offset_subrange_memlets(cuda):
@@ -423,3 +466,47 @@ def test_fused_map_reduce_fp16_accumulates_in_fp32(cuda):
     assert np.all(np.abs(s.astype(np.float64) - ref) <= 2.0 ** -10 * ref + 1e-3)    # one fp16 rounding of the sum
     naive16 = sq.cumsum(axis=1, dtype=np.float16)[:, -1].astype(np.float64)          # fp16 accumulation drifts far more
     assert np.abs(s.astype(np.float64) - ref).max() <= np.abs(naive16 - ref).max()
+
+
+def _custom_golden():
+    import json
+    g = np.load(os.path.join(os.path.dirname(__file__), 'golden', 'custom_golden.npz'))
+    meta = json.load(open(os.path.join(os.path.dirname(__file__), 'golden', 'custom_golden_meta.json')))['custom']
+    return g, meta
+
+
+@pytest.mark.parametrize('tag', ['app_i64_rows', 'app_i64_cols', 'app_i64_full', 'app_i64_lead2', 'absmax_f32_rows',
+                                 'absmax_f32_noident', 'refmin_f32_full'])
+def test_custom_wcr_lambdas_match_the_reference_pure_expansion(tag, cuda):
+    """ReductionType.Custom Reduce nodes expanded with 'B200' (generated functor + header kernels) replay the golden
+    vectors the unmodified reference produced with its `pure` expansion - bit for bit (integer arithmetic; the
+    float lambdas only select)."""
+    import torch
+    g, meta = _custom_golden()
+    m = next(x for x in meta if x['tag'] == tag)
+    a = g[tag + '__in']
+    want = g[tag + '__out']
+    b0 = g[tag + '__init'] if m['identity'] is None else np.full(want.shape, 77, want.dtype)
+    ta, tb = torch.from_numpy(a).to(cuda), torch.from_numpy(b0.copy()).to(cuda)
+    syms = {'D%d' % i: s for i, s in enumerate(a.shape)}
+    prog('b200_custom_' + tag)(A=ta.data_ptr(), B=tb.data_ptr(), **syms)
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(tb.cpu().numpy(), want)
+
+
+def test_custom_wcr_lambda_large_shapes_same_program(cuda):
+    """The same DaCe-built programs at sizes that split rows over CTAs / row slices over the workspace."""
+    import torch
+    g = torch.Generator(device=cuda)
+    g.manual_seed(3)
+    for name, shape, dim in (('b200_custom_app_i64_rows', (7, 3000001), 1), ('b200_custom_app_i64_cols', (300001, 70), 0),
+                             ('b200_custom_app_i64_full', (5000003, ), 0)):
+        x = torch.randint(-3, 4, shape, device=cuda, dtype=torch.int64, generator=g) * 2
+        kept = [s for i, s in enumerate(shape) if i != dim] if len(shape) > 1 else [1]
+        out = torch.zeros(kept, dtype=torch.int64, device=cuda)
+        prog(name)(A=x.data_ptr(), B=out.data_ptr(), **{'D%d' % i: s for i, s in enumerate(shape)})
+        torch.cuda.synchronize()
+        f = (x.cpu().numpy() + 1).astype(np.uint64)
+        with np.errstate(over='ignore'):
+            ref = (np.multiply.reduce(f, axis=dim, dtype=np.uint64) - np.uint64(1)).astype(np.int64)
+        np.testing.assert_array_equal(out.cpu().numpy().reshape(ref.shape), ref)

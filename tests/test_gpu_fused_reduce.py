@@ -109,3 +109,45 @@ def test_fused_column_folds(cuda, lib, rows, n):
     ol = torch.zeros(n * 2, dtype=torch.int64, device=cuda)[::2]
     _run(lib, 13, al, w, ol, rows, n, True, ws)
     assert torch.equal(ol, (al * w[None, :]).sum(0) + 11)
+
+
+# ---- custom WCR functors (no neutral element: accumulators carry a "holds a value" flag) ----
+
+def _add_plus_product_ref(x: torch.Tensor, dim: int, identity: int) -> np.ndarray:
+    """fold of a + b + a*b = prod(1 + x_i) - 1, exact modulo 2^64 like the device's int64 arithmetic."""
+    f = (x.cpu().numpy().astype(np.int64) + 1).astype(np.uint64)
+    with np.errstate(over='ignore'):
+        p = np.multiply.reduce(f, axis=dim, dtype=np.uint64) * np.uint64(identity + 1)
+        return (p - np.uint64(1)).astype(np.int64)
+
+
+@pytest.mark.parametrize('rows,n', [(1, 20), (1, 3000001), (3, 100000), (600, 5000), (5000, 300), (70000, 40), (2, 0)])
+def test_fused_custom_functors_rows(cuda, lib, rows, n):
+    ws = db.Workspace(cuda)
+    g = torch.Generator(device=cuda).manual_seed(rows + n)
+    x = torch.rand(rows, n, device=cuda, generator=g) * 100 + 1
+    out = torch.full((rows, ), -1.0, device=cuda)
+    _run(lib, 20, x, None, out, rows, n, True, ws)                     # lambda a, b: a if a < b else b, identity 9999999
+    ref = x.min(dim=1).values if n else torch.full((rows, ), 9999999.0, device=cuda)
+    assert torch.equal(out, ref)
+    out2 = torch.full((rows, ), 50.0, device=cuda)
+    _run(lib, 20, x, None, out2, rows, n, False, None)                 # identity None: fold into the output
+    assert torch.equal(out2, torch.minimum(ref, torch.tensor(50.0, device=cuda)))
+    xi = torch.randint(-3, 4, (rows, n), device=cuda, dtype=torch.int64, generator=g) * 2     # 1 + x is odd
+    oi = torch.zeros(rows, dtype=torch.int64, device=cuda)
+    _run(lib, 21, xi, None, oi, rows, n, True, ws)                     # lambda a, b: a + b + a * b, identity 0
+    np.testing.assert_array_equal(oi.cpu().numpy(), _add_plus_product_ref(xi, 1, 0))
+
+
+@pytest.mark.parametrize('rows,n', [(20, 1), (3000001, 1), (100000, 3), (5000, 600), (300, 5000), (64, 70000)])
+def test_fused_custom_functors_cols(cuda, lib, rows, n):
+    ws = db.Workspace(cuda)
+    g = torch.Generator(device=cuda).manual_seed(rows * 3 + n)
+    x = torch.rand(rows, n, device=cuda, generator=g) * 100 + 1
+    out = torch.full((n, ), -1.0, device=cuda)
+    _run(lib, 30, x, None, out, rows, n, True, ws)
+    assert torch.equal(out, x.min(dim=0).values)
+    xi = torch.randint(-3, 4, (rows, n), device=cuda, dtype=torch.int64, generator=g) * 2
+    oi = torch.zeros(n, dtype=torch.int64, device=cuda)
+    _run(lib, 31, xi, None, oi, rows, n, True, ws)
+    np.testing.assert_array_equal(oi.cpu().numpy(), _add_plus_product_ref(xi, 0, 0))

@@ -14,6 +14,7 @@ import pytest
 import torch
 
 from dace_b200 import _lib
+from dace_b200.api import Workspace
 
 pytestmark = pytest.mark.gpu
 
@@ -28,10 +29,15 @@ def _call_noalloc(lib, red, dt, x, out, rows, n, stride, identity_bytes):
     assert st == 0, lib.dace_b200_status_string(st)
 
 
+_WS = []
+
+
 def _call_regular(lib, red, dt, x, out, rows, n, stride, identity_bytes):
+    if not _WS:
+        _WS.append(Workspace(x.device))     # the regular entry point works in a caller-owned workspace
     ident = ctypes.create_string_buffer(identity_bytes, 8)
-    st = lib.dace_b200_reduce_rows(red, dt, dt, x.data_ptr(), out.data_ptr(), rows, n, stride, ident, None, 0,
-                                   torch.cuda.current_stream().cuda_stream)
+    st = lib.dace_b200_reduce_rows(red, dt, dt, x.data_ptr(), out.data_ptr(), rows, n, stride, ident, _WS[0].ptr,
+                                   _WS[0].nbytes, torch.cuda.current_stream().cuda_stream)
     assert st == 0, lib.dace_b200_status_string(st)
 
 
