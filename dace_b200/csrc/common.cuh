@@ -387,6 +387,11 @@ struct Launch {
     Workspace ws;
     void* extra = nullptr;       // scratch past the base workspace (two-pass `mid`, partition buffers)
     size_t extra_bytes = 0;
+    // Dry run of the planner (dace_b200_reduce_nd_workspace_bytes): nothing is launched, *dry_need becomes the
+    // largest scratch offset a real run of the same plan would touch.
+    size_t* dry_need = nullptr;
+    size_t dry_base = 0;
+    void take(size_t bytes) const { if (dry_need && dry_base + bytes > *dry_need) *dry_need = dry_base + bytes; }
 };
 
 // Experiment knobs (environment variables), read ONCE when the library is loaded - never on a call path.
@@ -395,6 +400,7 @@ struct Tuning {
     int wide_wc;            // DACE_B200_WIDE_WC (0 = default)
     int part_chunk_log2;    // DACE_B200_PART_CHUNK_LOG2 (0 = default)
     int part_divert;        // DACE_B200_PART_DIVERT (-1 = default)
+    int part_hint;          // DACE_B200_PART_HINT (-1 = default)
 };
 const Tuning& tuning();
 

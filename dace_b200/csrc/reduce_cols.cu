@@ -544,9 +544,64 @@ static cudaError_t launch_cols_narrow(const ColsArgs& a, const Launch& l) {
     return cudaGetLastError();
 }
 
+// Many small dense blocks ([O, R, K] with K a power of two <= 32 and R * K elements of a few KiB: the first pass
+// of an inner-first plan over [..., R3, K4] with a tiny innermost kept axis, per-pixel channel statistics, ...).
+// A warp streams one block as a flat run: lane l reads elements l, l + 32, ... whose column is l % K for good, so a
+// lane needs one accumulator; lanes with the same column meet through xor-shuffles.  Fully coalesced 128-byte
+// requests, 8 loads in flight per lane, warps walk consecutive blocks.  The general kernel would launch one
+// 256-thread CTA per block with most warps idle (measured 0.07 of the HBM peak at [64^4, 4] axes (1, 3)).
+constexpr int kSmallThreads = 256;
+constexpr int kSmallUnroll = 8;
+constexpr size_t kSmallMaxBlock = 16384;   // elements per block
+
+template <class L, class A, class S, class Op>
+__global__ void __launch_bounds__(kSmallThreads)
+cols_small_kernel(const L* __restrict__ in, S* __restrict__ out, size_t outer, unsigned n, unsigned K, size_t so,
+                  ptrdiff_t oo, ptrdiff_t oi, Finish<A> fin) {
+    const unsigned lane = threadIdx.x & 31;
+    const size_t warp = (size_t(blockIdx.x) * kSmallThreads + threadIdx.x) >> 5;
+    const size_t nwarps = (size_t(gridDim.x) * kSmallThreads) >> 5;
+    for (size_t o = warp; o < outer; o += nwarps) {
+        const L* p = in + o * so;
+        A acc = Op::neutral();
+        unsigned e = lane;
+        for (; e + (kSmallUnroll - 1) * 32 < n; e += kSmallUnroll * 32) {
+            A v[kSmallUnroll];
+#pragma unroll
+            for (int u = 0; u < kSmallUnroll; ++u) v[u] = to_acc<A, L>(ldg_scalar(p + e + u * 32));
+#pragma unroll
+            for (int u = 0; u < kSmallUnroll; ++u) acc = Op::apply(acc, v[u]);
+        }
+        for (; e < n; e += 32) acc = Op::apply(acc, to_acc<A, L>(ldg_scalar(p + e)));
+        for (unsigned m = 16; m >= K; m >>= 1) acc = Op::apply(acc, shfl_xor(acc, int(m)));
+        if (lane < K) write_result<Op, A, S>(out + ptrdiff_t(o) * oo + ptrdiff_t(lane) * oi, acc, fin);
+    }
+}
+
+template <class T, class Op>
+static cudaError_t launch_cols_small(const ColsArgs& a, const Launch& l) {
+    using L = typename T::L; using A = typename T::A; using S = typename T::S;
+    const size_t K = a.inner;
+    if (K < 2 || K > 32 || (K & (K - 1)) != 0 || a.in_stride_r != K || a.reduced * K > kSmallMaxBlock ||
+        a.outer < size_t(sm_count()) * 64 || tuning().no_tiled)
+        return cudaErrorNotSupported;
+    const size_t warps_per_cta = kSmallThreads / 32;
+    size_t grid = (a.outer + warps_per_cta - 1) / warps_per_cta;
+    const size_t cap = size_t(sm_count()) * 8;
+    if (grid > cap) grid = cap;
+    cols_small_kernel<L, A, S, Op><<<(unsigned)grid, kSmallThreads, 0, l.stream>>>(
+        (const L*)a.in, (S*)a.out, a.outer, unsigned(a.reduced * K), unsigned(K), a.in_stride_o, a.out_stride_o,
+        a.out_stride_i, make_finish<A, S>(a.identity));
+    return cudaGetLastError();
+}
+
 template <class T, class Op>
 static cudaError_t launch_cols_t(const ColsArgs& a, const Launch& l) {
     using L = typename T::L;
+    {
+        cudaError_t e = launch_cols_small<T, Op>(a, l);
+        if (e != cudaErrorNotSupported) return e;
+    }
     {
         cudaError_t e = launch_cols_narrow<T, Op>(a, l);
         if (e != cudaErrorNotSupported) return e;

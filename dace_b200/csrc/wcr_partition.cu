@@ -50,10 +50,40 @@ constexpr int kCntSlots = kMaxBuckets + 1;      // + the bucket that collects ou
 constexpr size_t kChunkKeysDefault = size_t(1) << 24;  // ~64 MiB of keys per chunk (measured best of 2^22..2^26)
 constexpr size_t kMaxChunks = 4096;
 constexpr int kDivertDefault = 0;             // 1 tile in N straight to global atomics (0 = none)
+constexpr int kHintDefault = 0;               // L2 residency hints (bits 1 | 2, see below); DACE_B200_PART_HINT
 constexpr int kPhaseBUnroll = 8;              // 128-bit L2 loads in flight per thread in phase B
 
 template <class V>
 __device__ __forceinline__ void smem_add_v(V* p, V v) { atomicAdd(p, v); }
+
+// L2 residency control for the partition buffer (hint bits of the kernel, DACE_B200_PART_HINT):
+//   1: the key stream is read with an evict-first policy (it is dead after one use);
+//   2: the partitioned keys are stored with an evict-last policy (phase B reads them back a moment later);
+// Measured (profiles/r2_c4_hint_sweep.txt): no change in time for chunks of 2^22 .. 2^24 keys (0.785 / 0.84 / 1.03 ms
+// with or without) - the kernel is bound by the shared-memory pipeline, not by the buffer's trip through
+// DRAM.  A third variant, `discard.global.L2` of every consumed 128-byte line in phase B (so that dirty lines
+// never reach DRAM), was 47 % SLOWER (1.155 ms) and raced with the next use of the buffer at small chunks
+// (wrong counts at 2^22): removed.
+__device__ __forceinline__ unsigned long long policy_evict_first() {
+    unsigned long long p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ unsigned long long policy_evict_last() {
+    unsigned long long p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ Words<16> ldg_policy16(const void* p, unsigned long long pol) {
+    Words<16> r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]) : "l"(p), "l"(pol));
+    return r;
+}
+__device__ __forceinline__ void stg_policy(unsigned* p, unsigned v, unsigned long long pol) {
+    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(pol) : "memory");
+}
+
 
 // Barrier among the kGroupThreads threads of one group (ids 1..kGroups; 0 is __syncthreads / grid.sync).
 __device__ __forceinline__ void group_sync(unsigned g) {
@@ -64,8 +94,8 @@ template <class V>
 __global__ void __launch_bounds__(kPartThreads, 1)
 scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict__ bins, unsigned nbins, V cval,
                          unsigned* buf, unsigned* gcur, size_t chunk, unsigned cap, int B, int S, int aligned,
-                         const int* __restrict__ gate, int divert) {
-    if (*gate != 0) return;   // clustered keys: the global-atomic kernel behind this one does the work (grid-uniform)
+                         const int* __restrict__ gate, int divert, int hint) {
+    if (*gate != 0) return;   // clustered / skewed keys: one of the kernels behind this one does the work (grid-uniform)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     V* hist = reinterpret_cast<V*>(smem_raw);                                  // [kBucketBins]
     unsigned* stage_all = reinterpret_cast<unsigned*>(smem_raw + size_t(kBucketBins) * sizeof(V));   // [kGroups][kTileKeys]
@@ -87,6 +117,8 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
     for (unsigned i = tid; i < kBucketBins; i += kPartThreads) hist[i] = V(0);
     if (gtid < kCntSlots) cnt[gtid] = 0;
     __syncthreads();
+    const unsigned long long pol_first = policy_evict_first(), pol_last = policy_evict_last();
+    const bool keys_first = hint & 1, buf_last = hint & 2;
 
     const size_t nchunks = (n + chunk - 1) / chunk;
     for (size_t c = 0; c < nchunks; ++c) {
@@ -104,7 +136,8 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
             if (aligned && base + kTileKeys <= chunk_n) {
 #pragma unroll
                 for (int u = 0; u < kKeysPerThread / 4; ++u) {
-                    Words<16> w = ldg_stream16(ck + base + (size_t(gtid) + size_t(u) * kGroupThreads) * 4);
+                    const unsigned* src = ck + base + (size_t(gtid) + size_t(u) * kGroupThreads) * 4;
+                    Words<16> w = keys_first ? ldg_policy16(src, pol_first) : ldg_stream16(src);
 #pragma unroll
                     for (int j = 0; j < 4; ++j) k[u * 4 + j] = w.w[j];
                 }
@@ -185,7 +218,10 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
 #pragma unroll
                 for (int j = 0; j < kKeysPerThread; ++j) d[j] = delta[key[j] >> kBucketBits];
 #pragma unroll
-                for (int j = 0; j < kKeysPerThread; ++j) bufc[j * kGroupThreads + gtid + d[j]] = key[j];
+                for (int j = 0; j < kKeysPerThread; ++j) {
+                    unsigned* dstp = bufc + (j * kGroupThreads + gtid + d[j]);
+                    if (buf_last) stg_policy(dstp, key[j], pol_last); else *dstp = key[j];
+                }
             } else if (!ovf_tile) {
 #pragma unroll
                 for (int j = 0; j < kKeysPerThread; ++j) {
@@ -223,8 +259,9 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
             const unsigned b = blockIdx.x / S, s = blockIdx.x % S;
             unsigned cntb = __ldcg(cur + b);
             if (cntb > cap) cntb = cap;
-            const unsigned lo = unsigned((size_t(cntb) * s / S)) & ~3u;
-            const unsigned hi = (s == unsigned(S - 1)) ? cntb : (unsigned((size_t(cntb) * (s + 1) / S)) & ~3u);
+            // slices start on 128-byte lines (bucket bases are 128-byte aligned: cap is a multiple of 32 words)
+            const unsigned lo = unsigned((size_t(cntb) * s / S)) & ~31u;
+            const unsigned hi = (s == unsigned(S - 1)) ? cntb : (unsigned((size_t(cntb) * (s + 1) / S)) & ~31u);
             const unsigned* src = bufc + size_t(b) * cap;
             const unsigned nvec = (hi - lo) / 4;
             const uint4* v4 = reinterpret_cast<const uint4*>(src + lo);
@@ -264,15 +301,53 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
     }
 }
 
-// Key sampler: 1024 adjacent pairs spread over the keys.  Sorted input or long runs of one key
-// (>= half of the pairs equal) are cheap for warp-merged global atomics and unbalanced for the
-// partition (one bucket gets a whole chunk), so the flag routes the call to the other kernel.
-__global__ void __launch_bounds__(1024) scatter_sample_kernel(const unsigned* __restrict__ keys, size_t n, int* flag) {
-    const size_t stride = (n - 1) / 1024;
-    const size_t p = size_t(threadIdx.x) * stride;
-    const int equal = __ldg(keys + p) == __ldg(keys + p + 1);
+// Key sampler (one CTA, same stream, ~3 us): decides ON THE DEVICE which of three kernels serves the call.
+//   * 4096 keys spread over the input go into a shared-memory hash set; keys that were already there are
+//     counted.  Uniform keys over nbins bins repeat ~S^2 / (2 nbins) times in S samples; many more repeats
+//     = a few hot keys carry much of the mass (Zipf, all keys equal, keys confined to a small range)
+//     -> flag 2: the hot-key cache kernel (wcr_scatter.cu), which absorbs them in shared memory.
+//   * 1024 adjacent pairs: sorted input / long runs of one key (>= half of the pairs equal) are cheap for
+//     warp-merged global atomics and unbalanced for the partition (one bucket gets a whole chunk)
+//     -> flag 1: the global-atomic kernel.
+//   * otherwise flag 0: the radix partition below.
+constexpr int kSampleKeys = 4096;
+constexpr int kSampleSlots = 8192;
+
+__global__ void __launch_bounds__(1024) scatter_sample_kernel(const unsigned* __restrict__ keys, size_t n, unsigned nbins,
+                                                              int* flag) {
+    __shared__ unsigned table[kSampleSlots];
+    __shared__ unsigned dups;
+    for (int i = threadIdx.x; i < kSampleSlots; i += 1024) table[i] = 0xffffffffu;
+    if (threadIdx.x == 0) dups = 0;
+    __syncthreads();
+    const size_t stride = (n - 1) / kSampleKeys;
+    unsigned mine = 0;
+    int equal = 0;
+#pragma unroll
+    for (int j = 0; j < kSampleKeys / 1024; ++j) {
+        const size_t p = (size_t(j) * 1024 + threadIdx.x) * stride;
+        const unsigned k = __ldg(keys + p);
+        if (j == 0) equal = k == __ldg(keys + p + 1);
+        if (k >= nbins) continue;
+        unsigned slot = (k * 2654435761u) >> 19;          // top 13 bits
+        for (int probe = 0; probe < 16; ++probe) {
+            const unsigned old = atomicCAS(&table[slot], 0xffffffffu, k);
+            if (old == 0xffffffffu) break;
+            if (old == k) { ++mine; break; }
+            slot = (slot + 1) & (kSampleSlots - 1);
+        }
+    }
+    if (mine) atomicAdd(&dups, mine);
     const int cnt = __syncthreads_count(equal);
-    if (threadIdx.x == 0) *flag = (cnt >= 512) ? 1 : 0;
+    if (threadIdx.x == 0) {
+        // repeats expected from uniform keys: S - nbins * (1 - exp(-S / nbins)) ~ S^2 / (2 nbins) for nbins >> S
+        const float S = float(kSampleKeys), nb = float(nbins);
+        const float expect = S - nb * (1.0f - __expf(-S / nb));
+        int f = 0;
+        if (float(dups) > 2.0f * expect + 128.0f) f = 2;
+        else if (cnt >= 512) f = 1;
+        *flag = f;
+    }
 }
 
 // Geometry + scratch layout of one partitioned call.  The scratch is the caller's
@@ -303,8 +378,8 @@ static bool part_plan(int dtidx, int dtval, bool has_values, size_t n, size_t nb
     if (lg >= 20 && lg <= 26) p.chunk = wave * std::max<size_t>(1, ((size_t(1) << lg) + wave / 2) / wave);
     p.nchunks = (n + p.chunk - 1) / p.chunk;
     if (p.nchunks > kMaxChunks) return false;
-    // 1.5x the uniform share per bucket, multiple of 4 words so every bucket base stays 16-byte aligned
-    p.cap = unsigned(((p.chunk * 3 / 2) / p.B + 3) & ~size_t(3));
+    // 1.5x the uniform share per bucket, multiple of 32 words so every bucket base stays 128-byte aligned
+    p.cap = unsigned(((p.chunk * 3 / 2) / p.B + 31) & ~size_t(31));   // 128-byte lines: phase B discards whole lines
     p.smem = size_t(kBucketBins) * 4 + size_t(kGroups) * kTileKeys * sizeof(unsigned);
     p.gcur_off = 256;
     p.buf_off = (p.gcur_off + p.nchunks * size_t(p.B) * sizeof(unsigned) + 255) & ~size_t(255);
@@ -352,7 +427,7 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Part
     if (e != cudaSuccess) return e;
     const unsigned* keys = reinterpret_cast<const unsigned*>(a.idx);
     size_t n = a.n;
-    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(keys, n, flag);
+    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(keys, n, unsigned(a.nbins), flag);
     const int* gate = flag;
     *gate_out = gate;
     V* bins = reinterpret_cast<V*>(a.bins);
@@ -362,7 +437,8 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Part
     int B_arg = p.B, S_arg = p.S;
     int aligned = (reinterpret_cast<size_t>(a.idx) & 15) == 0;
     int divert = tuning().part_divert >= 0 ? tuning().part_divert : kDivertDefault;   // tuning knob (0 = off)
-    void* args[] = {&keys, &n, &bins, &nbins, &cval, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert};
+    int hint = tuning().part_hint >= 0 ? tuning().part_hint : kHintDefault;
+    void* args[] = {&keys, &n, &bins, &nbins, &cval, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert, &hint};
     e = cudaLaunchCooperativeKernel((void*)scatter_partition_kernel<V>, dim3(sm_count()), dim3(kPartThreads), args,
                                     p.smem, l.stream);
     if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }

@@ -133,6 +133,10 @@ def _resolve_redtype(wcr: str, allow_custom: bool = False) -> ReductionType:
     if rt == ReductionType.Custom:
         rt = lower_custom(wcr)
     if rt == ReductionType.Custom and allow_custom:
+        # `a - b` / `a / b` are "reductions" only for the reference's OpenMP expansion (reduce.py:274-286); they are
+        # neither associative nor commutative, so a tree over them is not the reference's result: not taken
+        if str(detect_reduction_type(wcr, openmp=True)).split('.')[-1] in ('Sub', 'Div'):
+            raise NotImplementedError('Reduce expansion "B200": %s is not associative; use the "pure" expansion' % wcr)
         return rt
     if rt not in _SUPPORTED:
         raise NotImplementedError('Reduce expansion "B200": reduction type %s has no precompiled sm_100a kernel '
@@ -170,23 +174,7 @@ def _expand_custom(node, state, sdfg, in_desc, out_desc, shape, istr, reduced, o
     cannot sit behind a precompiled C ABI.  Served layouts: all axes, trailing axes (rows) or leading axes
     (columns) reduced, each group of axes dense enough to merge; anything else is refused (use 'pure')."""
     from dace.codegen.targets.cpp import unparse_cr_split
-    kept = [i for i, r in enumerate(reduced) if not r]
-    red = [i for i, r in enumerate(reduced) if r]
-    if not red:
-        raise NotImplementedError('Reduce expansion "B200": custom WCR without a reduced axis')
-    if kept and not (max(kept) < min(red) or max(red) < min(kept)):
-        raise NotImplementedError('Reduce expansion "B200": custom WCR lambdas are served for all / trailing / leading '
-                                  'reduced axes only (got interleaved axes); use the "pure" expansion')
-    cols = bool(kept) and max(red) < min(kept)
-    mk = _merge([shape[i] for i in kept], [istr[i] for i in kept])
-    mr = _merge([shape[i] for i in red], [istr[i] for i in red])
-    mo = _merge([shape[i] for i in kept], list(ostr))
-    if mk is None or mr is None or mo is None:
-        raise NotImplementedError('Reduce expansion "B200": custom WCR needs kept and reduced axes that each merge into '
-                                  'one index (dense sub-ranges); use the "pure" expansion')
-    (nk, sk), (nr, sr), (_, so) = mk, mr, mo
-    if not kept:
-        so = 1
+    cols, nk, sk, nr, sr, so = custom_layout(shape, istr, reduced, ostr)
     body, (arg1, arg2) = unparse_cr_split(sdfg, node.wcr)
     ident = '%s_%d_%d_%d' % (sdfg.name, state.parent_graph.node_id(state), state.node_id(node), next(_ws_counter))
     tin, tout = in_desc.dtype.ctype, out_desc.dtype.ctype
@@ -238,6 +226,48 @@ def _is_one(expr) -> bool:
         return False
 
 
+def _memlet_dims(node, in_edge, out_edge, in_desc, out_desc):
+    """Input memlet as (extents, element strides, reduced flags) + output strides of the kept axes; compile-time
+    unit dims are squeezed like the reference does (reference reduce.py:40-54)."""
+    in_subset = copy.deepcopy(in_edge.data.subset)
+    in_sizes = in_subset.size()
+    input_dims = len(in_sizes)
+    axes = list(node.axes) if node.axes is not None else list(range(input_dims))
+    axes = [a % input_dims for a in axes]
+    shape, istr, reduced = [], [], []
+    for i, (rng, size) in enumerate(zip(in_subset.ranges, in_sizes)):
+        if _is_one(size):
+            continue
+        shape.append(size)
+        istr.append(in_desc.strides[i] * rng[2])
+        reduced.append(i in axes)
+    out_subset = copy.deepcopy(out_edge.data.subset)
+    ostr = [out_desc.strides[j] * rng[2]
+            for j, (rng, size) in enumerate(zip(out_subset.ranges, out_subset.size())) if not _is_one(size)]
+    return shape, istr, reduced, ostr
+
+
+def custom_layout(shape, istr, reduced, ostr):
+    """(cols, n_kept, s_kept, n_red, s_red, s_out) of a layout the custom-lambda kernels serve, else
+    NotImplementedError: all / trailing (rows) / leading (columns) axes reduced, each group merging into one index."""
+    kept = [i for i, r in enumerate(reduced) if not r]
+    red = [i for i, r in enumerate(reduced) if r]
+    if not red:
+        raise NotImplementedError('Reduce expansion "B200": custom WCR without a reduced axis')
+    if kept and not (max(kept) < min(red) or max(red) < min(kept)):
+        raise NotImplementedError('Reduce expansion "B200": custom WCR lambdas are served for all / trailing / leading '
+                                  'reduced axes only (got interleaved axes); use the "pure" expansion')
+    cols = bool(kept) and max(red) < min(kept)
+    mk = _merge([shape[i] for i in kept], [istr[i] for i in kept])
+    mr = _merge([shape[i] for i in red], [istr[i] for i in red])
+    mo = _merge([shape[i] for i in kept], list(ostr))
+    if mk is None or mr is None or mo is None:
+        raise NotImplementedError('Reduce expansion "B200": custom WCR needs kept and reduced axes that each merge into '
+                                  'one index (dense sub-ranges); use the "pure" expansion')
+    (nk, sk), (nr, sr), (_, so) = mk, mr, mo
+    return cols, nk, sk, nr, sr, (so if kept else 1)
+
+
 @dace.library.register_expansion(Reduce, 'B200')
 class ExpandReduceB200(ExpandTransformation):
     """Reduce -> one call into libdace_b200_reduce.so (hand-written sm_100a kernels)."""
@@ -261,23 +291,8 @@ class ExpandReduceB200(ExpandTransformation):
                                       (in_desc.dtype, out_desc.dtype))
         redtype = _resolve_redtype(node.wcr, allow_custom=True)
 
-        # Input memlet: per-dimension extent and element stride (array stride x range step);
-        # compile-time unit dims are squeezed like the reference does (reduce.py:40-54).
-        in_subset = copy.deepcopy(in_edge.data.subset)
-        in_sizes = in_subset.size()
-        input_dims = len(in_sizes)
-        axes = list(node.axes) if node.axes is not None else list(range(input_dims))
-        axes = [a % input_dims for a in axes]
-        shape, istr, reduced = [], [], []
-        for i, (rng, size) in enumerate(zip(in_subset.ranges, in_sizes)):
-            if _is_one(size):
-                continue
-            shape.append(size)
-            istr.append(in_desc.strides[i] * rng[2])
-            reduced.append(i in axes)
-        out_subset = copy.deepcopy(out_edge.data.subset)
-        ostr = [out_desc.strides[j] * rng[2]
-                for j, (rng, size) in enumerate(zip(out_subset.ranges, out_subset.size())) if not _is_one(size)]
+        # Input memlet: per-dimension extent and element stride (array stride x range step)
+        shape, istr, reduced, ostr = _memlet_dims(node, in_edge, out_edge, in_desc, out_desc)
         n_kept = sum(1 for r in reduced if not r)
         if len(ostr) != n_kept:
             raise ValueError('Reduce expansion "B200": output memlet %s has %d non-unit dimensions, expected %d' %

@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 17
+VERSION = 18
 
 
 def up_to_date() -> bool:
@@ -492,6 +492,44 @@ def _programs(dace):
             sdfg.arrays[a].storage = dace.StorageType.GPU_Global
         progs.append(sdfg)
 
+    # (15) Privatised shared-memory WCR tiles: the reference's own AccumulateTransient between a
+    #      thread-block map and its kernel map, tile in shared memory - generated call sites
+    #      dace::ResetShared<..>::Reset / dace::SharedToGlobal1D<..>::Accum<Sum> are served by
+    #      include/dace_b200_shared_accum.cuh (dace_b200/shared_tile.py).
+    from dace_b200 import shared_tile as ST
+
+    @dace.program
+    def b200_shared_tile_hist(keys: dace.int32[N], bins: dace.int32[256]):
+        for b in dace.map[0:N // 1024]:
+            for t in dace.map[0:256]:
+                for j in range(4):
+                    with dace.tasklet:
+                        k << keys[b * 1024 + j * 256 + t]
+                        out >> bins(1, lambda x, y: x + y)[:]
+                        out[k] = 1
+
+    @dace.program
+    def b200_shared_tile_weighted_f32(keys: dace.int32[N], w: dace.float32[N], bins: dace.float32[512]):
+        for b in dace.map[0:N // 512]:
+            for t in dace.map[0:128]:
+                for j in range(4):
+                    with dace.tasklet:
+                        k << keys[b * 512 + j * 128 + t]
+                        v << w[b * 512 + j * 128 + t]
+                        out >> bins(1, lambda x, y: x + y)[:]
+                        out[k] = v
+
+    for p in (b200_shared_tile_hist, b200_shared_tile_weighted_f32):
+        sdfg = _to_sdfg(p, simplify=True)
+        sdfg.apply_gpu_transformations()
+        st = next(s_ for s_ in sdfg.states() if sum(isinstance(n, dace.nodes.MapExit) for n in s_.nodes()) >= 2)
+        exits = [n for n in st.nodes() if isinstance(n, dace.nodes.MapExit)]
+        inner = next(e for e in exits if e.map.params == ['t'])
+        outer = next(e for e in exits if e.map.params == ['b'])
+        st.entry_node(inner).map.schedule = dace.ScheduleType.GPU_ThreadBlock
+        ST.privatise_wcr_in_shared(sdfg, st, inner, outer)
+        progs.append(sdfg)
+
     return progs
 
 
@@ -554,7 +592,7 @@ def _compile_one(i):
         'lib': lib, 'args': args,
         'init_symbols': [{'name': s, 'ctype': g.symbols[s].ctype} for s in init_names],
         'b200_calls': src.count('dace_b200_reduce_nd(') + src.count('dace_b200_wcr_scatter(') +
-        src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') + src.count('__b200_fused_') // 2 + src.count('DACE_GPU_CHECK(__b200_custom_') +
+        src.count('dace_b200_reduce_arg(') + src.count('dace_b200_reduce_rows_max_sum(') + src.count('__b200_fused_') // 2 + src.count('DACE_GPU_CHECK(__b200_custom_') + cu.count('dace_b200 shared tiles') +
         cu.count('dace_b200::block_reduce<') + cu.count('dace_b200::block_allreduce<'),
         'comm_calls': src.count('dace_b200_comm_allreduce('),
     }

@@ -8,7 +8,9 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 OUT = os.path.join(HERE, '_built')
 HARNESS = os.path.join(OUT, 'libblock_reduce_harness.so')
 FUSED_HARNESS = os.path.join(OUT, 'libfused_reduce_harness.so')
-_HEADERS = [os.path.join(ROOT, 'include', h) for h in ('dace_b200_block_reduce.cuh', 'dace_b200_fused_reduce.cuh')]
+SHARED_HARNESS = os.path.join(OUT, 'libshared_accum_harness.so')
+_HEADERS = [os.path.join(ROOT, 'include', h) for h in ('dace_b200_block_reduce.cuh', 'dace_b200_fused_reduce.cuh',
+                                                            'dace_b200_shared_accum.cuh')]
 
 
 def _build_one(src: str, lib: str, force: bool) -> str:
@@ -23,6 +25,7 @@ def _build_one(src: str, lib: str, force: bool) -> str:
 
 def build(force: bool = False) -> str:
     _build_one(os.path.join(HERE, 'fused_reduce_harness.cu'), FUSED_HARNESS, force)
+    _build_one(os.path.join(HERE, 'shared_accum_harness.cu'), SHARED_HARNESS, force)
     return _build_one(os.path.join(HERE, 'block_reduce_harness.cu'), HARNESS, force)
 
 

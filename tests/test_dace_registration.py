@@ -36,7 +36,8 @@ def test_registered_in_reduce_implementations(dace):
     from dace.libraries.standard.nodes.reduce import Reduce
     from dace_b200.expansion import ExpandReduceB200, B200Reduce
     assert Reduce.implementations['B200'] is ExpandReduceB200
-    assert ExpandReduceB200.environments == [B200Reduce]
+    from dace_b200.expansion import B200FusedReduce
+    assert ExpandReduceB200.environments == [B200Reduce, B200FusedReduce]   # C ABI + the header for custom-lambda functors
     assert set(Reduce.implementations) >= {'pure', 'OpenMP', 'CUDA (device)', 'GPUAuto', 'B200'}
     assert Reduce.default_implementation == 'pure'   # importing the plug-in does not hijack the default
 

@@ -510,3 +510,23 @@ def test_custom_wcr_lambda_large_shapes_same_program(cuda):
         with np.errstate(over='ignore'):
             ref = (np.multiply.reduce(f, axis=dim, dtype=np.uint64) - np.uint64(1)).astype(np.int64)
         np.testing.assert_array_equal(out.cpu().numpy().reshape(ref.shape), ref)
+
+
+def test_shared_tile_wcr_flush_through_the_b200_header(cuda):
+    """SURVEY a13: AccumulateTransient + shared-memory tile; the generated dace::ResetShared / SharedToGlobal1D::Accum
+    call sites are served by include/dace_b200_shared_accum.cuh.  Integer histogram bit-exact; the fp32 variant adds
+    small integers (exact in fp32), so it is exact too."""
+    rng = np.random.default_rng(12)
+    n = 1024 * 3000
+    keys = rng.integers(0, 256, n).astype(np.int32)
+    keys[: n // 2] = rng.integers(3, 9, n // 2)            # most of the tile stays untouched in many blocks
+    bins = rng.integers(0, 5, 256).astype(np.int32)
+    want = bins + np.bincount(keys, minlength=256).astype(np.int32)
+    prog('b200_shared_tile_hist')(keys=keys, bins=bins, N=n)
+    np.testing.assert_array_equal(bins, want)
+    n2 = 512 * 5000
+    k2 = rng.integers(0, 512, n2).astype(np.int32)
+    w2 = rng.integers(0, 4, n2).astype(np.float32)
+    b2 = np.zeros(512, np.float32)
+    prog('b200_shared_tile_weighted_f32')(keys=k2, w=w2, bins=b2, N=n2)
+    np.testing.assert_array_equal(b2, np.bincount(k2, weights=w2, minlength=512).astype(np.float32))

@@ -509,6 +509,90 @@ def test_interleaved_axes_host_peel(dtype, shape, axes, cuda):
     _check(got, ref, dtype, a, axes, 'sum')
 
 
+@pytest.mark.parametrize('dtype', [np.float32, np.int32, np.int64, np.uint8, np.float64])
+@pytest.mark.parametrize('shape,axes', [
+    ([100, 7, 9, 130], (0, 2)),          # [R1, K1, R2, K2] with an outer axis too long for the host peel
+    ([70, 5, 8, 3], (0, 2)),             # tiny innermost kept axis
+    ([9, 6, 7, 8, 4], (1, 3)),           # [K0, R1, K2, R3, K4]
+    ([66, 3, 4, 5, 6, 20], (0, 2, 4)),   # three reduced axes: two intermediates
+    ([70, 6, 5, 40], (1, 3)),            # [K0, R1, K2, R3]: innermost axis reduced (rows first), long outer kept axis
+    ([3, 2, 2, 2, 2, 2, 2, 33], (0, 2, 4, 6)),
+])
+def test_interleaved_axes_inner_first(dtype, shape, axes, cuda):
+    """Interleaved kept / reduced axes without a direct kernel: the innermost reduced axis is folded first into a
+    contiguous intermediate (all outer axes as one index), the rest is planned on the intermediate - one streaming
+    pass per reduced axis group instead of the strided kernel.  Identity counts once; identity None folds into the
+    output; integers bit-exact."""
+    rng = np.random.default_rng(18)
+    a = _data(rng, shape, dtype, 'sum')
+    for op in ('sum', 'max', 'min'):
+        got, ref = _run(a, axes, op, cuda)
+        _check(got, ref, dtype, a, axes, op)
+    kept = [s for i, s in enumerate(shape) if i not in axes]
+    init = _data(rng, kept, dtype, 'sum')
+    got, ref = _run(a, axes, 'sum', cuda, identity=None, out_init=init)
+    _check(got, ref, dtype, a, axes, 'sum')
+    got, ref = _run(a, axes, 'sum', cuda, identity=3)
+    _check(got, ref, dtype, a, axes, 'sum')
+
+
+@pytest.mark.parametrize('dtype', [np.float32, np.int32, np.int64, np.uint8, np.float64])
+@pytest.mark.parametrize('shape,axes', [([20000, 16, 8], (1, )), ([10000, 100, 2], (1, )), ([12345, 7, 32], (1, )),
+                                        ([9500, 511, 4], (1, )), ([40, 6, 50, 8, 4], (1, 3)), ([10000, 3, 16], (1, ))])
+def test_many_small_dense_blocks(dtype, shape, axes, cuda):
+    """[O, R, K] with K a power of two <= 32 and small R * K: a warp streams one block as a flat run
+    (cols_small_kernel); also as the first pass of an inner-first plan."""
+    rng = np.random.default_rng(19)
+    a = _data(rng, shape, dtype, 'sum')
+    for op in ('sum', 'max'):
+        got, ref = _run(a, axes, op, cuda)
+        _check(got, ref, dtype, a, axes, op)
+    kept = [s for i, s in enumerate(shape) if i not in axes]
+    init = _data(rng, kept, dtype, 'sum')
+    got, ref = _run(a, axes, 'sum', cuda, identity=None, out_init=init)
+    _check(got, ref, dtype, a, axes, 'sum')
+    # unaligned start (a view one element into the allocation) and a strided output
+    flat = np.concatenate([np.zeros(1, dtype), a.reshape(-1)])
+    tv = torch.from_numpy(flat).to(cuda)[1:].view(*shape)
+    out = torch.zeros([2 * k for k in kept], dtype=tv.dtype, device=cuda)[tuple(slice(None, None, 2) for _ in kept)]
+    db.reduce('lambda a, b: a + b', tv, out, axis=axes, identity=0)
+    _check(out.cpu().numpy(), O.reduce(O.SUM, a, axes, identity=0, wide=True), dtype, a, axes, 'sum')
+
+
+def test_inner_first_views_bf16_and_workspace_query(cuda):
+    """The same plan on a bf16 input (fp32 intermediates), on a strided output, with a base-only workspace (falls
+    back to the scratch-free kernels, same result) and the scratch the query asks for."""
+    import ctypes
+    from dace_b200 import _lib
+    from dace_b200.api import Workspace
+    lib = _lib.load()
+    g = torch.Generator(device=cuda)
+    g.manual_seed(21)
+    x = torch.randn(80, 6, 12, 96, device=cuda, generator=g).to(torch.bfloat16)
+    out = torch.empty(6, 96, dtype=torch.float32, device=cuda)
+    db.reduce('lambda a, b: a + b', x, out, axis=(0, 2), identity=0)
+    ref = x.double().sum((0, 2))
+    assert torch.allclose(out.double(), ref, rtol=1e-5, atol=1e-3)
+    mx = torch.empty(6, 96, dtype=torch.float32, device=cuda)
+    db.reduce('lambda a, b: max(a, b)', x, mx, axis=(0, 2), identity=-3e38)
+    assert torch.equal(mx, x.float().amax((0, 2)))
+    xi = torch.randint(-50, 50, (90, 5, 11, 70), dtype=torch.int32, device=cuda, generator=g)
+    want = xi.sum((0, 2), dtype=torch.int32)
+    shape = (ctypes.c_int64 * 4)(*xi.shape)
+    istr = (ctypes.c_int64 * 4)(*xi.stride())
+    need = lib.dace_b200_reduce_nd_workspace_bytes(2, 2, 4, shape, istr, 0b0101)
+    base = lib.dace_b200_workspace_bytes()
+    assert need >= base + 90 * 5 * 70 * 4          # the first intermediate [R1, K1, K2]
+    for ws in (Workspace(cuda), Workspace(cuda, nbytes=need)):
+        o = torch.zeros(70, 5, dtype=torch.int32, device=cuda).t()          # transposed destination
+        db.reduce('lambda a, b: a + b', xi, o, axis=(0, 2), identity=0, workspace=ws)
+        assert torch.equal(o, want)
+    # a padded view (outer axes not dense): no intermediate plan, still exact
+    big = torch.randint(-50, 50, (90, 5, 11, 80), dtype=torch.int32, device=cuda, generator=g)
+    v = big[:, :, :, :70]
+    assert torch.equal(db.reduce('lambda a, b: a + b', v, axis=(0, 2), identity=0), v.sum((0, 2), dtype=torch.int32))
+
+
 @pytest.mark.parametrize('dtype', [np.float32, np.int32, np.float64])
 @pytest.mark.parametrize('shape', [[6, 5, 8, 300], [3, 70, 4, 33], [2, 2, 2, 2], [40, 3, 100, 1000]])
 def test_outer_kept_two_pass(dtype, shape, cuda):
