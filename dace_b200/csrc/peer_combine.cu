@@ -27,7 +27,7 @@ namespace db200 {
 
 constexpr int kPeerMaxWorld = 16;
 constexpr size_t kPeerFlagBytes = 1024;
-constexpr int kPeerThreads = 1024;
+constexpr int kPeerThreads = 512;
 
 struct PeerArgs {
     void* base[kPeerMaxWorld];   // this process' mapping of every rank's exchange buffer
@@ -49,6 +49,10 @@ template <class T, class Op>
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_kernel(T* __restrict__ data, size_t nelem, PeerArgs p) {
     const unsigned tid = threadIdx.x;
     const size_t slot_off = kPeerFlagBytes + size_t(p.epoch & 1) * size_t(p.world) * p.cap_bytes;
+    // Launched as a programmatic dependent of the kernel before it on the stream (the local reduction):
+    // this CTA is already resident when that kernel's last CTA retires and only waits here for its
+    // results to be visible - the launch gap between the two kernels (~4 us) is off the critical path.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     // 1. push my partial to every rank (own buffer included)
     for (int r = 0; r < p.world; ++r) {
         const int dst_rank = (p.rank + r) % p.world;   // spread the first writes over the links
@@ -80,8 +84,16 @@ template <class T>
 static cudaError_t peer_launch_t(int red, void* data, size_t nelem, const PeerArgs& p, cudaStream_t stream) {
     return dispatch_op<T>(red, [&](auto op) -> cudaError_t {
         using Op = decltype(op);
-        peer_allreduce_kernel<T, Op><<<1, kPeerThreads, 0, stream>>>(static_cast<T*>(data), nelem, p);
-        return cudaGetLastError();
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(1);
+        cfg.blockDim = dim3(kPeerThreads);
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        return cudaLaunchKernelEx(&cfg, peer_allreduce_kernel<T, Op>, static_cast<T*>(data), nelem, p);
     });
 }
 

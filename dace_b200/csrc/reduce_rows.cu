@@ -101,16 +101,22 @@ rows_tiny_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, uns
         }
         __syncthreads();
         if constexpr (WIDTH == 1) {
-            // a thread per row: n shared-memory reads at stride n words (conflict-free for odd n, 2-way for n = 2 mod 4)
+            // a thread per row: n shared-memory reads at stride n elements - conflict-free for odd n.  For even n
+            // every thread starts at column (row mod n) and wraps around: neighbouring threads are then n + 1
+            // elements apart, an odd stride again (a fold does not care where it starts).
+            const bool rotate = (n & 1u) == 0 && sizeof(L) >= 4;
             for (unsigned r = threadIdx.x; r < nrows; r += kRowThreads) {
                 A a0 = Op::neutral(), a1 = Op::neutral();
                 const L* p = tile + r * n;
-                unsigned c = 0;
-                for (; c + 1 < n; c += 2) {
+                unsigned c = rotate ? r % n : 0;
+                unsigned j = 0;
+                for (; j + 1 < n; j += 2) {
+                    const unsigned c1 = (c + 1 == n) ? 0 : c + 1;
                     a0 = Op::apply(a0, to_acc<A, L>(p[c]));
-                    a1 = Op::apply(a1, to_acc<A, L>(p[c + 1]));
+                    a1 = Op::apply(a1, to_acc<A, L>(p[c1]));
+                    c = (c1 + 1 == n) ? 0 : c1 + 1;
                 }
-                if (c < n) a0 = Op::apply(a0, to_acc<A, L>(p[c]));
+                if (j < n) a0 = Op::apply(a0, to_acc<A, L>(p[c]));
                 write_result<Op, A, S>(out + ptrdiff_t(row0 + r) * out_stride, Op::apply(a0, a1), fin);
             }
         } else {
@@ -136,7 +142,6 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
     if (a.n > size_t(kTinyMaxN) || a.n < 2 || a.row_stride != a.n || a.rows * a.n < (size_t(1) << 22) ||
         tuning().no_tiny_rows)
         return cudaErrorNotSupported;
-    if ((a.n * sizeof(L) / 4) % 4 == 0 && sizeof(L) >= 4) return cudaErrorNotSupported;   // stride would be >= 4-way bank conflicted
     const unsigned n = unsigned(a.n);
     const unsigned rows_per_tile = kTinyTile / n;
     const size_t ntiles = (a.rows + rows_per_tile - 1) / rows_per_tile;
@@ -146,7 +151,20 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
 #define DB200_TINY(W)                                                                                                   \
     rows_tiny_kernel<L, A, S, Op, W><<<(unsigned)grid, kRowThreads, 0, l.stream>>>((const L*)a.in, (S*)a.out, a.rows, n, \
                                                                                   rows_per_tile, a.out_stride, fin)
-    DB200_TINY(1);
+    // lanes per row: a thread per row while a tile holds at least 64 rows (n <= 64: measured faster than two lanes
+    // per row, [8M, 33] 0.63 vs 0.57 of the peak); for longer rows as many lanes as keep the 256 threads busy in the
+    // fold ([2.7M, 100]: 40 rows per tile, 4 lanes each, 0.54 -> 0.61)
+    unsigned width = 1;
+    if (rows_per_tile <= 64)
+        while (width < 32 && rows_per_tile * width * 2 <= unsigned(kRowThreads)) width <<= 1;
+    switch (width) {
+        case 1: DB200_TINY(1); break;
+        case 2: DB200_TINY(2); break;
+        case 4: DB200_TINY(4); break;
+        case 8: DB200_TINY(8); break;
+        case 16: DB200_TINY(16); break;
+        default: DB200_TINY(32); break;
+    }
 #undef DB200_TINY
     return cudaGetLastError();
 }

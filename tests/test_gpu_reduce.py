@@ -656,3 +656,19 @@ def test_tiny_rows_bf16_to_f32_and_strided_out(cuda):
     assert bool(((out.double() - ref).abs() <= 1e-5 * scale + 1e-12).all())
     mx = db.reduce('lambda a, b: max(a, b)', x, axis=1, identity=-3e38)
     assert torch.equal(mx, x.amax(1))
+
+
+def test_signed_zero_max_is_a_zero(cuda):
+    """Float max / min use fmaxf / fminf where the reference uses `(a > b) ? a : b` (reference
+    dace/runtime/include/dace/math.h:51-55).  On NaN-free data they agree except for the SIGN of a zero result,
+    where the reference itself depends on the fold order (max(-0.0, +0.0) keeps whichever came second).  The
+    decision: the value is pinned (a zero), the sign is not."""
+    x = torch.tensor([-0.0, 0.0] * 5000 + [-0.0], device=cuda)
+    for lam, ident in (('lambda a, b: max(a, b)', -1.0), ('lambda a, b: min(a, b)', 1.0)):
+        got = db.reduce(lam, x, axis=None, identity=ident)
+        assert got.item() == 0.0
+        rows = db.reduce(lam, x[:10000].view(100, 100), axis=1, identity=ident)
+        assert torch.all(rows == 0.0)
+    neg = torch.full((4097, ), -0.0, device=cuda)
+    got = db.reduce('lambda a, b: max(a, b)', neg, axis=None, identity=-1.0)
+    assert got.item() == 0.0 and torch.signbit(got).item()      # all inputs -0.0: no choice to make
