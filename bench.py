@@ -45,9 +45,11 @@ WORKLOADS = {
 }
 
 
-def config_for(workload, world, combine='peer'):
+def config_for(workload, world, combine='peer', dist_name='uniform'):
     """The `config` object of the JSON line - built the same way by both arms (--impl b200 / reference)."""
     desc, nbytes = WORKLOADS[workload]
+    if workload == 'c4' and dist_name != 'uniform':
+        desc = desc.replace('(uniform keys)', '(%s keys)' % dist_name)
     payload = {'c2': 4, 'c4': 4 << 20, 'c5': 16384}.get(workload)
     if world == 1 or payload is None:
         comb = 'none'
@@ -440,7 +442,7 @@ def run_reference_arm(args):
         'impl': 'reference', 'metric': METRIC, 'value': best, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': len(res),
         'warmup': max(1, args.warmup), 'ms_per_step': mean_s * 1e3, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': dtype_of(args.workload), 'data': 'synthetic',
-        'config': config_for(args.workload, args.gpus, args.combine),
+        'config': config_for(args.workload, args.gpus, args.combine, args.dist),
         'cpu_baseline': {k: base[k] for k in ('value', 'unit', 'cores', 'kind', 'sample', 'omp_threads')},
         'e2e': {'value': best, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'parity_ok': base['parity_ok'], 'rel_err_vs_fp64': base['rel_err_vs_fp64'],
@@ -684,12 +686,12 @@ def main():
     launches_per_step = int(w.get('launches', 1)) + (1 if (dist is not None and combine is not None) else 0)
     peak, peak_src = peaks()
 
-    def entry(name, ww, k):
+    def entry(name, ww, k, traffic_key=None):
         m_full, m_kernel, okk = measure(ww, k, 3)
         nb = WORKLOADS[name][1]
         ach = nb / (m_kernel * 1e-3) / 1e9
         e = {'GB/s': world * nb / (m_full * 1e-3) / 1e9, 'ms_per_step': m_full, 'kernel_ms': m_kernel,
-             'frac_of_hbm_peak': ach / peak, 'traffic': recorded_traffic(name) if world == 1 else None,
+             'frac_of_hbm_peak': ach / peak, 'traffic': recorded_traffic(traffic_key or name) if world == 1 else None,
              'parity_ok': okk}
         if world > 1 and ww['combine'] is not None:
             e['combine_us'] = (m_full - m_kernel) * 1e3
@@ -711,7 +713,7 @@ def main():
         if world == 1 and args.workload != 'c4':
             for dn in ('zipf1.1', 'all_equal'):
                 ww = make_workload('c4', dev, rank, torch, db, dn)
-                others['c4_' + dn.replace('.', '_')] = entry('c4', ww, 10)
+                others['c4_' + dn.replace('.', '_')] = entry('c4', ww, 10, 'c4_' + dn.replace('.', '_'))
                 del ww
                 torch.cuda.empty_cache()
         flush['buf'] = None
@@ -739,9 +741,10 @@ def main():
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': dtype_of(args.workload), 'data': 'synthetic',
-            'config': config_for(args.workload, world, args.combine if peer is not None or world == 1 else 'nccl'),
+            'config': config_for(args.workload, world, args.combine if peer is not None or world == 1 else 'nccl', args.dist),
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': UNIT, 'frac': achieved / peak,
-                         'traffic': recorded_traffic(args.workload) if world == 1 else None, 'peak_source': peak_src, 'kernel_ms': kernel_ms,
+                         'traffic': recorded_traffic(args.workload if args.dist == 'uniform' else 'c4_' + args.dist.replace('.', '_')) if world == 1 else None,
+                         'peak_source': peak_src, 'kernel_ms': kernel_ms,
                          'frac_of_8TBs_nominal': achieved / 8000.0},
             'parity_ok': ok,
             'cpu_baseline': cpu, 'e2e': e2e, 'gpu_launches': args.steps * launches_per_step, 'clocks': clocks,
