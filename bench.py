@@ -599,8 +599,9 @@ def main():
         h2d_bytes = sum(t.numel() * t.element_size() for t in e2e_inputs)
         e2e_prepare = w.get('e2e_prepare', lambda: None)
 
-        # the link's own speed: the same pinned buffers copied with nothing else in the step
-        torch.cuda.synchronize()
+        # the link's own speed: the same pinned buffers copied with nothing else in the step (all ranks at once:
+        # the host side of the link is shared)
+        barrier()
         t0 = time.perf_counter()
         for h, t in zip(hosts, e2e_inputs):
             t.copy_(h, non_blocking=True)
@@ -658,8 +659,10 @@ def main():
                             'frac': e2e_val / world / h2d_gbs,
                             'peak_source': 'cudaMemcpyAsync of the same pinned buffers alone, measured in this run '
                                            '(per GPU, slowest rank)'},
-               'numa': 'pinned host buffers are allocated by the rank that uses them; every GPU of this box hangs '
-                       'off NUMA node 0 (SCALE_r01 topology), so node-local placement is what first-touch gives'}
+               'numa': 'pinned host buffers are allocated by the rank that uses them; the 8-GPU boxes of this pool have '
+                       'ONE NUMA node (profiles/r2_numa_probe_8gpu.txt: node0 = cpus 0-31, every GPU NUMA affinity 0), so '
+                       'there is no placement to choose; 8 ranks copying at once share 231 GB/s of host-side bandwidth '
+                       '(4 GPUs at 23 GB/s, 4 at 35 GB/s)'}
         if plugin is not None:
             plugin.close()
         # device-resident arrays through the plug-in: launch + the program's own stream synchronise

@@ -29,7 +29,11 @@ rows_group_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, si
     const unsigned g = lane & (G - 1);            // lane within the row group
     const unsigned sub = lane / G;                // row slot within the warp
     const unsigned rows_per_warp = 32 / G;
-    const size_t warp = (size_t(blockIdx.x) * kRowThreads + threadIdx.x) >> 5;
+    // Warps are numbered CTA-interleaved (warp w of CTA c is global warp w * gridDim.x + c): when the rows do not
+    // fill the last CTAs, every CTA - and with a grid that is a multiple of the SM count every SM - is short of
+    // the same number of rows, instead of some SMs holding one whole CTA more than others (C1: 4096 rows of
+    // 16 KiB were 512 full CTAs on 148 SMs, 4 on some and 3 on others: 16 % imbalance on a one-wave kernel).
+    const size_t warp = size_t(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     const size_t nwarps = (size_t(gridDim.x) * kRowThreads) >> 5;
 
     for (size_t rb = warp * rows_per_warp; rb < rows; rb += nwarps * rows_per_warp) {
@@ -191,6 +195,7 @@ static cudaError_t launch_rows_t(const RowsArgs& a, const Launch& l) {
     size_t grid = (a.rows + rows_per_cta - 1) / rows_per_cta;
     const size_t cap = size_t(sms) * 8;  // 8 x 256 threads = 2048 resident threads per SM
     if (grid > cap) grid = cap;
+    else if (grid > size_t(sms)) grid = ((grid + sms - 1) / sms) * sms;   // whole CTAs per SM (see the kernel)
     if (grid == 0) grid = 1;
     rows_group_kernel<L, A, S, Op, VB, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
         (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G);

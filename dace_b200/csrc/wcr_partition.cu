@@ -56,6 +56,16 @@ constexpr int kPhaseBUnroll = 8;              // 128-bit L2 loads in flight per 
 template <class V>
 __device__ __forceinline__ void smem_add_v(V* p, V v) { atomicAdd(p, v); }
 
+// Bins may be wider than the shared-memory table: 64-bit bins (i64 / u64 / f64) are COUNTED in 32-bit tables
+// (a call has fewer than 2^32 keys) and the counts are scaled by the constant increment when they are flushed.
+template <class W>
+__device__ __forceinline__ void bins_add(W* p, W v) {
+    if constexpr (std::is_same<W, long long>::value)
+        atomicAdd(reinterpret_cast<unsigned long long*>(p), static_cast<unsigned long long>(v));
+    else
+        atomicAdd(p, v);
+}
+
 // L2 residency control for the partition buffer (hint bits of the kernel, DACE_B200_PART_HINT):
 //   1: the key stream is read with an evict-first policy (it is dead after one use);
 //   2: the partitioned keys are stored with an evict-last policy (phase B reads them back a moment later);
@@ -90,9 +100,9 @@ __device__ __forceinline__ void group_sync(unsigned g) {
     asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kGroupThreads) : "memory");
 }
 
-template <class V>
+template <class V, class W>
 __global__ void __launch_bounds__(kPartThreads, 1)
-scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict__ bins, unsigned nbins, V cval,
+scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restrict__ bins, unsigned nbins, V cval, W scale,
                          unsigned* buf, unsigned* gcur, size_t chunk, unsigned cap, int B, int S, int aligned,
                          const int* __restrict__ gate, int divert, int hint) {
     if (*gate != 0) return;   // clustered / skewed keys: one of the kernels behind this one does the work (grid-uniform)
@@ -164,7 +174,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
                 // take their turn at different iterations (it starts at g), so the two paths overlap.
 #pragma unroll
                 for (int j = 0; j < kKeysPerThread; ++j)
-                    if (k[j] < nbins) atomicAdd(bins + k[j], cval);
+                    if (k[j] < nbins) bins_add(bins + k[j], W(cval) * scale);
                 continue;
             }
             // rank inside (tile, bucket); keys >= nbins land in bucket index >= B and are dropped
@@ -247,7 +257,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
                     const unsigned ovf = __ballot_sync(kFullMask, valid && !fits);
                     if (valid && !fits) {
                         const unsigned peers = __match_any_sync(ovf, key);
-                        if (lane == unsigned(__ffs(peers) - 1) && key < nbins) atomicAdd(bins + key, cval * V(__popc(peers)));
+                        if (lane == unsigned(__ffs(peers) - 1) && key < nbins) bins_add(bins + key, W(cval * V(__popc(peers))) * scale);
                     }
                 }
             }
@@ -296,7 +306,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, V* __restr
         for (unsigned i = tid; i < kBucketBins; i += kPartThreads) {
             const V h = hist[i];
             const unsigned bin = b * kBucketBins + i;
-            if (h != V(0) && bin < nbins) atomicAdd(bins + bin, h);
+            if (h != V(0) && bin < nbins) bins_add(bins + bin, W(h) * scale);
         }
     }
 }
@@ -364,7 +374,8 @@ struct PartPlan {
 static bool part_plan(int dtidx, int dtval, bool has_values, size_t n, size_t nbins, PartPlan& p) {
     if (has_values) return false;
     if (dtidx != DT_I32 && dtidx != DT_U32) return false;
-    if (dtval != DT_I32 && dtval != DT_U32 && dtval != DT_F32) return false;
+    if (dtval != DT_I32 && dtval != DT_U32 && dtval != DT_F32 && dtval != DT_I64 && dtval != DT_U64 && dtval != DT_F64)
+        return false;
     if (n < (size_t(1) << 22)) return false;
     if (nbins * 4 <= (size_t(96) << 10) || nbins > size_t(kMaxBuckets) * kBucketBins) return false;
     const int sms = sm_count();
@@ -403,11 +414,16 @@ static bool partition_supported(size_t smem) {
         int coop = 0, occ = 0;
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
         if (coop) {
-            if (cudaFuncSetAttribute(scatter_partition_kernel<int>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
-                cudaFuncSetAttribute(scatter_partition_kernel<unsigned>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
-                cudaFuncSetAttribute(scatter_partition_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            const int sm = (int)smem;
+            const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
+            if (cudaFuncSetAttribute(scatter_partition_kernel<int, int>, at, sm) != cudaSuccess ||
+                cudaFuncSetAttribute(scatter_partition_kernel<unsigned, unsigned>, at, sm) != cudaSuccess ||
+                cudaFuncSetAttribute(scatter_partition_kernel<float, float>, at, sm) != cudaSuccess ||
+                cudaFuncSetAttribute(scatter_partition_kernel<unsigned, long long>, at, sm) != cudaSuccess ||
+                cudaFuncSetAttribute(scatter_partition_kernel<unsigned, unsigned long long>, at, sm) != cudaSuccess ||
+                cudaFuncSetAttribute(scatter_partition_kernel<unsigned, double>, at, sm) != cudaSuccess)
                 coop = 0;
-            else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scatter_partition_kernel<int>, kPartThreads, smem) != cudaSuccess || occ < 1)
+            else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scatter_partition_kernel<int, int>, kPartThreads, smem) != cudaSuccess || occ < 1)
                 coop = 0;
         }
         cudaGetLastError();
@@ -416,8 +432,8 @@ static bool partition_supported(size_t smem) {
     return g_part_coop[dev] == 1;
 }
 
-template <class V>
-static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const PartPlan& p, const Launch& l,
+template <class V, class W>
+static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, W scale, const PartPlan& p, const Launch& l,
                                         const int** gate_out) {
     unsigned char* base = static_cast<unsigned char*>(l.extra);
     int* flag = reinterpret_cast<int*>(base);
@@ -430,7 +446,7 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Part
     scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(keys, n, unsigned(a.nbins), flag);
     const int* gate = flag;
     *gate_out = gate;
-    V* bins = reinterpret_cast<V*>(a.bins);
+    W* bins = reinterpret_cast<W*>(a.bins);
     unsigned nbins = unsigned(a.nbins);
     size_t chunk_arg = p.chunk;
     unsigned cap_arg = p.cap;
@@ -438,8 +454,8 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, const Part
     int aligned = (reinterpret_cast<size_t>(a.idx) & 15) == 0;
     int divert = tuning().part_divert >= 0 ? tuning().part_divert : kDivertDefault;   // tuning knob (0 = off)
     int hint = tuning().part_hint >= 0 ? tuning().part_hint : kHintDefault;
-    void* args[] = {&keys, &n, &bins, &nbins, &cval, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert, &hint};
-    e = cudaLaunchCooperativeKernel((void*)scatter_partition_kernel<V>, dim3(sm_count()), dim3(kPartThreads), args,
+    void* args[] = {&keys, &n, &bins, &nbins, &cval, &scale, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert, &hint};
+    e = cudaLaunchCooperativeKernel((void*)scatter_partition_kernel<V, W>, dim3(sm_count()), dim3(kPartThreads), args,
                                     p.smem, l.stream);
     if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }
     return cudaSuccess;
@@ -454,9 +470,13 @@ cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& 
         return cudaErrorNotSupported;
     if (!partition_supported(p.smem)) return cudaErrorNotSupported;
     switch (dtval) {
-        case DT_I32: { int c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<int>(a, c, p, l, gate); }
-        case DT_U32: { unsigned c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<unsigned>(a, c, p, l, gate); }
-        case DT_F32: { float c = 1.f; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<float>(a, c, p, l, gate); }
+        case DT_I32: { int c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<int, int>(a, c, 1, p, l, gate); }
+        case DT_U32: { unsigned c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<unsigned, unsigned>(a, c, 1u, p, l, gate); }
+        case DT_F32: { float c = 1.f; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<float, float>(a, c, 1.f, p, l, gate); }
+        // 64-bit bins: occurrences are counted in 32-bit tables, the counts scaled by the increment at the flush
+        case DT_I64: { long long c = 1; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, long long>(a, 1u, c, p, l, gate); }
+        case DT_U64: { unsigned long long c = 1; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, unsigned long long>(a, 1u, c, p, l, gate); }
+        case DT_F64: { double c = 1.0; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, double>(a, 1u, c, p, l, gate); }
         default: return cudaErrorNotSupported;
     }
 }

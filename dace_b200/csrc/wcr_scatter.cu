@@ -247,6 +247,14 @@ scatter_smem_kernel(const I* __restrict__ idx, const V* __restrict__ values, V c
 constexpr int kCacheSlots = 16384;                 // 64 KiB of tags + 64 KiB of counts
 constexpr int kCacheThreads = 1024;
 
+template <class V>
+__device__ __forceinline__ void add_any(V* p, V v) {
+    if constexpr (std::is_same<V, long long>::value)
+        atomicAdd(reinterpret_cast<unsigned long long*>(p), static_cast<unsigned long long>(v));
+    else
+        atomicAdd(p, v);
+}
+
 template <class V, int U>
 __global__ void __launch_bounds__(kCacheThreads, 1)
 scatter_cache_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict__ bins, unsigned nbins, V cval,
@@ -266,8 +274,8 @@ scatter_cache_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict_
             const unsigned old = atomicCAS(&tags[slot], 0xffffffffu, k);
             tag = (old == 0xffffffffu) ? k : old;
         }
-        if (tag == k) atomicAdd(&counts[slot], v);
-        else atomicAdd(bins + k, v);
+        if (tag == k) add_any(&counts[slot], v);
+        else add_any(bins + k, v);
     };
     const size_t addr = reinterpret_cast<size_t>(keys);
     size_t h = ((16 - (addr & 15)) & 15) / 4;
@@ -303,18 +311,18 @@ scatter_cache_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict_
     __syncthreads();
     for (int i = threadIdx.x; i < kCacheSlots; i += kCacheThreads) {
         const V c = counts[i];
-        if (c != V(0)) atomicAdd(bins + tags[i], c);
+        if (c != V(0)) add_any(bins + tags[i], c);
     }
 }
 
 // Launched behind the partitioned kernel, gated on the sampler's flag (2 = skewed keys).
 cudaError_t launch_scatter_cache(int dtval, const ScatterArgs& a, const Launch& l) {
-    const size_t smem = size_t(kCacheSlots) * 8;
     const unsigned grid = unsigned(sm_count());
 #define DB200_CACHE_LAUNCH(V)                                                                                   \
     {                                                                                                           \
-        V cval = V(1);                                                                                          \
+        V cval = static_cast<V>(1);                                                                             \
         if (a.const_value) memcpy(&cval, a.const_value, sizeof(V));                                             \
+        const size_t smem = size_t(kCacheSlots) * (sizeof(unsigned) + sizeof(V));                               \
         static PerDeviceOnce once;                                                                              \
         if (bool* done = once.slot(); !*done) {                                                                 \
             cudaError_t e = cudaFuncSetAttribute(scatter_cache_kernel<V, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
@@ -329,6 +337,9 @@ cudaError_t launch_scatter_cache(int dtval, const ScatterArgs& a, const Launch& 
         case DT_I32: DB200_CACHE_LAUNCH(int)
         case DT_U32: DB200_CACHE_LAUNCH(unsigned)
         case DT_F32: DB200_CACHE_LAUNCH(float)
+        case DT_I64: DB200_CACHE_LAUNCH(long long)
+        case DT_U64: DB200_CACHE_LAUNCH(unsigned long long)
+        case DT_F64: DB200_CACHE_LAUNCH(double)
         default: return cudaErrorNotSupported;
     }
 #undef DB200_CACHE_LAUNCH

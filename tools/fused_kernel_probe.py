@@ -4,7 +4,7 @@ import ctypes, os, sys, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import dace_b200 as db
-h = ctypes.CDLL(os.path.join(ROOT, 'tests', 'native', '_built', 'libfused_reduce_harness.so'))
+h = ctypes.CDLL(os.path.join(ROOT, 'tests', 'native', '_built', os.environ.get('FUSED_HARNESS', 'libfused_reduce_harness.so')))
 h.fused_reduce_harness_run.restype = ctypes.c_int
 h.fused_reduce_harness_run.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong,
                                        ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_int, ctypes.c_void_p,
