@@ -76,8 +76,9 @@ cudaError_t launch_arg(int red, int dtin, const ArgArgs& a, const Launch& l);
 struct ScatterArgs {
     const void* idx; const void* values; const void* const_value;
     size_t n; void* bins; size_t nbins;
-    // Device-side path selection: when `gate` is set, a kernel runs only if *gate == gate_run_if
-    // (written by the key sampler of wcr_partition.cu earlier on the same stream).
+    // Device-side path selection: when `gate` is set, a kernel runs only if *gate == gate_run_if, or for a
+    // negative gate_run_if only if *gate != -gate_run_if (written by the key sampler of wcr_partition.cu
+    // earlier on the same stream).
     const int* gate = nullptr; int gate_run_if = 0;
 };
 // reduce_generic.cu: fp32 vector -> bf16 / f16 output with the identity fold (end of a two-pass plan).
@@ -96,5 +97,8 @@ size_t peer_buffer_bytes(int world, size_t cap_bytes);
 // gated on 1.  Scratch = l.extra (the caller's workspace, scatter_partition_bytes() large).
 cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& a, const Launch& l, const int** gate);
 size_t scatter_partition_bytes(int dtidx, int dtval, bool has_values, size_t n, size_t nbins);
+// Scatters with per-element values: only the key sampler runs (flag in l.extra); the caller gates the global-atomic
+// kernel on "flag != 2" (gate_run_if = -2) and the hot-key cache kernel on 2.
+cudaError_t launch_scatter_sample(int dtidx, int dtval, const ScatterArgs& a, const Launch& l, const int** gate);
 
 }  // namespace db200

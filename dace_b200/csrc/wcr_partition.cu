@@ -398,9 +398,29 @@ static bool part_plan(int dtidx, int dtval, bool has_values, size_t n, size_t nb
     return true;
 }
 
+// Per-element values: no partition, but the key sampler still picks between the global atomics and the hot-key
+// cache (skewed keys), so the call wants the 256-byte flag.
+static bool valued_selection_applies(int dtidx, int dtval, size_t n, size_t nbins) {
+    if (dtidx != DT_I32 && dtidx != DT_U32) return false;
+    if (dtval != DT_I32 && dtval != DT_U32 && dtval != DT_F32 && dtval != DT_I64 && dtval != DT_U64 && dtval != DT_F64)
+        return false;
+    return n >= (size_t(1) << 22) && nbins * dtype_size(dtval) > (size_t(96) << 10) && nbins <= 0xffffffffull;
+}
+
 size_t scatter_partition_bytes(int dtidx, int dtval, bool has_values, size_t n, size_t nbins) {
     PartPlan p;
-    return part_plan(dtidx, dtval, has_values, n, nbins, p) ? p.total : 0;
+    if (part_plan(dtidx, dtval, has_values, n, nbins, p)) return p.total;
+    return (has_values && valued_selection_applies(dtidx, dtval, n, nbins)) ? 256 : 0;
+}
+
+// Only the sampler (flag at the start of the caller's scratch): for scatters with per-element values.
+cudaError_t launch_scatter_sample(int dtidx, int dtval, const ScatterArgs& a, const Launch& l, const int** gate) {
+    if (a.values == nullptr || !valued_selection_applies(dtidx, dtval, a.n, a.nbins)) return cudaErrorNotSupported;
+    if (l.extra == nullptr || l.extra_bytes < 256 || (reinterpret_cast<size_t>(l.extra) & 15) != 0) return cudaErrorNotSupported;
+    int* flag = reinterpret_cast<int*>(l.extra);
+    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(reinterpret_cast<const unsigned*>(a.idx), a.n, unsigned(a.nbins), flag);
+    *gate = flag;
+    return cudaGetLastError();
 }
 
 // Cooperative launch + 192 KiB of dynamic shared memory: checked once per device (-1 unknown, 0 no, 1 yes).

@@ -102,7 +102,7 @@ template <int RED, class I, class V, bool HAS_VALUES, int U>
 __global__ void __launch_bounds__(512)
 scatter_global_kernel(const I* __restrict__ idx, const V* __restrict__ values, V cval, size_t n,
                       V* __restrict__ bins, size_t nbins, const int* __restrict__ gate, int gate_run_if) {
-    if (gate != nullptr && *gate != gate_run_if) return;   // the partitioned kernel took this call
+    if (gate != nullptr && (gate_run_if >= 0 ? *gate != gate_run_if : *gate == -gate_run_if)) return;   // another kernel took this call
     const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     const size_t nthr = size_t(gridDim.x) * blockDim.x;
     if constexpr (HAS_VALUES) {
@@ -257,8 +257,8 @@ __device__ __forceinline__ void add_any(V* p, V v) {
 
 template <class V, int U>
 __global__ void __launch_bounds__(kCacheThreads, 1)
-scatter_cache_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict__ bins, unsigned nbins, V cval,
-                     const int* __restrict__ gate, int gate_run_if) {
+scatter_cache_kernel(const unsigned* __restrict__ keys, const V* __restrict__ values, size_t n, V* __restrict__ bins,
+                     unsigned nbins, V cval, const int* __restrict__ gate, int gate_run_if) {
     if (gate != nullptr && *gate != gate_run_if) return;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned* tags = reinterpret_cast<unsigned*>(smem_raw);
@@ -277,6 +277,26 @@ scatter_cache_kernel(const unsigned* __restrict__ keys, size_t n, V* __restrict_
         if (tag == k) add_any(&counts[slot], v);
         else add_any(bins + k, v);
     };
+    if (values != nullptr) {
+        // per-element values: scalar coalesced loads of (key, value), U pairs in flight per thread
+        const size_t tid = size_t(blockIdx.x) * kCacheThreads + threadIdx.x, nthr = size_t(gridDim.x) * kCacheThreads;
+        size_t i = tid;
+        for (; i + size_t(2 * U - 1) * nthr < n; i += size_t(2 * U) * nthr) {
+            unsigned k[2 * U];
+            V v[2 * U];
+#pragma unroll
+            for (int u = 0; u < 2 * U; ++u) { k[u] = __ldg(keys + i + size_t(u) * nthr); v[u] = ldg_scalar(values + i + size_t(u) * nthr); }
+#pragma unroll
+            for (int u = 0; u < 2 * U; ++u) add_key(k[u], v[u]);
+        }
+        for (; i < n; i += nthr) add_key(__ldg(keys + i), ldg_scalar(values + i));
+        __syncthreads();
+        for (int s = threadIdx.x; s < kCacheSlots; s += kCacheThreads) {
+            const V c = counts[s];
+            if (c != V(0)) add_any(bins + tags[s], c);
+        }
+        return;
+    }
     const size_t addr = reinterpret_cast<size_t>(keys);
     size_t h = ((16 - (addr & 15)) & 15) / 4;
     if (h > n) h = n;
@@ -330,7 +350,7 @@ cudaError_t launch_scatter_cache(int dtval, const ScatterArgs& a, const Launch& 
             *done = true;                                                                                       \
         }                                                                                                       \
         scatter_cache_kernel<V, 4><<<grid, kCacheThreads, smem, l.stream>>>(                                    \
-            (const unsigned*)a.idx, a.n, (V*)a.bins, (unsigned)a.nbins, cval, a.gate, a.gate_run_if);           \
+            (const unsigned*)a.idx, (const V*)a.values, a.n, (V*)a.bins, (unsigned)a.nbins, cval, a.gate, a.gate_run_if); \
         return cudaGetLastError();                                                                              \
     }
     switch (dtval) {
@@ -430,6 +450,19 @@ cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, 
             ScatterArgs g = a;
             g.gate = gate;
             g.gate_run_if = 1;
+            e = (dtidx == DT_I32) ? launch_scatter_val<int>(red, dtval, g, l) : launch_scatter_val<unsigned>(red, dtval, g, l);
+            if (e != cudaSuccess) return e;
+            g.gate_run_if = 2;
+            return launch_scatter_cache(dtval, g, l);
+        }
+        if (e != cudaErrorNotSupported) return e;
+        // per-element values (weighted histograms) into a large bin array: the sampler still guards against skewed
+        // keys - hot bins are absorbed by the shared-memory cache instead of serialising in L2
+        e = launch_scatter_sample(dtidx, dtval, a, l, &gate);
+        if (e == cudaSuccess) {
+            ScatterArgs g = a;
+            g.gate = gate;
+            g.gate_run_if = -2;       // anything but "skewed"
             e = (dtidx == DT_I32) ? launch_scatter_val<int>(red, dtval, g, l) : launch_scatter_val<unsigned>(red, dtval, g, l);
             if (e != cudaSuccess) return e;
             g.gate_run_if = 2;

@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 18
+VERSION = 19
 
 
 def up_to_date() -> bool:

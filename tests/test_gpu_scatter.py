@@ -267,3 +267,34 @@ def test_device_side_path_selection(dist, cuda):
         ref = 3 * np.bincount(uniform, minlength=nbins).astype(np.int32)
         np.testing.assert_array_equal(b1.cpu().numpy(), ref)
         np.testing.assert_array_equal(b2.cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize('dist', ['half_hot', 'zipf', 'uniform', 'all_equal'])
+def test_weighted_scatter_large_bins_skew_goes_through_the_hot_key_cache(dist, cuda):
+    """Per-element values into a large bin array: no partition, but the key sampler still routes skewed keys to the
+    shared-memory hot-key cache (values path) instead of letting hot bins serialise in L2.  Integer values exact;
+    float values are small integers, so their sums are exact too whatever the order."""
+    rng = np.random.default_rng(31)
+    n, nbins = (1 << 22) + 1234, 1 << 20
+    if dist == 'half_hot':
+        keys = rng.integers(0, nbins, n)
+        keys[rng.random(n) < 0.5] = 31337
+    elif dist == 'zipf':
+        keys = rng.zipf(1.2, n) % nbins
+    elif dist == 'all_equal':
+        keys = np.full(n, 99)
+    else:
+        keys = rng.integers(-2, nbins + 2, n)          # a few out of range
+    keys = keys.astype(np.int32)
+    ok = (keys >= 0) & (keys < nbins)
+    tk = torch.from_numpy(keys).to(cuda)
+    for dt, tdt in ((np.int32, torch.int32), (np.float32, torch.float32), (np.int64, torch.int64), (np.float64, torch.float64)):
+        w = rng.integers(0, 4, n).astype(dt)
+        start = rng.integers(0, 3, nbins).astype(dt)
+        bins = torch.from_numpy(start.copy()).to(cuda)
+        db.wcr_scatter('lambda a, b: a + b', bins, tk, torch.from_numpy(w).to(cuda))
+        want = start + np.bincount(keys[ok], weights=w[ok].astype(np.float64), minlength=nbins).astype(dt)
+        np.testing.assert_array_equal(bins.cpu().numpy(), want)
+    lib = __import__('dace_b200')._lib.load()
+    assert lib.dace_b200_wcr_scatter_workspace_bytes(3, 2, 0, 1, n, nbins) == 256      # values: the sampler's flag only
+    assert lib.dace_b200_wcr_scatter_workspace_bytes(3, 2, 0, 1, 1000, nbins) == 0
