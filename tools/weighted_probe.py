@@ -13,13 +13,14 @@ u = torch.randint(0, nb, (n,), device=dev, dtype=torch.int32, generator=g)
 # DACE_B200_NO_PARTITION=1 (read when the library is loaded) turns the device-side selection off: run this probe
 # once with and once without it to compare the hot-key cache with plain global atomics.
 label = 'global atomics only' if os.environ.get('DACE_B200_NO_PARTITION') else 'device-side selection'
+wi = torch.randint(0, 5, (n,), device=dev, dtype=torch.int32, generator=g)
 for name, keys in (('uniform', u), ('zipf1.1', z)):
-    for ws in (None, ):
-        bins = torch.zeros(nb, device=dev)
-        db.wcr_scatter('lambda a, b: a + b', bins, keys, w, workspace=ws)
+    for wname, wt in (('f32', w), ('i32', wi)):
+        bins = torch.zeros(nb, device=dev, dtype=wt.dtype)
+        db.wcr_scatter('lambda a, b: a + b', bins, keys, wt)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(3): db.wcr_scatter('lambda a, b: a + b', bins, keys, w, workspace=ws)
+        for _ in range(3): db.wcr_scatter('lambda a, b: a + b', bins, keys, wt)
         e1.record(); torch.cuda.synchronize()
-        print('weighted f32 %-8s %-22s %.3f ms' % (name, label, e0.elapsed_time(e1) / 3), flush=True)
+        print('weighted %s %-8s %-22s %.3f ms' % (wname, name, label, e0.elapsed_time(e1) / 3), flush=True)
