@@ -183,6 +183,18 @@ def _expand_custom(node, state, sdfg, in_desc, out_desc, shape, istr, reduced, o
     else:
         ident_decl = 'const %s __identity = %s;' % (tout, symstr(node.identity, cpp_mode=True))
         ident_arg = '&__identity'
+    # vector interface of the load functor (include/dace_b200_fused_reduce.cuh, VECTOR LOADS): 32 bytes per access
+    kvec = min(8, 32 // in_desc.dtype.bytes) if in_desc.dtype.bytes in (1, 2, 4, 8) else 0
+    vec_code = '' if kvec < 2 else """
+    static constexpr int kVec = %d;
+    using value_type = %s;
+    template <int __V>
+    __device__ __forceinline__ void vec(size_t __row, size_t __col, %s (&__v)[__V]) const {
+        %s __t[__V];
+        dace_b200::stream_load<%s, __V>(in + (long long)__row * s_row + (long long)__col, __t);
+        #pragma unroll
+        for (int __k = 0; __k < __V; ++__k) __v[__k] = (%s)__t[__k];
+    }""" % (kvec, tout, tout, tin, tin, tout)
     sig = ('const %s* __in, %s* __out, size_t __kept, size_t __red, long long __s_kept, long long __s_red, '
            'long long __s_out, void* __workspace, size_t __workspace_bytes, cudaStream_t __stream' % (tin, tout))
     sdfg.append_global_code("""
@@ -196,18 +208,26 @@ struct __b200_custom_load_{id} {{
     const {tin}* __restrict__ in; long long s_row, s_col;
     __device__ __forceinline__ {tout} operator()(size_t __row, size_t __col) const {{
         return ({tout})in[(long long)__row * s_row + (long long)__col * s_col];
-    }}
+    }}{vec_code}
 }};
 DACE_EXPORTED cudaError_t __b200_custom_{id}({sig});
 cudaError_t __b200_custom_{id}({sig}) {{
     {ident_decl}
+    // widest vector access that is legal for this call: unit column stride, rows and base aligned to it
+    const long long __s_col = {s_col}, __s_row = {s_row};
+    const size_t __n = {n};
+    int __max_vec = 1;
+    for (int __v = {kvec}; __v >= 2 && __s_col == 1; __v /= 2)
+        if (__n % __v == 0 && __s_row % __v == 0 && ((size_t)__in % (__v * sizeof({tin}))) == 0) {{ __max_vec = __v; break; }}
     return {call};
 }}
 """.format(id=ident, a=arg1, b=arg2, body=body, tin=tin, tout=tout, sig=sig, ident_decl=ident_decl,
+           kvec=kvec, vec_code=vec_code, s_col='__s_kept' if cols else '__s_red', s_row='__s_red' if cols else '__s_kept',
+           n='__kept' if cols else '__red',
            call=('dace_b200::fused_cols_custom<__b200_custom_op_{id}, {t}, {t}>(__b200_custom_load_{id}{{__in, __s_red, __s_kept}}, '
-                 '__out, (ptrdiff_t)__s_out, __red, __kept, {ia}, __workspace, __workspace_bytes, __stream)' if cols else
+                 '__out, (ptrdiff_t)__s_out, __red, __kept, {ia}, __workspace, __workspace_bytes, __stream, __max_vec)' if cols else
                  'dace_b200::fused_rows_custom<__b200_custom_op_{id}, {t}, {t}>(__b200_custom_load_{id}{{__in, __s_kept, __s_red}}, '
-                 '__out, (ptrdiff_t)__s_out, __kept, __red, {ia}, __workspace, __workspace_bytes, __stream)'
+                 '__out, (ptrdiff_t)__s_out, __kept, __red, {ia}, __workspace, __workspace_bytes, __stream, __max_vec)'
                  ).format(id=ident, t=tout, ia=ident_arg)), 'cuda')
     sdfg.append_global_code('DACE_EXPORTED cudaError_t __b200_custom_%s(%s);\n' % (ident, sig), 'frame')
     ws, ws_bytes = node_workspace(sdfg, state, node)

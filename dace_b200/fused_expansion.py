@@ -216,6 +216,7 @@ def _generate(state, sdfg, m: _Match):
 
     arrays, symbols = [], set()
     body, need_params = [], False
+    vbody, vec_arrays = [], []          # the same tasklets with flat reads taken from vector registers
 
     def note_symbols(expr):
         for s in getattr(expr, 'free_symbols', []):
@@ -235,7 +236,7 @@ def _generate(state, sdfg, m: _Match):
                 need_params = True
             elif fs in sdfg.symbols:
                 symbols.add(fs)
-        lines = []
+        lines, vlines = [], []
         defined = {out_conn: m.value_dtype if final else sdfg.arrays[out_edge.dst.data].dtype}
         for e in state.in_edges(t):
             if e.data.is_empty():
@@ -257,13 +258,19 @@ def _generate(state, sdfg, m: _Match):
                     off = symstr(expr, cpp_mode=True)
                     need_params = True
                 lines.append('const %s %s = %s[%s];' % (d.dtype.ctype, e.dst_conn, name, off))
+                if flat and d.dtype.bytes in (1, 2, 4, 8):
+                    if name not in vec_arrays:
+                        vec_arrays.append(name)
+                    vlines.append('const %s %s = __b200_v_%s[__k];' % (d.dtype.ctype, e.dst_conn, name))
+                else:
+                    vlines.append(lines[-1])
             else:
                 lines.append('const %s %s = %s;' % (sdfg.arrays[e.src.data].dtype.ctype, e.dst_conn, e.src.data))
-        lines.append('%s %s;' % (out_ctype, out_conn))
-        lines.append(_unparse(t.code.as_string, defined))
-        lines.append('%s = %s;' % (out_name, out_conn))
+                vlines.append(lines[-1])
+        tail = ['%s %s;' % (out_ctype, out_conn), _unparse(t.code.as_string, defined), '%s = %s;' % (out_name, out_conn)]
         decl = '' if final else '%s %s;\n        ' % (out_ctype, out_name)
-        body.append(decl + '{ ' + '\n          '.join(lines) + ' }')
+        body.append(decl + '{ ' + '\n          '.join(lines + tail) + ' }')
+        vbody.append(decl + '{ ' + '\n          '.join(vlines + tail) + ' }')
 
     # (row, col) -> map parameters
     rows_expr = 1
@@ -305,6 +312,38 @@ def _generate(state, sdfg, m: _Match):
     else:
         ident_decl = 'const %s __identity = %s;' % (acc, symstr(m.identity, cpp_mode=True))
         ident_arg = '&__identity'
+    # Vector interface (include/dace_b200_fused_reduce.cuh, VECTOR LOADS): operands read at the map's own flat index
+    # are fetched V elements at a time (32 bytes of the widest operand, at most 8), everything else stays as it is.
+    vec_code, vec_arg = '', ''
+    if vec_arrays:
+        kvec = min(8, 32 // max(sdfg.arrays[a].dtype.bytes for a in vec_arrays))
+        loads = ['%s __b200_v_%s[__V]; dace_b200::stream_load<%s, __V>(%s + __flat0, __b200_v_%s);' %
+                 (sdfg.arrays[a].dtype.ctype, a, sdfg.arrays[a].dtype.ctype, a, a) for a in vec_arrays]
+        vec_code = """
+    static constexpr int kVec = {kvec};
+    using value_type = {acc};
+    template <int __V>
+    __device__ __forceinline__ void vec(size_t __row, size_t __col0, {acc} (&__b200_out)[__V]) const {{
+        const size_t __flat0 = {flat0};
+        {loads}
+        #pragma unroll
+        for (int __k = 0; __k < __V; ++__k) {{
+            const size_t __col = __col0 + __k; (void)__col;
+            const size_t __flat = __flat0 + __k; (void)__flat;
+            {pcode}
+            {val} __b200_value;
+            {body}
+            __b200_out[__k] = ({acc})__b200_value;
+        }}
+    }}""".format(kvec=kvec, acc=acc, flat0=flat_expr.replace('__col', '__col0'), loads='\n        '.join(loads),
+                 pcode='\n            '.join(pcode), val=m.value_dtype.ctype, body='\n            '.join(vbody))
+        aligned = ' && '.join('((size_t)%s %% (__v * sizeof(%s))) == 0' % (a, sdfg.arrays[a].dtype.ctype) for a in vec_arrays)
+        vec_arg = ', __b200_max_vec'
+        vec_pick = ('int __b200_max_vec = 1;\n    for (int __v = %d; __v >= 2; __v /= 2)\n'
+                    '        if (((size_t)(%s)) %% __v == 0 && %s) { __b200_max_vec = __v; break; }' %
+                    (kvec, symstr(n_expr, cpp_mode=True), aligned))
+    else:
+        vec_pick = ''
     cuda_code = """
 struct __b200_load_{id} {{
     {members}
@@ -314,18 +353,20 @@ struct __b200_load_{id} {{
         {val} __b200_value;
         {body}
         return ({acc})__b200_value;
-    }}
+    }}{vec_code}
 }};
 DACE_EXPORTED cudaError_t __b200_fused_{id}({sig});
 cudaError_t __b200_fused_{id}({sig}) {{
     __b200_load_{id} __load{{{init}}};
     {ident_decl}
+    {vec_pick}
     return dace_b200::{fn}<{red}, {acc}, {out_t}>(__load, __out, (ptrdiff_t)1, (size_t)({rows}), (size_t)({n}), {ident_arg},
-                                                      __workspace, __workspace_bytes, __stream);
+                                                      __workspace, __workspace_bytes, __stream{vec_arg});
 }}
 """.format(id=ident, members='\n    '.join(members), acc=acc, out_t=out_t, flat=flat_expr, pcode='\n        '.join(pcode),
            val=m.value_dtype.ctype, body='\n        '.join(body), sig=', '.join(sig), init=', '.join(arrays + syms), ident_decl=ident_decl,
-           fn='fused_cols' if m.cols else 'fused_rows', red=int(m.redtype), rows=symstr(rows_expr, cpp_mode=True), n=symstr(n_expr, cpp_mode=True), ident_arg=ident_arg)
+           fn='fused_cols' if m.cols else 'fused_rows', red=int(m.redtype), rows=symstr(rows_expr, cpp_mode=True), n=symstr(n_expr, cpp_mode=True), ident_arg=ident_arg,
+           vec_code=vec_code, vec_pick=vec_pick, vec_arg=vec_arg)
     frame_decl = 'DACE_EXPORTED cudaError_t __b200_fused_%s(%s);\n' % (ident, ', '.join(sig))
     call = ('DACE_GPU_CHECK(__b200_fused_%s(%s));' %
             (ident, ', '.join(['_in_' + a for a in arrays] + ['_out'] + syms +

@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 19
+VERSION = 21
 
 
 def up_to_date() -> bool:
@@ -480,6 +480,46 @@ def _programs(dace):
         if FE.lower_wcr_maps(sdfg) != 1:
             raise RuntimeError('%s: WCRMapToFusedReduce did not apply' % sdfg.name)
         progs.append(sdfg)
+    # (13b) ONE map with several WCR outputs computed by different tasklets (reference tests/multiple_cr_test.py: a
+    #       sum and a product from the same map): split into one map per output (dace_b200/split_wcr.py), each
+    #       piece lowered to a fused tree reduction - through apply_b200, the entry point auto_optimize uses.
+    from dace_b200 import auto as AUTO
+    sdfg = dace.SDFG('b200_multiple_cr')
+    sdfg.add_array('A', [N], dace.int64)
+    sdfg.add_array('s', [1], dace.int64)
+    sdfg.add_array('p', [1], dace.int64)
+    st = sdfg.add_state()
+    me, mx = st.add_map('mymap', dict(i='0:N'))
+    rd = st.add_read('A')
+    for tname, arr, wcr in (('task1', 's', 'lambda a, b: a + b'), ('task2', 'p', 'lambda a, b: a * b')):
+        t = st.add_tasklet(tname, {'a'}, {'b'}, 'b = a')
+        st.add_memlet_path(rd, me, t, dst_conn='a', memlet=dace.Memlet('A[i]'))
+        st.add_memlet_path(t, mx, st.add_write(arr), src_conn='b', memlet=dace.Memlet('%s[0]' % arr, wcr=wcr))
+    sdfg.apply_gpu_transformations()
+    got = AUTO.apply_b200(sdfg)
+    if got['split'] != 1 or got['wcr_fused'] != 2:
+        raise RuntimeError('b200_multiple_cr: %s' % got)
+    progs.append(sdfg)
+
+    @dace.program
+    def b200_two_wcr_rows(A: dace.float32[N, M], s: dace.float32[N], big: dace.float32[N]):
+        for i, j in dace.map[0:N, 0:M]:
+            with dace.tasklet:
+                xin << A[i, j]
+                res >> s(1, lambda x, y: x + y)[i]
+                res = xin
+            with dace.tasklet:
+                xin2 << A[i, j]
+                res2 >> big(1, lambda x, y: max(x, y))[i]
+                res2 = xin2 * xin2
+
+    sdfg = _to_sdfg(b200_two_wcr_rows, simplify=True)
+    sdfg.apply_gpu_transformations()
+    got = AUTO.apply_b200(sdfg)
+    if got['split'] != 1 or got['wcr_fused'] != 2:
+        raise RuntimeError('b200_two_wcr_rows: %s' % got)
+    progs.append(sdfg)
+
     # (14) Custom WCR lambdas on the device-level Reduce node (ReductionType.Custom): the lambda becomes a generated
     #      functor instantiated with the header kernels (dace_b200/expansion.py:_expand_custom), as the reference's
     #      CUB expansion does (reference reduce.py:453-468).  Same SDFGs as the golden vectors the reference's `pure`

@@ -53,6 +53,12 @@ def test_map_body_becomes_a_load_functor(dace):
     assert 'struct __b200_load_fused_cg_' in cu and 'const float __in1 = gpu_A[__flat];' in cu
     assert 'const float __in2 = gpu_mx[i];' in cu and '__out = exp(__in1);' in cu
     assert 'dace_b200::fused_rows<3, float, float>(__load, __out, (ptrdiff_t)1, (size_t)(N), (size_t)(M), &__identity' in cu
+    # vector interface: the operand read at the map's flat index comes through 32-byte accesses, the row-indexed one
+    # stays a scalar read; the call site works out the widest legal access from n and the pointer
+    assert 'static constexpr int kVec = 8;' in cu and 'using value_type = float;' in cu
+    assert 'float __b200_v_gpu_A[__V]; dace_b200::stream_load<float, __V>(gpu_A + __flat0, __b200_v_gpu_A);' in cu
+    assert 'const float __in1 = __b200_v_gpu_A[__k];' in cu and cu.count('const float __in2 = gpu_mx[i];') == 2
+    assert '((size_t)gpu_A % (__v * sizeof(float))) == 0' in cu and '__workspace_bytes, __stream, __b200_max_vec);' in cu
     assert 'DACE_GPU_CHECK(__b200_fused_fused_cg_' in frame and ', __b200_ws_fused_cg_' in frame     # per-kernel workspace
     assert '__global__' not in cu.split('struct __b200_load_')[0] or 'reduce_atomic' not in cu   # no WCR map kernel
     assert FE.fuse_maps_into_reductions(sdfg) == 0

@@ -46,11 +46,7 @@ def _through(dace, sdfg):
     return counts, _census(dace, sdfg)
 
 
-def test_multiple_cr_two_wcr_outputs_of_one_map_stay_on_reference_atomics():
-    """reference tests/multiple_cr_test.py: one map, two tasklets, `s += a` and `p *= a` into scalars.  Left alone:
-    the fused tree-reduction rewrite takes maps with ONE WCR output (two outputs would need two accumulators per
-    thread and two combines in one kernel; the reference's two atomics per element are what runs)."""
-    dace = import_reference()
+def _multiple_cr(dace):
     N = dace.symbol('N')
     sdfg = dace.SDFG('multiple_cr')
     sdfg.add_array('A', [N], dace.int64)
@@ -59,13 +55,55 @@ def test_multiple_cr_two_wcr_outputs_of_one_map_stay_on_reference_atomics():
     state = sdfg.add_state()
     me, mx = state.add_map('mymap', dict(i='0:N'))
     a = state.add_read('A')
+    tasklets = []
     for name, arr, wcr in (('task1', 's', 'lambda a, b: a + b'), ('task2', 'p', 'lambda a, b: a * b')):
         t = state.add_tasklet(name, {'a'}, {'b'}, 'b = a')
         state.add_memlet_path(a, me, t, dst_conn='a', memlet=dace.Memlet('A[i]'))
         state.add_memlet_path(t, mx, state.add_write(arr), src_conn='b', memlet=dace.Memlet('%s[0]' % arr, wcr=wcr))
+        tasklets.append(t)
+    return sdfg, state, tasklets
+
+
+def test_multiple_cr_two_wcr_outputs_of_one_map_are_split_and_fused():
+    """reference tests/multiple_cr_test.py: one map, two tasklets, `s += a` and `p *= a` into scalars.  The outputs come
+    from disjoint tasklets, so the map is split into one map per output (dace_b200/split_wcr.py) and each becomes a
+    fused tree reduction: two streaming passes instead of two same-address atomics per element."""
+    dace = import_reference()
+    sdfg, _, _ = _multiple_cr(dace)
     counts, census = _through(dace, sdfg)
-    assert counts['wcr_fused'] == 0 and counts['scatter'] == 0
-    assert census['wcr_edges'] >= 2 and census['fused_kernels'] == 0
+    assert counts['split'] == 1 and counts['wcr_fused'] == 2 and counts['scatter'] == 0
+    assert census['wcr_edges'] == 0 and census['fused_kernels'] == 2
+
+
+def test_wcr_outputs_that_share_a_tasklet_stay_on_reference_atomics():
+    """The same two outputs fed by ONE tasklet (or through a shared intermediate): splitting would duplicate work the
+    program wrote once, and the fused rewrite takes maps with one WCR output - left alone, stated here."""
+    dace = import_reference()
+    N = dace.symbol('N')
+    sdfg = dace.SDFG('multiple_cr_shared')
+    sdfg.add_array('A', [N], dace.int64)
+    sdfg.add_array('s', [1], dace.int64)
+    sdfg.add_array('p', [1], dace.int64)
+    state = sdfg.add_state()
+    me, mx = state.add_map('mymap', dict(i='0:N'))
+    t = state.add_tasklet('both', {'a'}, {'b', 'c'}, 'b = a\nc = a')
+    state.add_memlet_path(state.add_read('A'), me, t, dst_conn='a', memlet=dace.Memlet('A[i]'))
+    state.add_memlet_path(t, mx, state.add_write('s'), src_conn='b', memlet=dace.Memlet('s[0]', wcr='lambda a, b: a + b'))
+    state.add_memlet_path(t, mx, state.add_write('p'), src_conn='c', memlet=dace.Memlet('p[0]', wcr='lambda a, b: a * b'))
+    counts, census = _through(dace, sdfg)
+    assert counts['split'] == 0 and counts['wcr_fused'] == 0 and census['wcr_edges'] >= 2
+
+
+def test_split_is_undone_when_a_piece_would_not_be_lowered():
+    """One of the two outputs uses an operator the sm_100a kernels do not serve (`a - b`): the map is left whole."""
+    dace = import_reference()
+    sdfg, state, _ = _multiple_cr(dace)
+    for e in state.edges():
+        if e.data.wcr is not None and e.data.data == 'p':
+            e.data.wcr = 'lambda a, b: a - b'
+    before = len(state.nodes())
+    counts, census = _through(dace, sdfg)
+    assert counts['split'] == 0 and counts['wcr_fused'] == 0 and census['wcr_edges'] >= 2
 
 
 def test_confres_reduce_nodes_move_the_mixed_wcr_map_stays():

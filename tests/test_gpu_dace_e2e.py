@@ -455,6 +455,27 @@ def test_wcr_map_reductions(cuda):
     np.testing.assert_array_equal(out, exp)
 
 
+def test_one_map_with_two_wcr_outputs_is_split_and_fused(cuda):
+    """reference tests/multiple_cr_test.py (a sum and a product out of one map) and a rows variant (row sums and row
+    maxima of squares from one 2-D map): dace_b200/split_wcr.py gives each output its own map, both become fused tree
+    reductions that fold into the existing outputs.  Integers exact (the product wraps modulo 2^64 like the
+    reference's), fp32 sums to 1e-5, the max exact."""
+    rng = np.random.default_rng(17)
+    a = rng.integers(1, 4, 100003).astype(np.int64)
+    s, p = np.array([5], np.int64), np.array([3], np.int64)
+    prog('b200_multiple_cr')(A=a, s=s, p=p, N=a.size)
+    with np.errstate(over='ignore'):
+        assert s[0] == 5 + a.sum() and p[0] == np.multiply.reduce(a, dtype=np.int64) * np.int64(3)
+    x = rng.standard_normal((777, 4100)).astype(np.float32)
+    rs, big = np.full(777, 1.5, np.float32), np.full(777, 0.25, np.float32)
+    big[5] = 1e9                                              # an existing value that must survive the max
+    prog('b200_two_wcr_rows')(A=x, s=rs, big=big, N=777, M=4100)
+    np.testing.assert_allclose(rs, 1.5 + x.astype(np.float64).sum(1), rtol=1e-5, atol=1e-3)
+    exp = np.maximum((x * x).max(1), np.float32(0.25))
+    exp[5] = 1e9
+    np.testing.assert_array_equal(big, exp)
+
+
 def test_fused_map_reduce_fp16_accumulates_in_fp32(cuda):
     """fp16 producer and fp16 output, fp32 accumulator: the result is the fp32 sum rounded once to fp16."""
     rng = np.random.default_rng(91)

@@ -151,3 +151,71 @@ def test_fused_custom_functors_cols(cuda, lib, rows, n):
     oi = torch.zeros(n, dtype=torch.int64, device=cuda)
     _run(lib, 31, xi, None, oi, rows, n, True, ws)
     np.testing.assert_array_equal(oi.cpu().numpy(), _add_plus_product_ref(xi, 0, 0))
+
+
+# ---- vector-load functors (kVec / vec(), see VECTOR LOADS in the header) ----
+
+VEC_ROW_SHAPES = [(1, 8), (1, 5000000), (3, 100000), (7, 4104), (600, 5000), (5000, 304), (70000, 40), (300000, 128),
+                  (40000, 512), (3000, 2040), (300, 2047), (11, 64)]
+VEC_COL_SHAPES = [(1, 8), (100000, 8), (4097, 40), (300, 5000), (64, 70000), (1000, 4096), (5, 19000), (33, 1 << 20),
+                  (700, 40000), (9, 1200001)]
+
+
+@pytest.mark.parametrize('rows,n', VEC_ROW_SHAPES)
+@pytest.mark.parametrize('case', [40, 41])
+def test_fused_vector_loads_rows_f32(cuda, lib, case, rows, n):
+    """Same results as the scalar functor, to fp32 rounding (the grouping of the additions differs); odd n and
+    misaligned operands fall back to the scalar kernels inside the same call."""
+    ws = db.Workspace(cuda)
+    g = torch.Generator(device=cuda).manual_seed(rows * 31 + n)
+    buf = torch.randn(rows * n + 8, device=cuda, generator=g)
+    for off in (0, 1):                                              # off = 1: 4 bytes off the vector alignment
+        x = buf[off:off + rows * n].view(rows, n)
+        m = x.max(dim=1).values
+        out = torch.full((rows, ), 3.0, device=cuda)
+        _run(lib, case, x, m, out, rows, n, True, ws)
+        ref = torch.exp(x.double() - m.double()[:, None]).sum(1)
+        assert torch.allclose(out.double(), ref, rtol=2e-5, atol=1e-30)
+        out2 = torch.full((rows, ), 3.0, device=cuda)
+        _run(lib, case, x, m, out2, rows, n, False, None)
+        assert torch.allclose(out2.double(), ref + 3.0, rtol=2e-5)
+
+
+@pytest.mark.parametrize('rows,n', VEC_ROW_SHAPES)
+def test_fused_vector_loads_rows_int64_exact(cuda, lib, rows, n):
+    ws = db.Workspace(cuda)
+    g = torch.Generator(device=cuda).manual_seed(n + 5)
+    al = torch.randint(-10**6, 10**6, (rows, n), device=cuda, dtype=torch.int64, generator=g)
+    w = torch.randint(-10**6, 10**6, (n, ), device=cuda, dtype=torch.int64, generator=g)
+    outl = torch.zeros(rows * 2, dtype=torch.int64, device=cuda)[::2]
+    _run(lib, 42, al, w, outl, rows, n, True, ws)
+    assert torch.equal(outl, (al * w[None, :]).sum(1) + 11)
+    xi = torch.randint(-3, 4, (rows, n), device=cuda, dtype=torch.int64, generator=g) * 2
+    oi = torch.zeros(rows, dtype=torch.int64, device=cuda)
+    _run(lib, 43, xi, None, oi, rows, n, True, ws)                     # custom functor + vector loads
+    np.testing.assert_array_equal(oi.cpu().numpy(), _add_plus_product_ref(xi, 1, 0))
+
+
+@pytest.mark.parametrize('rows,n', VEC_COL_SHAPES)
+def test_fused_vector_loads_cols(cuda, lib, rows, n):
+    ws = db.Workspace(cuda)
+    g = torch.Generator(device=cuda).manual_seed(rows * 7 + n)
+    x = torch.randn(rows, n, device=cuda, generator=g)
+    m = torch.randn(rows, device=cuda, generator=g) * 0.1
+    ref = torch.exp(x.double() - m.double()[:, None]).sum(0)
+    for case in (50, 51):
+        out = torch.full((n, ), 3.0, device=cuda)
+        _run(lib, case, x, m, out, rows, n, True, ws)
+        assert torch.allclose(out.double(), ref, rtol=2e-5, atol=1e-30)
+        out2 = torch.full((n, ), 3.0, device=cuda)
+        _run(lib, case, x, m, out2, rows, n, False, None)
+        assert torch.allclose(out2.double(), ref + 3.0, rtol=2e-5)
+    al = torch.randint(-10**6, 10**6, (rows, n), device=cuda, dtype=torch.int64, generator=g)
+    w = torch.randint(-10**6, 10**6, (n, ), device=cuda, dtype=torch.int64, generator=g)
+    ol = torch.zeros(n * 2, dtype=torch.int64, device=cuda)[::2]
+    _run(lib, 52, al, w, ol, rows, n, True, ws)
+    assert torch.equal(ol, (al * w[None, :]).sum(0) + 11)
+    xi = torch.randint(-3, 4, (rows, n), device=cuda, dtype=torch.int64, generator=g) * 2
+    oi = torch.zeros(n, dtype=torch.int64, device=cuda)
+    _run(lib, 53, xi, None, oi, rows, n, True, ws)
+    np.testing.assert_array_equal(oi.cpu().numpy(), _add_plus_product_ref(xi, 0, 0))
