@@ -193,6 +193,53 @@ class ArgReduceMapToLibrary(xf.SingleStateTransformation):
         return node
 
 
+_IDX_OF_PAIR = re.compile(r'\s*(\w+)\[0\]\.idx\s*')
+
+
+def lower_flat_arg_results(sdfg) -> int:
+    """``np.argmax(A)`` / ``np.argmin(A)`` over ALL elements: keep the result on the data-flow side.
+
+    The frontend reduces a flat view of ``A`` into a one-element (value, index) transient and then reads
+    ``pair[0].idx`` on an INTERSTATE edge into a symbol that the next state stores (reference
+    dace/frontend/python/replacements/reduction.py:276-348).  On a GPU that edge is host code reading a device
+    container, and the reference's own ``apply_gpu_transformations`` rejects the program
+    (``InvalidSDFGInterstateEdgeError``).  Here the symbol is replaced by a memlet: the storing tasklet of the next
+    state reads ``pair[0]`` itself and takes ``.idx`` - after that the GPU transformation goes through, and the
+    reduction map is the ordinary 1-D arg-reduce map that :class:`ArgReduceMapToLibrary` takes.
+
+    Call BEFORE ``apply_gpu_transformations`` (``dace_b200.auto.auto_optimize`` does).  Only the frontend's exact
+    shape is rewritten: the symbol has one use, a tasklet ``__out = <symbol>`` without inputs.  Returns how many."""
+    done = 0
+    for ise in list(sdfg.all_interstate_edges()):
+        for sym, expr in list(ise.data.assignments.items()):
+            m = _IDX_OF_PAIR.fullmatch(expr)
+            if m is None or m.group(1) not in sdfg.arrays:
+                continue
+            arr = m.group(1)
+            desc = sdfg.arrays[arr]
+            if not desc.transient or not isinstance(desc.dtype, dtypes.struct):
+                continue
+            dst = ise.dst
+            if not isinstance(dst, dace.SDFGState):
+                continue
+            users = [n for n in dst.nodes() if isinstance(n, nodes.Tasklet)]
+            if len(users) != 1 or users[0].in_connectors or users[0].code.as_string.strip() != '__out = %s' % sym:
+                continue
+            if any(sym in other.data.free_symbols for other in sdfg.all_interstate_edges() if other is not ise):
+                continue
+            if any(sym in map(str, st.free_symbols) for st in sdfg.states() if st is not dst):
+                continue
+            t = users[0]
+            t.add_in_connector('__pair')
+            t.code = dace.properties.CodeBlock('__out = __pair.idx')
+            dst.add_edge(dst.add_read(arr), None, t, '__pair', dace.Memlet('%s[0]' % arr))
+            del ise.data.assignments[sym]
+            if sym in sdfg.symbols:
+                sdfg.remove_symbol(sym)
+            done += 1
+    return done
+
+
 def use_b200_argreduce(sdfg) -> int:
     """Rewrite every argmin/argmax map the frontend generated; returns how many."""
     return sdfg.apply_transformations_repeated(ArgReduceMapToLibrary, validate=True)

@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 21
+VERSION = 22
 
 
 def up_to_date() -> bool:
@@ -480,6 +480,28 @@ def _programs(dace):
         if FE.lower_wcr_maps(sdfg) != 1:
             raise RuntimeError('%s: WCRMapToFusedReduce did not apply' % sdfg.name)
         progs.append(sdfg)
+    # (12b) np.argmax(A) / np.argmin(A) over ALL elements: the frontend reads the (value, index) pair on an interstate
+    #       edge, which the reference's GPU transformation rejects; arg_node.lower_flat_arg_results turns the read into
+    #       a memlet first, then the 1-D arg-reduce map becomes an ArgReduce node like the axis forms.
+    from dace_b200 import arg_node as AN
+
+    @dace.program
+    def b200_flat_argmax_f32(A: dace.float32[N, M], out: dace.int64[1]):
+        out[0] = np.argmax(A)
+
+    @dace.program
+    def b200_flat_argmin_i32(A: dace.int32[N, M, K], out: dace.int64[1]):
+        out[0] = np.argmin(A)
+
+    for p in (b200_flat_argmax_f32, b200_flat_argmin_i32):
+        sdfg = _to_sdfg(p, simplify=True)
+        if AN.lower_flat_arg_results(sdfg) != 1:
+            raise RuntimeError('%s: flat arg result not lowered' % sdfg.name)
+        sdfg.apply_gpu_transformations()
+        if AN.use_b200_argreduce(sdfg) != 1:
+            raise RuntimeError('%s: ArgReduceMapToLibrary did not apply' % sdfg.name)
+        progs.append(sdfg)
+
     # (13b) ONE map with several WCR outputs computed by different tasklets (reference tests/multiple_cr_test.py: a
     #       sum and a product from the same map): split into one map per output (dace_b200/split_wcr.py), each
     #       piece lowered to a fused tree reduction - through apply_b200, the entry point auto_optimize uses.

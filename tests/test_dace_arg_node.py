@@ -76,3 +76,49 @@ def test_other_maps_are_left_alone_and_host_arrays_rejected(dace):
     assert AN.use_b200_argreduce(host) == 1            # explicit request ...
     with pytest.raises(ValueError, match='no CPU fallback'):
         host.expand_library_nodes()                    # ... fails loudly instead of falling back
+
+
+def test_flat_argmax_is_kept_on_the_data_flow_side(dace):
+    """np.argmax(A) over all elements: the frontend reads `pair[0].idx` on an interstate edge, which the reference's
+    own GPU transformation rejects; lower_flat_arg_results replaces the symbol by a memlet, after which the program
+    moves to the GPU and the 1-D arg-reduce map becomes an ArgReduce node."""
+    from dace.sdfg.validation import InvalidSDFGInterstateEdgeError
+    from dace_b200 import arg_node as AN
+    N, M = dace.symbol('N', dace.int64), dace.symbol('M', dace.int64)
+
+    @dace.program
+    def flat(A: dace.float32[N, M], out: dace.int64[1]):
+        out[0] = np.argmax(A)
+
+    rejected = flat.to_sdfg(simplify=True)
+    with pytest.raises(InvalidSDFGInterstateEdgeError):
+        rejected.apply_gpu_transformations()               # the reference as it is
+    sdfg = flat.to_sdfg(simplify=True)
+    assert AN.lower_flat_arg_results(sdfg) == 1
+    assert AN.lower_flat_arg_results(sdfg) == 0
+    assert not any(e.data.assignments for e in sdfg.all_interstate_edges())
+    sdfg.validate()
+    sdfg.apply_gpu_transformations()
+    assert AN.use_b200_argreduce(sdfg) == 1
+    node = next(n for n, _ in sdfg.all_nodes_recursive() if isinstance(n, AN.ArgReduce))
+    assert node.func == 'max' and node.axis == 0           # axis 0 of the flat view
+    code = ''.join(c.clean_code for c in sdfg.generate_code())
+    assert 'dace_b200_reduce_arg(12, 0, 2, _in,' in code and '__pair.idx' in code and 'wcr_custom' not in code
+
+
+def test_flat_arg_lowering_leaves_other_interstate_reads_alone(dace):
+    from dace_b200 import arg_node as AN
+    N = dace.symbol('N', dace.int64)
+
+    @dace.program
+    def branchy(A: dace.float32[N], out: dace.int64[1]):
+        k = np.argmax(A)
+        if k > 3:                                          # the symbol feeds a condition: not the frontend's store shape
+            out[0] = k
+        else:
+            out[0] = 0
+
+    sdfg = branchy.to_sdfg(simplify=True)
+    before = sum(len(e.data.assignments) for e in sdfg.all_interstate_edges())
+    assert AN.lower_flat_arg_results(sdfg) == 0
+    assert sum(len(e.data.assignments) for e in sdfg.all_interstate_edges()) == before

@@ -322,6 +322,27 @@ def test_np_argmax_argmin_dace_programs(cuda):
     np.testing.assert_array_equal(outb, np.argmax(big, axis=1))
 
 
+def test_np_argmax_over_all_elements(cuda):
+    """np.argmax(A) / np.argmin(A) without an axis: flat index of the first extreme element (NumPy's rule and the
+    reference frontend's sequential order); the reference itself cannot put these programs on a GPU."""
+    rng = np.random.default_rng(33)
+    a = rng.standard_normal((777, 3001)).astype(np.float32)
+    out = np.array([-7], np.int64)
+    prog('b200_flat_argmax_f32')(A=a, out=out, N=777, M=3001)
+    assert out[0] == np.argmax(a)
+    a[5, 17] = a[600, 2] = a.max() + 1                             # a tie: the first occurrence wins
+    prog('b200_flat_argmax_f32')(A=a, out=out, N=777, M=3001)
+    assert out[0] == 5 * 3001 + 17
+    big = rng.standard_normal((4, 1 << 21)).astype(np.float32)     # one long flat row: split over CTAs
+    prog('b200_flat_argmax_f32')(A=big, out=out, N=4, M=1 << 21)
+    assert out[0] == np.argmax(big)
+    m = rng.integers(-9, 9, (33, 100, 17)).astype(np.int32)        # many ties
+    prog('b200_flat_argmin_i32')(A=m, out=out, N=33, M=100, K=17)
+    assert out[0] == np.argmin(m)
+    ridx, _ = O.reduce_arg(O.MIN_LOCATION, m.reshape(1, -1), 1)
+    assert out[0] == ridx[0]
+
+
 # ---- row max + row sum fused into one pass (dace_b200/fuse_node.py -> dace_b200_reduce_rows_max_sum) ----
 
 def test_fused_row_max_sum_programs(cuda):
@@ -407,6 +428,52 @@ def test_fused_map_reduce_programs(cuda):
     o3 = np.zeros((19, 23))
     prog('b200_fused_weighted_3d')(A=t, w=w, out=o3, N=19, M=23, K=500)
     np.testing.assert_allclose(o3, (t * w[None, None, :] + np.arange(19)[:, None, None]).sum(2), rtol=1e-12, atol=1e-9)
+
+
+def test_fused_programs_take_the_vector_loads_when_the_call_allows(cuda):
+    """The generated load functors carry vec() for operands at the map's flat index; the call site picks the widest
+    legal access from n and the pointers at run time.  Same programs as above at shapes / pointers that do (n a
+    multiple of 8, aligned) and do not (base pointer 4 bytes off) qualify - same results either way."""
+    import torch
+    g = torch.Generator(device=cuda)
+    g.manual_seed(5)
+    for rows, n in ((512, 4096), (3000, 256), (40000, 64), (3, 1 << 21)):
+        buf = torch.randn(rows * n + 8, device=cuda, generator=g)
+        for off in (0, 1):
+            a = buf[off:off + rows * n].view(rows, n)
+            mx = a.max(dim=1).values.contiguous()
+            ref = torch.exp(a.double() - mx.double()[:, None]).sum(1)
+            s = torch.zeros(rows, device=cuda)
+            prog('b200_fused_softmax_den')(A=a.data_ptr(), mx=mx.data_ptr(), s=s.data_ptr(), N=rows, M=n)
+            torch.cuda.synchronize()
+            assert torch.allclose(s.double(), ref, rtol=2e-5), (rows, n, off)
+    rng = np.random.default_rng(66)
+    f = rng.standard_normal((1024, 2048))
+    out = np.zeros(1)
+    prog('b200_fused_sumsq')(A=f, s=out, N=1024, M=2048)
+    np.testing.assert_allclose(out[0], (f * f).sum(), rtol=1e-12)
+    x = rng.integers(-10**6, 10**6, (333, 4096)).astype(np.int32)
+    y = rng.integers(-10**6, 10**6, (333, 4096)).astype(np.int32)
+    o = np.zeros(333, np.int32)
+    prog('b200_fused_absdiff_max')(A=x, B=y, out=o, N=333, M=4096)
+    np.testing.assert_array_equal(o, np.abs(x - y).max(1))
+    xc = rng.integers(-10**6, 10**6, (4099, 8192)).astype(np.int32)
+    yc = rng.integers(-10**6, 10**6, (4099, 8192)).astype(np.int32)
+    oc = np.full(8192, -5, np.int32)
+    prog('b200_wcr_cols_max_i32')(A=xc, B=yc, out=oc, N=4099, M=8192)
+    np.testing.assert_array_equal(oc, np.maximum((xc - yc).max(0), -5))
+    # custom lambdas (a + b + a * b on int64): rows, columns and everything, vector-eligible sizes
+    for name, shape, dim in (('b200_custom_app_i64_rows', (7, 3000000), 1), ('b200_custom_app_i64_cols', (30001, 1024), 0),
+                             ('b200_custom_app_i64_full', (5000000, ), 0)):
+        xi = torch.randint(-3, 4, shape, device=cuda, dtype=torch.int64, generator=g) * 2
+        kept = [sz for i, sz in enumerate(shape) if i != dim] if len(shape) > 1 else [1]
+        oi = torch.zeros(kept, dtype=torch.int64, device=cuda)
+        prog(name)(A=xi.data_ptr(), B=oi.data_ptr(), **{'D%d' % i: sz for i, sz in enumerate(shape)})
+        torch.cuda.synchronize()
+        fu = (xi.cpu().numpy() + 1).astype(np.uint64)
+        with np.errstate(over='ignore'):
+            refi = (np.multiply.reduce(fu, axis=dim, dtype=np.uint64) - np.uint64(1)).astype(np.int64)
+        np.testing.assert_array_equal(oi.cpu().numpy().reshape(refi.shape), refi)
 
 
 def test_fused_map_reduce_column_fold(cuda):
