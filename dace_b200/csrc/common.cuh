@@ -405,6 +405,24 @@ struct Tuning {
 const Tuning& tuning();
 
 // Per-device "done once" flags for cudaFuncSetAttribute (function attributes are per device).
+// CTAs of one kernel instantiation that fit an SM (the register and shared-memory use of THIS build decide).
+// Persistent grids are sized as sm_count() * this: a grid sized for 8 CTAs/SM of a kernel that fits 6 runs 1.33
+// waves, and since every CTA of a persistent kernel carries the same share of the work the last third of a wave
+// costs a whole one (measured, rows [8M, 33]: 0.59 -> 0.8 of the HBM peak).  Host-side arithmetic on the function's
+// attributes, no synchronisation; cached per device.
+template <auto Kernel>
+inline int resident_ctas(int threads, size_t dynamic_smem = 0) {
+    static int cache[64];                         // 0 = not asked yet
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    int v = cache[dev];
+    if (v == 0) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, Kernel, threads, dynamic_smem) != cudaSuccess || v < 1) v = 1;
+        cache[dev] = v;
+    }
+    return v;
+}
+
 struct PerDeviceOnce {
     bool done[64] = {false};
     bool* slot() {

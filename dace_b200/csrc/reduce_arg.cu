@@ -362,7 +362,8 @@ static cudaError_t launch_arg_t(const ArgArgs& a_in, const Launch& l) {
             while (G < 32 && size_t(G) * 64 < row_bytes) G <<= 1;
             const size_t rows_per_cta = size_t(kArgThreads / 32) * (32 / G);
             size_t grid = (rows + rows_per_cta - 1) / rows_per_cta;
-            if (grid > sms * 8) grid = sms * 8;
+            const size_t cap = size_t(sms) * resident_ctas<arg_rows_group_kernel<L, A, IsMax>>(kArgThreads);
+            if (grid > cap) grid = cap;
             if (grid == 0) grid = 1;
             arg_rows_group_kernel<L, A, IsMax><<<(unsigned)grid, kArgThreads, 0, l.stream>>>(
                 (const L*)a.in, rows, n, a.inner, a.in_stride_o, a.in_stride_i, out, init, G);

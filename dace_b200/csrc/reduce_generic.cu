@@ -112,14 +112,15 @@ static cudaError_t launch_generic_t(const GenericArgs& a, const Launch& l) {
     // Empty axis list: the reference copies input to output and ignores the
     // identity (reference dace/libraries/standard/nodes/reduce.py:77-87).
     if (a.copy_only) fin.has_identity = 2;
-    const long long cap = (long long)sm_count() * 8;
     if (a.warp_per_output) {
+        const long long cap = (long long)sm_count() * resident_ctas<generic_kernel<L, A, S, Op, true>>(256);
         long long grid = (nout + 7) / 8;
         if (grid > cap) grid = cap;
         if (grid < 1) grid = 1;
         generic_kernel<L, A, S, Op, true><<<(unsigned)grid, 256, 0, l.stream>>>(
             (const L*)a.in, (S*)a.out, d, nout, nred, fin);
     } else {
+        const long long cap = (long long)sm_count() * resident_ctas<generic_kernel<L, A, S, Op, false>>(256);
         long long grid = (nout + 255) / 256;
         if (grid > cap) grid = cap;
         if (grid < 1) grid = 1;

@@ -149,12 +149,14 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
     const unsigned n = unsigned(a.n);
     const unsigned rows_per_tile = kTinyTile / n;
     const size_t ntiles = (a.rows + rows_per_tile - 1) / rows_per_tile;
-    size_t grid = size_t(sm_count()) * 8;
-    if (grid > ntiles) grid = ntiles;
     Finish<A> fin = make_finish<A, S>(a.identity);
 #define DB200_TINY(W)                                                                                                   \
-    rows_tiny_kernel<L, A, S, Op, W><<<(unsigned)grid, kRowThreads, 0, l.stream>>>((const L*)a.in, (S*)a.out, a.rows, n, \
-                                                                                  rows_per_tile, a.out_stride, fin)
+    do {                                                                                                                \
+        size_t grid = size_t(sm_count()) * resident_ctas<rows_tiny_kernel<L, A, S, Op, W>>(kRowThreads);                 \
+        if (grid > ntiles) grid = ntiles;                                                                               \
+        rows_tiny_kernel<L, A, S, Op, W><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(                                  \
+            (const L*)a.in, (S*)a.out, a.rows, n, rows_per_tile, a.out_stride, fin);                                    \
+    } while (0)
     // lanes per row: a thread per row while a tile holds at least 64 rows (n <= 64: measured faster than two lanes
     // per row, [8M, 33] 0.63 vs 0.57 of the peak); for longer rows as many lanes as keep the 256 threads busy in the
     // fold ([2.7M, 100]: 40 rows per tile, 4 lanes each, 0.54 -> 0.61)
@@ -185,7 +187,8 @@ static cudaError_t launch_rows_t(const RowsArgs& a, const Launch& l) {
     const size_t row_bytes = a.n * sizeof(L);
     const int sms = sm_count();
     if (row_bytes >= (size_t(32) << 10)) {
-        size_t grid = a.rows < size_t(sms) * 8 ? a.rows : size_t(sms) * 8;
+        const size_t slots = size_t(sms) * resident_ctas<rows_block_kernel<L, A, S, Op, VB, 4>>(kRowThreads);
+        size_t grid = a.rows < slots ? a.rows : slots;
         rows_block_kernel<L, A, S, Op, VB, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
             (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin);
         return cudaGetLastError();
@@ -193,7 +196,7 @@ static cudaError_t launch_rows_t(const RowsArgs& a, const Launch& l) {
     const int G = pick_group(row_bytes);
     const size_t rows_per_cta = size_t(kRowThreads / 32) * (32 / G);
     size_t grid = (a.rows + rows_per_cta - 1) / rows_per_cta;
-    const size_t cap = size_t(sms) * 8;  // 8 x 256 threads = 2048 resident threads per SM
+    const size_t cap = size_t(sms) * resident_ctas<rows_group_kernel<L, A, S, Op, VB, 4>>(kRowThreads);   // one full wave
     if (grid > cap) grid = cap;
     else if (grid > size_t(sms)) grid = ((grid + sms - 1) / sms) * sms;   // whole CTAs per SM (see the kernel)
     if (grid == 0) grid = 1;
@@ -295,7 +298,7 @@ static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& 
     const int G = pick_group(a.n * sizeof(L));
     const size_t rows_per_cta = size_t(kRowThreads / 32) * (32 / G);
     size_t grid = (a.rows + rows_per_cta - 1) / rows_per_cta;
-    const size_t cap = size_t(sms) * 8;
+    const size_t cap = size_t(sms) * resident_ctas<rows_max_sum_kernel<L, 32, 4>>(kRowThreads);
     if (grid > cap) grid = cap;
     if (grid == 0) grid = 1;
     rows_max_sum_kernel<L, 32, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(

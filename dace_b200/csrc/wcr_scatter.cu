@@ -393,7 +393,9 @@ static cudaError_t launch_scatter_t(const ScatterArgs& a, const Launch& l) {
 #undef DB200_SMEM_LAUNCH
         return cudaGetLastError();
     }
-    size_t grid = size_t(sms) * 4;
+    // a persistent grid of exactly one wave (what fits depends on the instantiation's registers)
+    size_t grid = size_t(sms) * (a.values ? resident_ctas<scatter_global_kernel<RED, I, V, true, 4>>(512)
+                                          : resident_ctas<scatter_global_kernel<RED, I, V, false, 4>>(512));
     const size_t need = (a.n + 511) / 512;
     if (grid > need) grid = need;
     if (a.values)

@@ -269,6 +269,34 @@ def test_cols_all_decompositions(outer, red, inner, cuda):
         np.testing.assert_array_equal(got, ref)
 
 
+@pytest.mark.parametrize('outer,red,inner', [(1, 7, 300004), (1, 7, 300001), (2, 5, 400000), (1, 3, 1000002),
+                                             (1, 64, 80000), (3, 1, 90000), (1, 9, 77777 * 4)])
+def test_few_rows_many_columns(outer, red, inner, cuda):
+    """[R <= 64, K] column folds (thread-per-column kernel, CTAs walk 1024-column chunks): whole chunks and the ragged
+    last one, 1 ... 64 rows (groups of four + tail), several outer slices, a view that starts one element into the
+    allocation, folding into an existing output."""
+    rng = np.random.default_rng(outer * 100 + red)
+    a = rng.uniform(-1, 1, (outer, red, inner)).astype(np.float32)
+    got, ref = _run(a, (1, ), 'sum', cuda)
+    _check(got, ref, np.float32, a, (1, ))
+    for dt in (np.int32, np.int64, np.float64):
+        ai = rng.integers(-100, 100, (outer, red, inner)).astype(dt)
+        for op in ('sum', 'max'):
+            got, ref = _run(ai, (1, ), op, cuda)
+            np.testing.assert_array_equal(got, ref)
+    # a view one element into the allocation (same pitch): not 16-byte aligned any more
+    buf = torch.from_numpy(rng.integers(-100, 100, outer * red * inner + 4).astype(np.int32)).to(cuda)
+    v = buf[1:1 + outer * red * inner].view(outer, red, inner)
+    out = torch.empty((outer, inner), dtype=torch.int32, device=cuda)
+    db.reduce('lambda a, b: a + b', v, out, axis=1, identity=0)
+    assert torch.equal(out, v.sum(1, dtype=torch.int32))
+    # identity None: fold into the existing output
+    out2 = torch.full((outer, inner), 5, dtype=torch.int32, device=cuda)
+    w = buf[:outer * red * inner].view(outer, red, inner)
+    db.reduce('lambda a, b: a + b', w, out2, axis=1, identity=None)
+    assert torch.equal(out2, w.sum(1, dtype=torch.int32) + 5)
+
+
 def test_bf16_f16_fp32_accumulate(cuda):
     """bf16/f16 inputs, fp32 accumulation and fp32 outputs; sum of 128 ones == 128
     (reference tests/fp8_bf16_dtypes_test.py:130-150)."""

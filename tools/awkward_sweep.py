@@ -30,6 +30,9 @@ cases = [
     ('[32,64,32,1024] (1,3)', (32, 64, 32, 1024), (1, 3)), ('[64,64,64,64,4] (1,3)', (64, 64, 64, 64, 4), (1, 3)),
     ('[N,M,K] mid axis 1', (1024, 256, 1024), (1, )),
 ]
+ONLY = sys.argv[1:]       # case names (substring match): run just those, e.g. for an ncu capture
+if ONLY:
+    cases = [c for c in cases if any(o in c[0] for o in ONLY)]
 print('%-28s %10s %9s %6s' % ('case', 'ms', 'GB/s', 'frac'))
 for name, shape, axes in cases:
     x = torch.rand(shape, device=dev)
@@ -39,6 +42,8 @@ for name, shape, axes in cases:
     ok = torch.allclose(out.double(), x.double().sum(axes) if axes is not None else x.double().sum(), rtol=1e-4)
     print('%-28s %10.3f %9.0f %6.2f %s' % (name, ms, gbs, gbs / PEAK, '' if ok else 'BAD'), flush=True)
     del x, out
+if ONLY:
+    sys.exit(0)
 # unaligned pointers: a view that starts 1 element into the allocation
 base = torch.rand(N + 8, device=dev)
 for off in (1, 3):
