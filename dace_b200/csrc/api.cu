@@ -42,6 +42,7 @@ static Tuning read_tuning() {
     t.no_partition = flag("DACE_B200_NO_PARTITION");
     t.no_tiled = flag("DACE_B200_NO_TILED");
     t.no_tiny_rows = flag("DACE_B200_NO_TINY_ROWS");
+    t.no_outer_first = flag("DACE_B200_NO_OUTER_FIRST");
     t.wide_wc = num("DACE_B200_WIDE_WC", 0);
     t.part_chunk_log2 = num("DACE_B200_PART_CHUNK_LOG2", 0);
     t.part_divert = num("DACE_B200_PART_DIVERT", -1);
@@ -206,6 +207,32 @@ static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, v
     return e;
 }
 
+// The same layout, OUTER axis first, for dense [R1, K, R2] with R1 >= R2: pass 1 folds R1 with the column kernels
+// over rows of K * R2 contiguous elements into mid[K, R2] (the widest, best-streaming form the array has), pass 2
+// folds the R2 runs of that small intermediate.  The intermediate is 1 / R1 of the input instead of 1 / R2, and a
+// short innermost axis never meets the tiny-row kernel at full size ([4096, 512, 8] f32: 35 -> ~17 us).
+static size_t outer_first_bytes(int dtin, size_t K, size_t R2) {
+    const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
+    return (K * R2 * dtype_size(dtmid) + 255) & ~size_t(255);
+}
+
+static cudaError_t plan_outer_first(int red, int dtin, int dtout, const void* in, void* out, size_t R1, size_t K,
+                                    size_t R2, ptrdiff_t out_stride_k, const void* identity, const Launch& l) {
+    const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
+    unsigned char neutral[8];
+    if (!supported_pair(dtin, dtmid) || !supported_pair(dtmid, dtout) || !neutral_bytes(red, dtmid, neutral))
+        return cudaErrorNotSupported;
+    const size_t need = outer_first_bytes(dtin, K, R2);
+    if (need > kMidMaxBytes) return cudaErrorNotSupported;
+    if (l.dry_need) { l.take(need); return cudaSuccess; }
+    if (need > l.extra_bytes) return cudaErrorNotSupported;
+    void* mid = l.extra;
+    ColsArgs a{in, mid, 1, R1, K * R2, 0, K * R2, 0, 1, neutral};
+    cudaError_t e = plan_cols(red, dtin, dtmid, a, l);
+    if (e != cudaSuccess) return e;
+    return plan_rows(red, dtmid, dtout, mid, out, K, R2, R2, out_stride_k, identity, l);
+}
+
 // The canonical forms that have a streaming kernel; cudaErrorNotSupported = none of them.
 static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void* out, const Dim* c, int nc, int nr,
                              const void* identity, const Launch& l) {
@@ -236,6 +263,11 @@ static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void*
     if (nr > 0 && nc == 3 && c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 &&
         c[1].in_stride >= c[2].shape && c[0].in_stride == c[1].in_stride * c[1].shape && c[2].shape >= 2 &&
         !tuning().no_two_pass) {
+        if (c[1].in_stride == c[2].shape && c[0].shape >= c[2].shape && !tuning().no_outer_first) {   // fully dense, long outer axis
+            cudaError_t e1 = plan_outer_first(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape,
+                                              (size_t)c[2].shape, (ptrdiff_t)c[1].out_stride, identity, l);
+            if (e1 != cudaErrorNotSupported) return e1;
+        }
         cudaError_t e2 = plan_two_pass(red, dtin, dtout, in, out, 1, (size_t)c[0].shape, (size_t)c[1].shape,
                                        (size_t)c[2].shape, (size_t)c[1].in_stride, 0, (ptrdiff_t)c[1].out_stride,
                                        identity, l);

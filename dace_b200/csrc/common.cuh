@@ -396,7 +396,8 @@ struct Launch {
 
 // Experiment knobs (environment variables), read ONCE when the library is loaded - never on a call path.
 struct Tuning {
-    bool no_two_pass, no_axis_sort, no_peel, no_wide_cols, no_few_rows, no_narrow_cols, no_partition, no_tiled, no_tiny_rows;
+    bool no_two_pass, no_axis_sort, no_peel, no_wide_cols, no_few_rows, no_narrow_cols, no_partition, no_tiled, no_tiny_rows,
+         no_outer_first;
     int wide_wc;            // DACE_B200_WIDE_WC (0 = default)
     int part_chunk_log2;    // DACE_B200_PART_CHUNK_LOG2 (0 = default)
     int part_divert;        // DACE_B200_PART_DIVERT (-1 = default)

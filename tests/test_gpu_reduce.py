@@ -409,7 +409,8 @@ def test_cols_wide_rows_bf16_and_2d(cuda):
 
 @pytest.mark.parametrize('dtype', [np.float32, np.float64, np.int32, np.int64, np.uint32, np.uint64, np.int8])
 @pytest.mark.parametrize('op', ['sum', 'max', 'min', 'prod'])
-@pytest.mark.parametrize('shape', [[6, 50, 64], [33, 7, 1000], [3, 300, 32], [2, 5, 40000]])
+@pytest.mark.parametrize('shape', [[6, 50, 64], [33, 7, 1000], [3, 300, 32], [2, 5, 40000],
+                                   [300, 7, 33], [2049, 64, 8], [70, 5, 70], [5000, 3, 2]])   # R1 >= R2: outer axis first
 def test_outer_inner_axes_two_pass(dtype, op, shape, cuda):
     """Per-channel statistics layout (axes (0, 2) of [N, C, H*W]); int8 has no two-pass plan and must
     still be right through the generic kernel."""
@@ -503,13 +504,18 @@ def test_two_pass_sixteen_bit_outputs(tdt, cuda):
     once (given, or the value already in the output)."""
     dt = getattr(torch, tdt)
     eps = 2.0 ** -8 if tdt == 'bfloat16' else 2.0 ** -11
-    x = (torch.rand(12, 40, 3000, device=cuda) - 0.3).to(dt)
+    _two_pass_sixteen_bit(torch.rand(12, 40, 3000, device=cuda), dt, eps)
+    _two_pass_sixteen_bit(torch.rand(3000, 40, 12, device=cuda), dt, eps)      # long outer axis: folded first
+
+
+def _two_pass_sixteen_bit(u, dt, eps):
+    x = (u - 0.3).to(dt)
     truth = x.double().sum((0, 2))
     scale = x.double().abs().sum((0, 2))
     got = db.reduce('lambda a, b: a + b', x, axis=(0, 2), identity=0)
     assert got.dtype == dt
     assert bool(((got.double() - truth).abs() <= eps * truth.abs() + 1e-5 * scale).all())
-    out = torch.full((40, ), 2.0, device=cuda, dtype=dt)
+    out = torch.full((40, ), 2.0, device=x.device, dtype=dt)
     db.reduce('lambda a, b: a + b', x, out, axis=(0, 2), identity=None)
     assert bool(((out.double() - (truth + 2.0)).abs() <= eps * (truth + 2.0).abs() + 1e-5 * scale).all())
     mx = db.reduce('lambda a, b: max(a, b)', x, axis=(0, 2), identity=-3e38)
