@@ -45,6 +45,7 @@ static Tuning read_tuning() {
     t.no_outer_first = flag("DACE_B200_NO_OUTER_FIRST");
     t.wide_wc = num("DACE_B200_WIDE_WC", 0);
     t.part_chunk_log2 = num("DACE_B200_PART_CHUNK_LOG2", 0);
+    t.rows_lane_bytes = num("DACE_B200_ROWS_LANE_BYTES", 0);
     t.part_divert = num("DACE_B200_PART_DIVERT", -1);
     t.part_hint = num("DACE_B200_PART_HINT", -1);
     return t;
@@ -139,6 +140,8 @@ static bool neutral_bytes(int red, int dt, unsigned char out[8]) {
                 case DT_F64: return put(1.0);
                 case DT_I32: case DT_U32: return put((int)1);
                 case DT_I64: case DT_U64: return put((long long)1);
+                case DT_I16: case DT_U16: return put((short)1);
+                case DT_I8: case DT_U8: return put((signed char)1);
                 default: return false;
             }
         case RT_BAnd: memset(out, 0xff, 8); return dt != DT_F32 && dt != DT_F64;
@@ -150,6 +153,10 @@ static bool neutral_bytes(int red, int dt, unsigned char out[8]) {
                 case DT_U32: return put(mn ? std::numeric_limits<unsigned>::max() : 0u);
                 case DT_I64: return put(mn ? std::numeric_limits<long long>::max() : std::numeric_limits<long long>::lowest());
                 case DT_U64: return put(mn ? std::numeric_limits<unsigned long long>::max() : 0ull);
+                case DT_I16: return put(mn ? std::numeric_limits<short>::max() : std::numeric_limits<short>::lowest());
+                case DT_U16: return put(mn ? std::numeric_limits<unsigned short>::max() : (unsigned short)0);
+                case DT_I8: return put(mn ? std::numeric_limits<signed char>::max() : std::numeric_limits<signed char>::lowest());
+                case DT_U8: return put(mn ? std::numeric_limits<unsigned char>::max() : (unsigned char)0);
                 default: return false;
             }
         default: (void)mx; return false;

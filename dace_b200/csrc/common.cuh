@@ -399,6 +399,7 @@ struct Tuning {
     bool no_two_pass, no_axis_sort, no_peel, no_wide_cols, no_few_rows, no_narrow_cols, no_partition, no_tiled, no_tiny_rows,
          no_outer_first;
     int wide_wc;            // DACE_B200_WIDE_WC (0 = default)
+    int rows_lane_bytes;    // DACE_B200_ROWS_LANE_BYTES (0 = default)
     int part_chunk_log2;    // DACE_B200_PART_CHUNK_LOG2 (0 = default)
     int part_divert;        // DACE_B200_PART_DIVERT (-1 = default)
     int part_hint;          // DACE_B200_PART_HINT (-1 = default)

@@ -507,28 +507,56 @@ static cudaError_t launch_cols_few_rows(const ColsArgs& a, const Launch& l) {
 constexpr int kNarrowMaxK = 1024;
 constexpr int kNarrowUnroll = 8;
 
-template <class L, class A, class Op>
+// N = adjacent columns per thread: 1, or as many 1- / 2-byte elements as fill a 32-bit word (a warp of scalar
+// 2-byte loads moves 64 bytes per instruction: [4M, 128] bf16 ran at 0.60 of the peak, uint8 at 0.35).  Then the
+// stream is one of K / N "word columns" and everything above holds for those.
+template <class L, class A, class Op, int N>
 __global__ void __launch_bounds__(1024)
 cols_narrow_kernel(const L* __restrict__ in, size_t total, unsigned K, A* __restrict__ partials) {
-    __shared__ A sm[1024];
+    __shared__ A sm[N][1024];
     const unsigned B = blockDim.x;
+    const unsigned KV = K / N;
     const size_t stride = size_t(gridDim.x) * B;
-    A acc = Op::neutral();
+    const size_t totalv = total / N;                  // K % N == 0, so total % N == 0
+    A acc[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) acc[j] = Op::neutral();
+    auto load = [&](size_t iv, A (&x)[N]) {
+        if constexpr (N == 1) {
+            x[0] = to_acc<A, L>(ldg_scalar(in + iv));
+        } else {
+            Words<4> w;
+            w.w[0] = __ldg(reinterpret_cast<const unsigned*>(in) + iv);
+#pragma unroll
+            for (int j = 0; j < N; ++j) x[j] = vec_elem<L, A, 4>(w, j);
+        }
+    };
     size_t i = size_t(blockIdx.x) * B + threadIdx.x;
-    for (; i + size_t(kNarrowUnroll - 1) * stride < total; i += size_t(kNarrowUnroll) * stride) {
-        A v[kNarrowUnroll];
+    for (; i + size_t(kNarrowUnroll - 1) * stride < totalv; i += size_t(kNarrowUnroll) * stride) {
+        A v[kNarrowUnroll][N];
 #pragma unroll
-        for (int u = 0; u < kNarrowUnroll; ++u) v[u] = to_acc<A, L>(ldg_scalar(in + i + size_t(u) * stride));
+        for (int u = 0; u < kNarrowUnroll; ++u) load(i + size_t(u) * stride, v[u]);
 #pragma unroll
-        for (int u = 0; u < kNarrowUnroll; ++u) acc = Op::apply(acc, v[u]);
+        for (int u = 0; u < kNarrowUnroll; ++u)
+#pragma unroll
+            for (int j = 0; j < N; ++j) acc[j] = Op::apply(acc[j], v[u][j]);
     }
-    for (; i < total; i += stride) acc = Op::apply(acc, to_acc<A, L>(ldg_scalar(in + i)));
-    sm[threadIdx.x] = acc;
+    for (; i < totalv; i += stride) {
+        A v[N];
+        load(i, v);
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] = Op::apply(acc[j], v[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < N; ++j) sm[j][threadIdx.x] = acc[j];
     __syncthreads();
-    if (threadIdx.x < K) {
-        A r = sm[threadIdx.x];
-        for (unsigned t = threadIdx.x + K; t < B; t += K) r = Op::apply(r, sm[t]);
-        partials[size_t(blockIdx.x) * K + threadIdx.x] = r;
+    if (threadIdx.x < KV) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            A r = sm[j][threadIdx.x];
+            for (unsigned t = threadIdx.x + KV; t < B; t += KV) r = Op::apply(r, sm[j][t]);
+            partials[size_t(blockIdx.x) * K + threadIdx.x * N + j] = r;
+        }
     }
 }
 
@@ -552,15 +580,23 @@ static cudaError_t launch_cols_narrow(const ColsArgs& a, const Launch& l) {
         a.reduced * a.inner < (size_t(1) << 22) || l.ws.partials == nullptr || tuning().no_narrow_cols)
         return cudaErrorNotSupported;
     const unsigned K = unsigned(a.inner);
-    const unsigned tmax = K <= 256 ? 256 : 1024;          // CTA size: the largest multiple of K that fits
-    const unsigned B = (tmax / K) * K;
+    // 1- and 2-byte elements: a 32-bit word of adjacent columns per thread when width and base allow
+    constexpr int NW = sizeof(L) < 4 ? 4 / int(sizeof(L)) : 1;
+    const bool words = NW > 1 && K % NW == 0 && K / NW >= 2 && (reinterpret_cast<size_t>(a.in) & 3) == 0;
+    const unsigned KV = words ? K / NW : K;
+    const unsigned tmax = KV <= 256 ? 256 : 1024;         // CTA size: the largest multiple of KV that fits
+    const unsigned B = (tmax / KV) * KV;
     const size_t total = a.reduced * a.inner;
     size_t grid = size_t(sm_count()) * (2048 / tmax);
-    const size_t need = ceil_div(total, size_t(B) * kNarrowUnroll);
+    const size_t need = ceil_div(total / (words ? NW : 1), size_t(B) * kNarrowUnroll);
     if (grid > need) grid = need;
+    if (grid == 0) grid = 1;
     if (grid * K * sizeof(A) > kPartialBytes) return cudaErrorNotSupported;
     A* partials = reinterpret_cast<A*>(l.ws.partials);
-    cols_narrow_kernel<L, A, Op><<<(unsigned)grid, B, 0, l.stream>>>((const L*)a.in, total, K, partials);
+    if (words)
+        cols_narrow_kernel<L, A, Op, NW><<<(unsigned)grid, B, 0, l.stream>>>((const L*)a.in, total, K, partials);
+    else
+        cols_narrow_kernel<L, A, Op, 1><<<(unsigned)grid, B, 0, l.stream>>>((const L*)a.in, total, K, partials);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     cols_narrow_finish_kernel<A, S, Op><<<(K + 7) / 8, 256, 0, l.stream>>>(partials, (unsigned)grid, K, (S*)a.out,

@@ -412,7 +412,7 @@ def test_cols_wide_rows_bf16_and_2d(cuda):
 @pytest.mark.parametrize('shape', [[6, 50, 64], [33, 7, 1000], [3, 300, 32], [2, 5, 40000],
                                    [300, 7, 33], [2049, 64, 8], [70, 5, 70], [5000, 3, 2]])   # R1 >= R2: outer axis first
 def test_outer_inner_axes_two_pass(dtype, op, shape, cuda):
-    """Per-channel statistics layout (axes (0, 2) of [N, C, H*W]); int8 has no two-pass plan and must
+    """Per-channel statistics layout (axes (0, 2) of [N, C, H*W]); every type through the two-pass plans and must
     still be right through the generic kernel."""
     rng = np.random.default_rng(3)
     a = _data(rng, shape, dtype, op)
@@ -666,7 +666,42 @@ def test_narrow_dense_column_folds(K, dtype, cuda):
     assert torch.equal(o1, o2)
 
 
-@pytest.mark.parametrize('n', [2, 3, 5, 8, 16, 17, 33, 100, 128])
+@pytest.mark.parametrize('K', [2, 4, 6, 8, 100, 128, 250, 256, 1000, 1024])
+@pytest.mark.parametrize('dtype', [np.uint8, np.int8, np.int16])
+def test_narrow_dense_column_folds_small_integer_types(K, dtype, cuda):
+    """1- and 2-byte elements: a thread takes a 32-bit word of adjacent columns when K is a multiple of the word
+    (4 / 2 elements) and the base is word-aligned, else one element - bit-exact either way, also for a view that
+    starts one element into the allocation."""
+    rng = np.random.default_rng(K + 1)
+    R = (1 << 22) // K + 37
+    a = _data(rng, [R, K], dtype, 'sum')
+    for op in ('sum', 'max', 'min'):
+        got, ref = _run(a, (0, ), op, cuda)
+        np.testing.assert_array_equal(got, ref)
+    buf = torch.from_numpy(np.concatenate([a.reshape(-1)[:1], a.reshape(-1)])).to(cuda)
+    v = buf[1:].view(R, K)                                         # same data, base off by one element
+    got = db.reduce('lambda a, b: max(a, b)', v, axis=(0, ), identity=int(np.iinfo(dtype).min))
+    np.testing.assert_array_equal(got.cpu().numpy(), a.max(0))
+
+
+@pytest.mark.parametrize('K', [2, 6, 128, 250, 1024])
+@pytest.mark.parametrize('tdt', ['bfloat16', 'float16'])
+def test_narrow_dense_column_folds_half_types(K, tdt, cuda):
+    dt = getattr(torch, tdt)
+    eps = 2.0 ** -8 if tdt == 'bfloat16' else 2.0 ** -11
+    R = (1 << 22) // K + 37
+    x = (torch.rand(R, K, device=cuda) - 0.3).to(dt)
+    out = torch.zeros(K, dtype=torch.float32, device=cuda)
+    db.reduce('lambda a, b: a + b', x, out, axis=(0, ), identity=0)             # fp32 output: no final rounding
+    ref, scale = x.double().sum(0), x.double().abs().sum(0)
+    assert bool(((out.double() - ref).abs() <= 1e-5 * scale).all())
+    if float(ref.abs().max()) < 3e4:                                            # (fp16 holds nothing past 65504)
+        got = db.reduce('lambda a, b: a + b', x, axis=(0, ), identity=0)        # 16-bit output: one rounding
+        assert bool(((got.double() - ref).abs() <= eps * ref.abs() + 1e-5 * scale).all())
+    assert torch.equal(db.reduce('lambda a, b: max(a, b)', x, axis=(0, ), identity=-60000.0), x.amax(0))
+
+
+@pytest.mark.parametrize('n', [2, 3, 5, 8, 16, 17, 33, 100, 128, 129, 250, 333, 511, 512, 513])   # > 128: the lanes-per-row kernel, rows not whole 32-byte vectors
 @pytest.mark.parametrize('dtype', [np.float32, np.int64, np.uint8, np.float64])
 def test_tiny_dense_rows(n, dtype, cuda):
     """[R, n <= 128] dense, axis 1: rows staged through shared memory as one flat tile per CTA."""
