@@ -104,7 +104,11 @@ template <class V, class W>
 __global__ void __launch_bounds__(kPartThreads, 1)
 scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restrict__ bins, unsigned nbins, V cval, W scale,
                          unsigned* buf, unsigned* gcur, size_t chunk, unsigned cap, int B, int S, int aligned,
-                         const int* __restrict__ gate, int divert, int hint) {
+                         const int* __restrict__ gate, int divert, int hint, int bits) {
+    // `bits`: log2 of the bins per bucket - kBucketBits for large bin arrays, fewer for mid-sized ones so that there
+    // are still ~32 buckets to rank into (two buckets meant 16-way conflicts on the rank counters: 2^16 bins ran at
+    // 206 Gkeys/s where 2^20 bins reach 306).
+    const unsigned bucket_bins = 1u << bits, bucket_mask = bucket_bins - 1;
     if (*gate != 0) return;   // clustered / skewed keys: one of the kernels behind this one does the work (grid-uniform)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     V* hist = reinterpret_cast<V*>(smem_raw);                                  // [kBucketBins]
@@ -124,7 +128,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restr
     unsigned* gbase = s_gbase[g];
     const unsigned uB = unsigned(B);
 
-    for (unsigned i = tid; i < kBucketBins; i += kPartThreads) hist[i] = V(0);
+    for (unsigned i = tid; i < bucket_bins; i += kPartThreads) hist[i] = V(0);
     if (gtid < kCntSlots) cnt[gtid] = 0;
     __syncthreads();
     const unsigned long long pol_first = policy_evict_first(), pol_last = policy_evict_last();
@@ -180,7 +184,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restr
             // rank inside (tile, bucket); keys >= nbins land in bucket index >= B and are dropped
 #pragma unroll
             for (int j = 0; j < kKeysPerThread; ++j)
-                rank[j] = atomicAdd(&cnt[min(k[j] >> kBucketBits, uB)], 1u);
+                rank[j] = atomicAdd(&cnt[min(k[j]  >> bits, uB)], 1u);
             group_sync(g);
             unsigned c0 = 0, c1 = 0, o0 = 0, o1 = 0, gb0 = 0, gb1 = 0;
             if (gtid < 32) {
@@ -209,7 +213,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restr
             group_sync(g);
 #pragma unroll
             for (int j = 0; j < kKeysPerThread; ++j)
-                stage[off[min(k[j] >> kBucketBits, uB)] + rank[j]] = k[j];
+                stage[off[min(k[j]  >> bits, uB)] + rank[j]] = k[j];
             if (gtid < 32) {
                 gbase[lane] = gb0;
                 gbase[lane + 32] = gb1;
@@ -226,7 +230,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restr
 #pragma unroll
                 for (int j = 0; j < kKeysPerThread; ++j) key[j] = stage[j * kGroupThreads + gtid];
 #pragma unroll
-                for (int j = 0; j < kKeysPerThread; ++j) d[j] = delta[key[j] >> kBucketBits];
+                for (int j = 0; j < kKeysPerThread; ++j) d[j] = delta[key[j]  >> bits];
 #pragma unroll
                 for (int j = 0; j < kKeysPerThread; ++j) {
                     unsigned* dstp = bufc + (j * kGroupThreads + gtid + d[j]);
@@ -238,7 +242,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restr
                     const unsigned slot = j * kGroupThreads + gtid;
                     if (slot < total) {
                         const unsigned key = stage[slot];
-                        bufc[slot + delta[key >> kBucketBits]] = key;
+                        bufc[slot + delta[key  >> bits]] = key;
                     }
                 }
             } else {
@@ -249,7 +253,7 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restr
                     unsigned key = 0, dst = 0, b = 0;
                     if (valid) {
                         key = stage[slot];
-                        b = key >> kBucketBits;
+                        b = key  >> bits;
                         dst = gbase[b] + (slot - off[b]);
                     }
                     const bool fits = valid && dst < cap;
@@ -282,30 +286,30 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restr
                 for (int u = 0; u < kPhaseBUnroll; ++u) w[u] = __ldcg(v4 + v + u * kPartThreads);
 #pragma unroll
                 for (int u = 0; u < kPhaseBUnroll; ++u) {
-                    smem_add_v(hist + (w[u].x & (kBucketBins - 1)), cval);
-                    smem_add_v(hist + (w[u].y & (kBucketBins - 1)), cval);
-                    smem_add_v(hist + (w[u].z & (kBucketBins - 1)), cval);
-                    smem_add_v(hist + (w[u].w & (kBucketBins - 1)), cval);
+                    smem_add_v(hist + (w[u].x & bucket_mask), cval);
+                    smem_add_v(hist + (w[u].y & bucket_mask), cval);
+                    smem_add_v(hist + (w[u].z & bucket_mask), cval);
+                    smem_add_v(hist + (w[u].w & bucket_mask), cval);
                 }
             }
             for (; v < nvec; v += kPartThreads) {
                 uint4 w = __ldcg(v4 + v);
-                smem_add_v(hist + (w.x & (kBucketBins - 1)), cval);
-                smem_add_v(hist + (w.y & (kBucketBins - 1)), cval);
-                smem_add_v(hist + (w.z & (kBucketBins - 1)), cval);
-                smem_add_v(hist + (w.w & (kBucketBins - 1)), cval);
+                smem_add_v(hist + (w.x & bucket_mask), cval);
+                smem_add_v(hist + (w.y & bucket_mask), cval);
+                smem_add_v(hist + (w.z & bucket_mask), cval);
+                smem_add_v(hist + (w.w & bucket_mask), cval);
             }
             for (unsigned i = lo + nvec * 4 + tid; i < hi; i += kPartThreads)
-                smem_add_v(hist + (__ldcg(src + i) & (kBucketBins - 1)), cval);
+                smem_add_v(hist + (__ldcg(src + i) & bucket_mask), cval);
         }
         // no second grid-wide barrier: the next chunk writes the other buffer and its own counters
     }
     __syncthreads();
     if (blockIdx.x < unsigned(B * S)) {
         const unsigned b = blockIdx.x / S;
-        for (unsigned i = tid; i < kBucketBins; i += kPartThreads) {
+        for (unsigned i = tid; i < bucket_bins; i += kPartThreads) {
             const V h = hist[i];
-            const unsigned bin = b * kBucketBins + i;
+            const unsigned bin = b * bucket_bins + i;
             if (h != V(0) && bin < nbins) bins_add(bins + bin, W(h) * scale);
         }
     }
@@ -369,6 +373,7 @@ struct PartPlan {
     unsigned cap;
     size_t smem;
     size_t gcur_off, buf_off, total;
+    int bits;
 };
 
 static bool part_plan(int dtidx, int dtval, bool has_values, size_t n, size_t nbins, PartPlan& p) {
@@ -379,7 +384,10 @@ static bool part_plan(int dtidx, int dtval, bool has_values, size_t n, size_t nb
     if (n < (size_t(1) << 22)) return false;
     if (nbins * 4 <= (size_t(96) << 10) || nbins > size_t(kMaxBuckets) * kBucketBins) return false;
     const int sms = sm_count();
-    p.B = int((nbins + kBucketBins - 1) / kBucketBins);
+    // bins per bucket: 2^15 (what fits shared memory) for large arrays, otherwise whatever leaves 17 ... 32 buckets
+    p.bits = kBucketBits;
+    while (p.bits > 10 && ((nbins + (size_t(1) << (p.bits - 1)) - 1) >> (p.bits - 1)) <= 32) --p.bits;
+    p.B = int((nbins + (size_t(1) << p.bits) - 1) >> p.bits);
     if (p.B > kMaxBuckets || p.B > sms) return false;
     p.S = sms / p.B;
     // every group of every CTA gets the same number of tiles per chunk (the grid barrier waits for the slowest)
@@ -474,7 +482,8 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, W scale, c
     int aligned = (reinterpret_cast<size_t>(a.idx) & 15) == 0;
     int divert = tuning().part_divert >= 0 ? tuning().part_divert : kDivertDefault;   // tuning knob (0 = off)
     int hint = tuning().part_hint >= 0 ? tuning().part_hint : kHintDefault;
-    void* args[] = {&keys, &n, &bins, &nbins, &cval, &scale, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert, &hint};
+    int bits_arg = p.bits;
+    void* args[] = {&keys, &n, &bins, &nbins, &cval, &scale, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert, &hint, &bits_arg};
     e = cudaLaunchCooperativeKernel((void*)scatter_partition_kernel<V, W>, dim3(sm_count()), dim3(kPartThreads), args,
                                     p.smem, l.stream);
     if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }

@@ -172,66 +172,113 @@ scatter_global_kernel(const I* __restrict__ idx, const V* __restrict__ values, V
     }
 }
 
-// ---- shared-memory privatised path (Sum only) ------------------------------
-template <class V, bool AGG, bool HAS_VALUES>
-__device__ __forceinline__ void smem_add(V* hist, long long k, size_t nbins, V val) {
-    const bool ok = k >= 0 && (size_t)k < nbins;
-    if constexpr (AGG && std::is_integral<V>::value) {
-        // Warp-aggregated: lanes with the same key elect a leader that adds the group's total.
-        const unsigned active = __ballot_sync(kFullMask, ok);
-        if (ok) {
-            const unsigned peers = __match_any_sync(active, k);
-            const int leader = __ffs(peers) - 1;
-            // Constant increments aggregate to val * popc; per-lane values need a segmented sum.
-            V total = val;
-            if constexpr (!HAS_VALUES) {
-                total = val * V(__popc(peers));
-            } else if (__popc(peers) > 1) {
-                total = V(0);
-                unsigned rest = peers;
-                while (rest) {
-                    int src = __ffs(rest) - 1;
-                    total += __shfl_sync(peers, val, src);
-                    rest &= rest - 1;
-                }
-            }
-            if ((int)(threadIdx.x & 31) == leader) atomic_reduce<RT_Sum, V>(hist + k, total);
-        }
-    } else {
-        if (ok) atomic_reduce<RT_Sum, V>(hist + k, val);
-    }
+// ---- shared-memory privatised path (Sum, Min, Max; bins that fit 96 KiB) ----------------------------------
+// Every warp of a CTA owns one of up to 16 private copies of the bins (seeded with the operator's neutral
+// element), so two lanes only meet on an address when they hold the same key.  Keys come in as 16-byte vectors,
+// U of them in flight per thread (per-element values: U scalar key / value pairs); the first version of this
+// kernel had ONE 4-byte load in flight per thread and ran 2^26 keys into 256 bins at 70-240 Gkeys/s, and Min / Max
+// did not have it at all (global atomics on 256 addresses: 4.4 Gkeys/s).  Constant increments merge equal keys
+// inside the warp (match.any) only while a periodic sample says that the keys are skewed, as the global kernel does.
+// At the end the copies are folded in a fixed order and each bin that received something goes to the global
+// bins with one atomic.
+template <int RED, class V>
+__device__ __forceinline__ V scatter_neutral() {
+    if constexpr (RED == RT_Sum) return V(0);
+    else if constexpr (std::is_same<V, float>::value) return __uint_as_float(RED == RT_Min ? 0x7f800000u : 0xff800000u);
+    else if constexpr (std::is_same<V, double>::value)
+        return __longlong_as_double(RED == RT_Min ? 0x7ff0000000000000ll : (long long)0xfff0000000000000ull);
+    else return RED == RT_Min ? std::numeric_limits<V>::max() : std::numeric_limits<V>::lowest();
+}
+template <int RED, class V>
+__device__ __forceinline__ V scatter_apply(V a, V b) {
+    if constexpr (RED == RT_Sum) return a + b;
+    else if constexpr (RED == RT_Min) return b < a ? b : a;
+    else return b > a ? b : a;
 }
 
-template <class I, class V, bool HAS_VALUES, bool AGG>
+template <int RED, class I, class V, bool HAS_VALUES, int U>
 __global__ void __launch_bounds__(512)
 scatter_smem_kernel(const I* __restrict__ idx, const V* __restrict__ values, V cval, size_t n,
                     V* __restrict__ bins, size_t nbins, int copies) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     V* hist = reinterpret_cast<V*>(smem_raw);
     const size_t total = nbins * copies;
-    for (size_t i = threadIdx.x; i < total; i += blockDim.x) hist[i] = V(0);
+    const V neutral = scatter_neutral<RED, V>();
+    for (size_t i = threadIdx.x; i < total; i += blockDim.x) hist[i] = neutral;
     __syncthreads();
     V* mine = hist + size_t((threadIdx.x >> 5) % copies) * nbins;
-
     const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     const size_t nthr = size_t(gridDim.x) * blockDim.x;
-    // Round the trip count up so that whole warps stay converged for match/shfl.
-    const size_t iters = (n + nthr - 1) / nthr;
-    for (size_t it = 0; it < iters; ++it) {
-        const size_t i = it * nthr + tid;
-        long long k = -1;
-        V v = cval;
-        if (i < n) {
-            k = (long long)ldg_scalar(idx + i);
-            if constexpr (HAS_VALUES) v = ldg_scalar(values + i);
+    if constexpr (HAS_VALUES) {
+        for (size_t i0 = tid; i0 < n; i0 += size_t(U) * nthr) {
+            long long k[U];
+            V v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const size_t i = i0 + size_t(u) * nthr;
+                k[u] = -1;
+                if (i < n) { k[u] = (long long)ldg_scalar(idx + i); v[u] = ldg_scalar(values + i); }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (k[u] >= 0 && (size_t)k[u] < nbins) atomic_reduce<RED, V>(mine + k[u], v[u]);
         }
-        smem_add<V, AGG, HAS_VALUES>(mine, k, nbins, v);
+    } else {
+        constexpr int N = 16 / int(sizeof(I));
+        const size_t addr = reinterpret_cast<size_t>(idx);
+        size_t h = ((16 - (addr & 15)) & 15) / sizeof(I);
+        if (h > n) h = n;
+        const char* pv = reinterpret_cast<const char*>(idx + h);
+        const size_t nvec = (n - h) / N;
+        const unsigned lane = threadIdx.x & 31;
+        bool merge = false;
+        unsigned it = 0;
+        for (size_t vb = tid - lane; vb < nvec; vb += size_t(U) * nthr, ++it) {     // warp-uniform trip count
+            Words<16> w[U];
+            bool have[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const size_t vi = vb + lane + size_t(u) * nthr;
+                have[u] = vi < nvec;
+                if (have[u]) w[u] = ldg_stream16(pv + vi * 16);
+            }
+            if ((it & 15u) == 0) {
+                const long long k0 = have[0] ? idx_at<I>(w[0], 0) : -1 - (long long)lane;
+                const unsigned same = __match_any_sync(kFullMask, k0);
+                merge = __popc(__ballot_sync(kFullMask, __popc(same) > 1)) >= 16;     // half of the lanes share a key
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    const long long k = have[u] ? idx_at<I>(w[u], j) : -1;
+                    const bool ok = k >= 0 && (size_t)k < nbins;
+                    if (merge) {
+                        const unsigned act = __ballot_sync(kFullMask, ok);
+                        if (ok) {
+                            const unsigned peers = __match_any_sync(act, k);
+                            if (lane == unsigned(__ffs(peers) - 1))
+                                atomic_reduce<RED, V>(mine + k, RED == RT_Sum ? V(cval * V(__popc(peers))) : cval);
+                        }
+                    } else if (ok) {
+                        atomic_reduce<RED, V>(mine + k, cval);
+                    }
+                }
+        }
+        for (size_t i = tid; i < h; i += nthr) {
+            const long long k = (long long)ldg_scalar(idx + i);
+            if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(mine + k, cval);
+        }
+        for (size_t i = h + nvec * N + tid; i < n; i += nthr) {
+            const long long k = (long long)ldg_scalar(idx + i);
+            if (k >= 0 && (size_t)k < nbins) atomic_reduce<RED, V>(mine + k, cval);
+        }
     }
     __syncthreads();
     for (size_t b = threadIdx.x; b < nbins; b += blockDim.x) {
         V s = hist[b];
-        for (int c = 1; c < copies; ++c) s += hist[size_t(c) * nbins + b];
-        if (s != V(0)) atomic_reduce<RT_Sum, V>(bins + b, s);
+        for (int c = 1; c < copies; ++c) s = scatter_apply<RED, V>(s, hist[size_t(c) * nbins + b]);
+        if (s != neutral) atomic_reduce<RED, V>(bins + b, s);
     }
 }
 
@@ -372,26 +419,33 @@ static cudaError_t launch_scatter_t(const ScatterArgs& a, const Launch& l) {
     if (a.const_value) memcpy(&cval, a.const_value, sizeof(V));
     if (a.n == 0) return cudaSuccess;
     const size_t hist_bytes = a.nbins * sizeof(V);
-    if (RED == RT_Sum && hist_bytes <= (size_t(96) << 10) && a.n >= (size_t(1) << 14)) {
-        int copies = int((size_t(96) << 10) / hist_bytes);
-        if (copies > 16) copies = 16;
-        if (copies < 1) copies = 1;
-        const size_t smem = hist_bytes * copies;
-        const bool agg = a.nbins <= 1024 && std::is_integral<V>::value;
-        size_t grid = size_t(sms) * 2;
-        const size_t need = (a.n + 511) / 512;
-        if (grid > need) grid = need;
-        cudaError_t e;
-#define DB200_SMEM_LAUNCH(HV, AG)                                                                          \
-        e = cudaFuncSetAttribute(scatter_smem_kernel<I, V, HV, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                 (int)(size_t(96) << 10));                                                 \
-        if (e != cudaSuccess) return e;                                                                    \
-        scatter_smem_kernel<I, V, HV, AG><<<(unsigned)grid, 512, smem, l.stream>>>(                        \
-            (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins, copies);
-        if (a.values) { if (agg) { DB200_SMEM_LAUNCH(true, true) } else { DB200_SMEM_LAUNCH(true, false) } }
-        else          { if (agg) { DB200_SMEM_LAUNCH(false, true) } else { DB200_SMEM_LAUNCH(false, false) } }
+    if constexpr (RED == RT_Sum || RED == RT_Min || RED == RT_Max) {
+        if (hist_bytes <= (size_t(96) << 10) && a.n >= (size_t(1) << 14) && a.gate == nullptr) {
+            int copies = int((size_t(96) << 10) / hist_bytes);
+            if (copies > 16) copies = 16;
+            if (copies < 1) copies = 1;
+            const size_t smem = hist_bytes * copies;
+            const size_t need = (a.n + 511) / 512;
+            cudaError_t e;
+#define DB200_SMEM_LAUNCH(HV)                                                                                  \
+            {                                                                                                  \
+                static PerDeviceOnce attr_set;                                                                 \
+                bool* done = attr_set.slot();                                                                  \
+                if (!*done) {                                                                                  \
+                    e = cudaFuncSetAttribute(scatter_smem_kernel<RED, I, V, HV, 4>,                            \
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(size_t(96) << 10)); \
+                    if (e != cudaSuccess) return e;                                                            \
+                    *done = true;                                                                              \
+                }                                                                                              \
+                size_t grid = size_t(sms) * 2;                                                                 \
+                if (grid > need) grid = need;                                                                  \
+                scatter_smem_kernel<RED, I, V, HV, 4><<<(unsigned)grid, 512, smem, l.stream>>>(                \
+                    (const I*)a.idx, (const V*)a.values, cval, a.n, (V*)a.bins, a.nbins, copies);              \
+            }
+            if (a.values) DB200_SMEM_LAUNCH(true) else DB200_SMEM_LAUNCH(false)
 #undef DB200_SMEM_LAUNCH
-        return cudaGetLastError();
+            return cudaGetLastError();
+        }
     }
     // a persistent grid of exactly one wave (what fits depends on the instantiation's registers)
     size_t grid = size_t(sms) * (a.values ? resident_ctas<scatter_global_kernel<RED, I, V, true, 4>>(512)

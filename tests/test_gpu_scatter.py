@@ -144,7 +144,7 @@ def test_unaligned_index_pointer(cuda):
         np.testing.assert_array_equal(bins.cpu().numpy(), np.bincount(keys[off:], minlength=1 << 17))
 
 
-@pytest.mark.parametrize('nbins', [24577, 100000, 1 << 20, (1 << 21) - 5])
+@pytest.mark.parametrize('nbins', [24577, 33000, 65536, 100000, 300001, 1 << 19, (1 << 19) + 1, 1 << 20, (1 << 21) - 5])   # 17 ... 64 buckets of 2^10 ... 2^15 bins
 @pytest.mark.parametrize('dist', ['uniform', 'zipf', 'halfhot'])
 def test_partitioned_histogram_large_bins(nbins, dist, cuda):
     """Radix-partition + shared-memory histogram path (wcr_partition.cu): several 2^23-key chunks,
@@ -298,3 +298,41 @@ def test_weighted_scatter_large_bins_skew_goes_through_the_hot_key_cache(dist, c
     lib = __import__('dace_b200')._lib.load()
     assert lib.dace_b200_wcr_scatter_workspace_bytes(3, 2, 0, 1, n, nbins) == 256      # values: the sampler's flag only
     assert lib.dace_b200_wcr_scatter_workspace_bytes(3, 2, 0, 1, 1000, nbins) == 0
+
+
+@pytest.mark.parametrize('nbins', [7, 256, 5000, 24576])
+@pytest.mark.parametrize('op,npop', [('lambda a, b: max(a, b)', np.maximum), ('lambda a, b: min(a, b)', np.minimum)])
+def test_privatised_min_max_small_bins(nbins, op, npop, cuda):
+    """Min / Max into bins that fit shared memory: per-warp private copies seeded with the neutral element, flushed
+    with one atomic per touched bin - exact for every type, negative floats included, existing contents kept,
+    constant value and per-element values, skewed keys (the warp merge)."""
+    rng = np.random.default_rng(nbins)
+    n = (1 << 20) + 77
+    keys = rng.integers(-2, nbins + 2, n).astype(np.int32)
+    keys[: n // 3] = nbins // 2                                     # a hot bin
+    ok = (keys >= 0) & (keys < nbins)
+    tk = torch.from_numpy(keys).to(cuda)
+    for dt in (np.int32, np.int64, np.float32, np.float64, np.uint32):
+        if np.issubdtype(dt, np.floating):
+            vals = rng.uniform(-100, 100, n).astype(dt)
+            start = rng.uniform(-50, 50, nbins).astype(dt)
+        elif dt == np.uint32:
+            vals = rng.integers(0, 1 << 31, n).astype(dt)
+            start = rng.integers(1 << 29, 1 << 30, nbins).astype(dt)
+        else:
+            vals = rng.integers(-1 << 30, 1 << 30, n).astype(dt)
+            start = rng.integers(-1 << 28, 1 << 28, nbins).astype(dt)
+        bins = torch.from_numpy(start.copy()).to(cuda)
+        db.wcr_scatter(op, bins, tk, torch.from_numpy(vals).to(cuda))
+        want = start.copy()
+        npop.at(want, keys[ok], vals[ok])
+        np.testing.assert_array_equal(bins.cpu().numpy(), want)
+        # constant value: every touched bin meets the constant once
+        bins = torch.from_numpy(start.copy()).to(cuda)
+        const = vals[:1].copy()
+        db.wcr_scatter(op, bins, tk, const[0].item())
+        want = start.copy()
+        touched = np.zeros(nbins, bool)
+        touched[keys[ok]] = True
+        want[touched] = npop(want[touched], const[0])
+        np.testing.assert_array_equal(bins.cpu().numpy(), want)
