@@ -333,6 +333,68 @@ arg_cols_kernel(const L* __restrict__ in, size_t reduced, size_t inner, long lon
     if (threadIdx.x == 0) counters[blockIdx.x] = 0;
 }
 
+// Few rows, many columns ([R <= 64, K], argmax over the R axis): a thread owns NV adjacent columns and walks all
+// rows itself, CTAs walk column chunks - no shared memory, no cross-warp combine, nothing to split.  The kernel
+// above would launch one CTA per 32 * NV columns with one row per warp (measured 1.1 TB/s at [8, 33M] f32).
+template <class L, class A, bool IsMax, int NV, int U>
+__global__ void __launch_bounds__(kArgThreads)
+arg_cols_few_rows_kernel(const L* __restrict__ in, size_t outer, size_t reduced, size_t inner, long long so, long long sr,
+                         ArgOut out, A init) {
+    constexpr int VB = NV * int(sizeof(L));
+    const size_t nvec = (inner + NV - 1) / NV;           // NV > 1 only when inner % NV == 0
+    const size_t per_o = (nvec + kArgThreads - 1) / kArgThreads;      // CTA-sized chunks per outer slice
+    for (size_t chunk = blockIdx.x; chunk < per_o * outer; chunk += gridDim.x) {
+        const size_t o = chunk / per_o, cv = (chunk % per_o) * kArgThreads + threadIdx.x;
+        if (cv >= nvec) continue;
+        const size_t col0 = cv * NV;
+        const L* p = in + (long long)o * so + (long long)col0;
+        A v[NV];
+        long long ix[NV];
+#pragma unroll
+        for (int j = 0; j < NV; ++j) { v[j] = ArgOp<A, IsMax>::neutral(); ix[j] = kNoIndex; }
+        size_t r = 0;
+        for (; r + U <= reduced; r += U) {
+            if constexpr (NV > 1) {
+                Words<VB> w[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) w[u] = ldg_stream<VB>(p + (long long)(r + u) * sr);
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int j = 0; j < NV; ++j) {
+                        const A x = vec_elem<L, A, VB>(w[u], j);
+                        if (ArgOp<A, IsMax>::better(x, v[j])) { v[j] = x; ix[j] = (long long)(r + u); }
+                    }
+            } else {
+                L w[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) w[u] = ldg_scalar(p + (long long)(r + u) * sr);
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const A x = to_acc<A, L>(w[u]);
+                    if (ArgOp<A, IsMax>::better(x, v[0])) { v[0] = x; ix[0] = (long long)(r + u); }
+                }
+            }
+        }
+        for (; r < reduced; ++r) {
+            if constexpr (NV > 1) {
+                Words<VB> w = ldg_stream<VB>(p + (long long)r * sr);
+#pragma unroll
+                for (int j = 0; j < NV; ++j) {
+                    const A x = vec_elem<L, A, VB>(w, j);
+                    if (ArgOp<A, IsMax>::better(x, v[j])) { v[j] = x; ix[j] = (long long)r; }
+                }
+            } else {
+                const A x = to_acc<A, L>(ldg_scalar(p + (long long)r * sr));
+                if (ArgOp<A, IsMax>::better(x, v[0])) { v[0] = x; ix[0] = (long long)r; }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < NV; ++j)
+            if (col0 + j < inner) arg_finish<L, A, IsMax>(out, o * inner + col0 + j, v[j], ix[j], init);
+    }
+}
+
 template <class L, class A, bool IsMax>
 static cudaError_t launch_arg_t(const ArgArgs& a_in, const Launch& l) {
     ArgOut out;
@@ -357,7 +419,10 @@ static cudaError_t launch_arg_t(const ArgArgs& a_in, const Launch& l) {
     if (a.in_stride_r == 1 || a.reduced <= 1) {
         const size_t rows = nout, n = a.reduced;
         const size_t row_bytes = n * sizeof(L);
-        if (row_bytes < (size_t(32) << 10)) {
+        // a warp per row (or less) also for rows up to 256 KiB when there are enough rows for every warp of the
+        // machine: a CTA per 32 KiB row left each thread with two loads and a block-wide combine per row
+        // (f64 [32768, 4096]: 3.2 -> 6.x TB/s)
+        if (row_bytes < (size_t(32) << 10) || (row_bytes <= (size_t(256) << 10) && rows >= sms * 32)) {
             int G = 1;
             const size_t per_lane = tuning().rows_lane_bytes > 0 ? size_t(tuning().rows_lane_bytes) : 128;   // as in reduce_rows.cu
             while (G < 32 && size_t(G) * per_lane < row_bytes) G <<= 1;
@@ -399,18 +464,40 @@ static cudaError_t launch_arg_t(const ArgArgs& a_in, const Launch& l) {
     const bool vec = a.in_stride_i == 1 && a.inner % NVmax == 0 && a.in_stride_r % NVmax == 0 &&
                      a.in_stride_o % NVmax == 0 && (reinterpret_cast<size_t>(a.in) & (kVecBytes - 1)) == 0;
     const size_t nv = vec ? NVmax : 1;
+    if (a.reduced <= 64 && a.in_stride_i == 1 && a.inner >= sms * kArgThreads) {
+        const size_t chunks = ((a.inner + nv - 1) / nv + kArgThreads - 1) / kArgThreads * a.outer;
+        if (vec) {
+            size_t grid = sms * resident_ctas<arg_cols_few_rows_kernel<L, A, IsMax, NVmax, 4>>(kArgThreads);
+            if (grid > chunks) grid = chunks;
+            arg_cols_few_rows_kernel<L, A, IsMax, NVmax, 4><<<(unsigned)grid, kArgThreads, 0, l.stream>>>(
+                (const L*)a.in, a.outer, a.reduced, a.inner, a.in_stride_o, a.in_stride_r, out, init);
+        } else {
+            size_t grid = sms * resident_ctas<arg_cols_few_rows_kernel<L, A, IsMax, 1, 8>>(kArgThreads);
+            if (grid > chunks) grid = chunks;
+            arg_cols_few_rows_kernel<L, A, IsMax, 1, 8><<<(unsigned)grid, kArgThreads, 0, l.stream>>>(
+                (const L*)a.in, a.outer, a.reduced, a.inner, a.in_stride_o, a.in_stride_r, out, init);
+        }
+        return cudaGetLastError();
+    }
     const size_t ncolblocks = (a.inner + 32 * nv - 1) / (32 * nv);
     const size_t gx = ncolblocks * a.outer;
     if (gx == 0) return cudaSuccess;
     if (gx > 0x7fffffffULL) return cudaErrorNotSupported;
     size_t splits = 1;
-    if (gx < 4 * sms && gx <= kCounters) {
-        splits = (4 * sms + gx - 1) / gx;
+    const size_t slots = sms * size_t(vec ? resident_ctas<arg_cols_kernel<L, A, IsMax, NVmax, 4>>(kArgThreads)
+                                          : resident_ctas<arg_cols_kernel<L, A, IsMax, 1, 8>>(kArgThreads));
+    if (gx < slots && gx <= kCounters) {
+        // CTAs of equal work: gx * splits should fill whole waves of what fits the machine (19 splits of 32 column
+        // blocks were 608 CTAs on 592 slots - a second wave for 16 of them: [65536, 4096] f32 at 0.68 of the peak)
         size_t most = (a.reduced + 63) / 64;        // at least 64 rows per CTA
-        if (splits > most) splits = most;
-        if (splits > 65535) splits = 65535;
-        while (splits > 1 && gx * splits * 32 * nv * 16 + 8 > kPartialBytes) --splits;
-        if (splits < 1) splits = 1;
+        if (most > 65535) most = 65535;
+        while (most > 1 && gx * most * 32 * nv * 16 + 8 > kPartialBytes) --most;
+        double best_eff = 0.0;
+        for (size_t sp = 1; sp <= most && gx * sp <= 2 * slots; ++sp) {
+            const size_t total = gx * sp, waves = (total + slots - 1) / slots;
+            const double eff = double(total) / double(waves * slots);
+            if (eff > best_eff + 1e-9) { best_eff = eff; splits = sp; }
+        }
     }
     dim3 grid((unsigned)gx, (unsigned)splits);
     if (vec)

@@ -65,6 +65,10 @@ _SHAPES = [
     ((3000, 77), 0),            # columns not a vector multiple -> scalar path
     ((6, 2000, 128), 1),        # [outer, reduced, inner]
     ((4, 300, 5), 1),
+    ((8, 200000), 0),           # few rows, many columns: a thread per column vector, all rows
+    ((3, 5, 77001), 1),         # the same with an outer axis and a width that is not a vector multiple
+    ((64, 40004), 0),
+    ((5000, 5000), 1),          # rows longer than 32 KiB (8-byte types) but thousands of them: still a warp per row
     ((1, 1), 1), ((5, 1), 1), ((1, 9), 0),
 ]
 
