@@ -13,6 +13,7 @@
 //   * one CTA per row for rows of tens of KiB and up;
 //   * rows of MiB size and few of them go to the split kernel (reduce_full.cu).
 #include "common.cuh"
+#include <cooperative_groups.h>
 #include "span.cuh"
 #include "kernels.h"
 
@@ -77,13 +78,79 @@ static inline int pick_group(size_t row_bytes) {
 // consecutive lanes).  The lanes-per-row kernel above reaches 0.4-0.5 of the peak on such rows.
 constexpr int kTinyTile = 4096;            // elements per CTA tile
 constexpr int kTinyMaxN = 128;
+constexpr int kTinyPadMax = 1024;          // room for the per-row padding below
 
-template <class L, class A, class S, class Op, int WIDTH>
+// Padding (elements) between the rows of a shared-memory tile read by `width` lanes per row, so that the lanes of a
+// warp - 32 / width rows at a time - land on different banks: the row pitch in bytes must be an odd multiple of the
+// bytes one row's lanes span per step (at least a word).  n = 64 floats, 4 lanes per row: pitch 256 B put all 8 rows
+// of a warp on the same four banks (measured 2.9 TB/s where n = 100 runs at 5.1); pitch 272 B does not.
+static inline unsigned tiny_row_pad(unsigned n, unsigned width, unsigned elem_bytes, unsigned rows_per_tile) {
+    unsigned span = width * elem_bytes;
+    if (span < 4) span = 4;
+    if (span > 64) return 0;
+    unsigned pad = 0;
+    while (((n + pad) * elem_bytes) % (2 * span) != span && pad < 64) ++pad;
+    if (pad >= 64 || size_t(pad) * rows_per_tile > size_t(kTinyPadMax)) return 0;
+    return pad;
+}
+static inline unsigned tiny_magic(unsigned n) { return unsigned((0x100000000ull / n) + 1); }   // i / n for i * n < 2^32
+
+// Stage `count` contiguous elements into the CTA's tile, every load issued before the first store.  `vec16`: the
+// tile starts on a 16-byte boundary (the host picks rows_per_tile accordingly), so whole 16-byte vectors go
+// global -> shared as they are (a warp of 2-byte scalar loads moves 64 bytes per instruction: [5M, 100] bf16 ran at
+// 2.6 TB/s).  The padded layout places every element on its own, so it keeps the scalar path.
+template <class L, bool PAD>
+__device__ __forceinline__ void tiny_stage(L* __restrict__ tile, const L* __restrict__ src, unsigned count, unsigned pad,
+                                           unsigned magic, int vec16) {
+    if (!PAD && vec16) {
+        constexpr int kV = (kTinyTile * int(sizeof(L)) / 16 + kRowThreads - 1) / kRowThreads;
+        const unsigned nv = count * unsigned(sizeof(L)) / 16;
+        Words<16> w[kV];
+#pragma unroll
+        for (int u = 0; u < kV; ++u) {
+            const unsigned iv = threadIdx.x + unsigned(u) * kRowThreads;
+            if (iv < nv) w[u] = ldg_stream16(reinterpret_cast<const char*>(src) + size_t(iv) * 16);
+        }
+#pragma unroll
+        for (int u = 0; u < kV; ++u) {
+            const unsigned iv = threadIdx.x + unsigned(u) * kRowThreads;
+            if (iv < nv) reinterpret_cast<Words<16>*>(tile)[iv] = w[u];
+        }
+        for (unsigned i = nv * (16 / unsigned(sizeof(L))) + threadIdx.x; i < count; i += kRowThreads) tile[i] = ldg_scalar(src + i);
+        return;
+    }
+    constexpr int kPer = kTinyTile / kRowThreads;
+    L v[kPer];
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+        const unsigned i = threadIdx.x + unsigned(u) * kRowThreads;
+        if (i < count) v[u] = ldg_scalar(src + i);
+    }
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+        const unsigned i = threadIdx.x + unsigned(u) * kRowThreads;
+        if (i < count) tile[PAD ? i + __umulhi(i, magic) * pad : i] = v[u];        // __umulhi(i, magic) == i / n
+    }
+}
+
+// rows per tile such that every tile starts on a 16-byte boundary (0: not possible / not worth it)
+static inline unsigned tiny_rows_per_tile_vec(unsigned n, unsigned elem_bytes, const void* base) {
+    if ((reinterpret_cast<size_t>(base) & 15) != 0) return 0;
+    unsigned g = n * elem_bytes, b = 16;
+    while (b) { const unsigned t = g % b; g = b; b = t; }      // g = gcd(n * elem_bytes, 16)
+    const unsigned m = 16 / g;
+    const unsigned rpt = (unsigned(kTinyTile) / n) / m * m;
+    return rpt;
+}
+
+template <class L, class A, class S, class Op, int WIDTH, bool PAD>
 __global__ void __launch_bounds__(kRowThreads)
 rows_tiny_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, unsigned n, unsigned rows_per_tile,
-                 ptrdiff_t out_stride, Finish<A> fin) {
-    __shared__ L tile[kTinyTile];
-    constexpr int kPer = kTinyTile / kRowThreads;
+                 ptrdiff_t out_stride, Finish<A> fin, unsigned pad, unsigned magic, int vec16) {
+    // rows sit n + pad elements apart in the tile (tiny_row_pad: no two lanes of a warp on one bank)
+    // (PAD = false: the plain layout, no index arithmetic on the way in - most row lengths need no padding)
+    __shared__ __align__(16) L tile[kTinyTile + (PAD ? kTinyPadMax : 0)];
+    const unsigned np = PAD ? n + pad : n;
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int W = WIDTH < 2 ? 2 : WIDTH;
     const unsigned seg = lane / W, pos = lane % W;
@@ -95,26 +162,16 @@ rows_tiny_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, uns
         const unsigned nrows = (rows - row0 < rows_per_tile) ? unsigned(rows - row0) : rows_per_tile;
         const unsigned count = nrows * n;
         const L* src = in + row0 * n;
-        L v[kPer];
-#pragma unroll
-        for (int u = 0; u < kPer; ++u) {
-            const unsigned i = threadIdx.x + unsigned(u) * kRowThreads;
-            if (i < count) v[u] = ldg_scalar(src + i);
-        }
-#pragma unroll
-        for (int u = 0; u < kPer; ++u) {
-            const unsigned i = threadIdx.x + unsigned(u) * kRowThreads;
-            if (i < count) tile[i] = v[u];
-        }
+        tiny_stage<L, PAD>(tile, src, count, pad, magic, vec16);
         __syncthreads();
         if constexpr (WIDTH == 1) {
             // a thread per row: n shared-memory reads at stride n elements - conflict-free for odd n.  For even n
             // every thread starts at column (row mod n) and wraps around: neighbouring threads are then n + 1
             // elements apart, an odd stride again (a fold does not care where it starts).
-            const bool rotate = (n & 1u) == 0 && sizeof(L) >= 4;
+            const bool rotate = (n & 1u) == 0 && sizeof(L) >= 4 && !PAD;
             for (unsigned r = threadIdx.x; r < nrows; r += kRowThreads) {
                 A a0 = Op::neutral(), a1 = Op::neutral();
-                const L* p = tile + r * n;
+                const L* p = tile + r * np;
                 unsigned c = rotate ? r % n : 0;
                 unsigned j = 0;
                 for (; j + 1 < n; j += 2) {
@@ -134,7 +191,7 @@ rows_tiny_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, uns
                 const bool valid = r < nrows;
                 A acc = Op::neutral();
                 if (valid)
-                    for (unsigned c = pos; c < n; c += WIDTH) acc = Op::apply(acc, to_acc<A, L>(tile[r * n + c]));
+                    for (unsigned c = pos; c < n; c += WIDTH) acc = Op::apply(acc, to_acc<A, L>(tile[r * np + c]));
                 acc = warp_reduce<Op, A, WIDTH>(acc);
                 if (valid && pos == 0) write_result<Op, A, S>(out + ptrdiff_t(row0 + r) * out_stride, acc, fin);
             }
@@ -149,16 +206,31 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
     if (a.n > size_t(kTinyMaxN) || a.n < 2 || a.row_stride != a.n || a.rows * a.n < (size_t(1) << 22) ||
         tuning().no_tiny_rows)
         return cudaErrorNotSupported;
+    // rows that are whole 32-byte vectors stream through the lanes-per-row kernel at full speed since its lanes
+    // take 128 bytes each ([4M, 64] f32: 6.1 TB/s there, 4.3 through the tile)
+    if ((a.n * sizeof(L)) % 32 == 0 && (reinterpret_cast<size_t>(a.in) & 31) == 0 && !tuning().tiny_rows_always &&
+        !(sizeof(L) >= 4 && a.n * sizeof(L) == 64))          // (64-byte rows of 4-byte elements: 4.4 vs 3.3 TB/s)
+        return cudaErrorNotSupported;
     const unsigned n = unsigned(a.n);
-    const unsigned rows_per_tile = kTinyTile / n;
+    const unsigned rpt_vec = tiny_rows_per_tile_vec(n, unsigned(sizeof(L)), a.in);
+    const int vec16 = rpt_vec > 0;
+    const unsigned rows_per_tile = vec16 ? rpt_vec : kTinyTile / n;
     const size_t ntiles = (a.rows + rows_per_tile - 1) / rows_per_tile;
     Finish<A> fin = make_finish<A, S>(a.identity);
 #define DB200_TINY(W)                                                                                                   \
     do {                                                                                                                \
-        size_t grid = size_t(sm_count()) * resident_ctas<rows_tiny_kernel<L, A, S, Op, W>>(kRowThreads);                 \
-        if (grid > ntiles) grid = ntiles;                                                                               \
-        rows_tiny_kernel<L, A, S, Op, W><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(                                  \
-            (const L*)a.in, (S*)a.out, a.rows, n, rows_per_tile, a.out_stride, fin);                                    \
+        const unsigned pad = tiny_row_pad(n, W, unsigned(sizeof(L)), rows_per_tile);                                    \
+        if (pad == 0) {                                                                                                 \
+            size_t grid = size_t(sm_count()) * resident_ctas<rows_tiny_kernel<L, A, S, Op, W, false>>(kRowThreads);      \
+            if (grid > ntiles) grid = ntiles;                                                                           \
+            rows_tiny_kernel<L, A, S, Op, W, false><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(                       \
+                (const L*)a.in, (S*)a.out, a.rows, n, rows_per_tile, a.out_stride, fin, 0u, 0u, vec16);                        \
+        } else {                                                                                                        \
+            size_t grid = size_t(sm_count()) * resident_ctas<rows_tiny_kernel<L, A, S, Op, W, true>>(kRowThreads);       \
+            if (grid > ntiles) grid = ntiles;                                                                           \
+            rows_tiny_kernel<L, A, S, Op, W, true><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(                        \
+                (const L*)a.in, (S*)a.out, a.rows, n, rows_per_tile, a.out_stride, fin, pad, tiny_magic(n), 0);            \
+        }                                                                                                               \
     } while (0)
     // lanes per row: a thread per row while a tile holds at least 64 rows (n <= 64: measured faster than two lanes
     // per row, [8M, 33] 0.63 vs 0.57 of the peak); for longer rows as many lanes as keep the 256 threads busy in the
@@ -295,9 +367,167 @@ rows_max_sum_kernel(const L* __restrict__ in, float* __restrict__ out_max, float
     }
 }
 
+// Tiny dense rows (softmax over 10 ... 128 classes): the flat-tile scheme of rows_tiny_kernel - the CTA stages
+// kTinyTile elements with coalesced loads, then WIDTH lanes fold each row out of shared memory for both results
+// (the lanes-per-row kernel above ran [16M, 33] bf16 at 2.6 TB/s, [8M, 64] at 3.5).
+template <class L, int WIDTH, bool PAD>
+__global__ void __launch_bounds__(kRowThreads)
+rows_max_sum_tiny_kernel(const L* __restrict__ in, float* __restrict__ out_max, float* __restrict__ out_sum, size_t rows,
+                         unsigned n, unsigned rows_per_tile, unsigned pad, unsigned magic, int vec16) {
+    __shared__ __align__(16) L tile[kTinyTile + (PAD ? kTinyPadMax : 0)];
+    const unsigned np = PAD ? n + pad : n;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned seg = lane / WIDTH, pos = lane % WIDTH;
+    constexpr unsigned kSegs = 32 / WIDTH;
+    const size_t ntiles = (rows + rows_per_tile - 1) / rows_per_tile;
+    for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const size_t row0 = t * rows_per_tile;
+        const unsigned nrows = (rows - row0 < rows_per_tile) ? unsigned(rows - row0) : rows_per_tile;
+        const unsigned count = nrows * n;
+        const L* src = in + row0 * n;
+        tiny_stage<L, PAD>(tile, src, count, pad, magic, vec16);
+        __syncthreads();
+        for (unsigned rb = warp * kSegs; rb < nrows; rb += (kRowThreads / 32) * kSegs) {      // warp-uniform trip count
+            const unsigned r = rb + seg;
+            const bool valid = r < nrows;
+            float mx = OpMax<float>::neutral(), sm = 0.f;
+            if (valid) {
+                const L* p = tile + r * np;
+                if constexpr (WIDTH == 1) {
+                    // a lane per row: the padded pitch keeps the banks apart; without padding an even n starts at
+                    // column (row mod n) and wraps, so that neighbouring lanes are n + 1 elements apart
+                    unsigned c = (!PAD && (n & 1u) == 0) ? r % n : 0;
+                    for (unsigned j = 0; j < n; ++j) {
+                        const float x = to_acc<float, L>(p[c]);
+                        mx = fmaxf(mx, x); sm += x;
+                        c = (c + 1 == n) ? 0 : c + 1;
+                    }
+                } else {
+                    for (unsigned c = pos; c < n; c += WIDTH) {
+                        const float x = to_acc<float, L>(p[c]);
+                        mx = fmaxf(mx, x); sm += x;
+                    }
+                }
+            }
+#pragma unroll
+            for (int m = WIDTH / 2; m >= 1; m >>= 1) {
+                mx = fmaxf(mx, __shfl_xor_sync(kFullMask, mx, m));
+                sm += __shfl_xor_sync(kFullMask, sm, m);
+            }
+            if (valid && pos == 0) { out_max[row0 + r] = mx; out_sum[row0 + r] = sm; }
+        }
+        __syncthreads();
+    }
+}
+
+// Few long rows (softmax of a small batch over a large vocabulary): a cluster of C CTAs per row, each folding one
+// segment; the CTAs of a cluster meet in the first one's shared memory (DSMEM) and are folded there in rank order -
+// no workspace, deterministic.  A warp per row left [256, 1M] f32 at 1.1 TB/s.
+template <class L, int VB, int U>
+__global__ void __launch_bounds__(kRowThreads)
+rows_max_sum_cluster_kernel(const L* __restrict__ in, float* __restrict__ out_max, float* __restrict__ out_sum,
+                            size_t rows, size_t n, size_t row_stride) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const unsigned C = cluster.num_blocks(), rank = cluster.block_rank();
+    __shared__ float smx[32], ssm[32];
+    __shared__ float cmx[16], csm[16];               // written by the CTAs of the cluster, read by rank 0
+    constexpr size_t N = VecInfo<L, VB>::N;
+    size_t seg = (n + C - 1) / C;
+    seg = (seg + N - 1) / N * N;
+    const size_t lo = size_t(rank) * seg < n ? size_t(rank) * seg : n;
+    const size_t hi = lo + seg < n ? lo + seg : n;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (size_t r = blockIdx.y; r < rows; r += gridDim.y) {
+        float mx = OpMax<float>::neutral(), sm = 0.f;
+        if (hi > lo) span_max_sum<L, VB, U>(in + r * row_stride + lo, hi - lo, threadIdx.x, kRowThreads, mx, sm);
+#pragma unroll
+        for (int m = 16; m >= 1; m >>= 1) {
+            mx = fmaxf(mx, __shfl_xor_sync(kFullMask, mx, m));
+            sm += __shfl_xor_sync(kFullMask, sm, m);
+        }
+        if (lane == 0) { smx[warp] = mx; ssm[warp] = sm; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < kRowThreads / 32; ++w) { mx = fmaxf(mx, smx[w]); sm += ssm[w]; }
+            float* rmx = cluster.map_shared_rank(cmx, 0);
+            float* rsm = cluster.map_shared_rank(csm, 0);
+            rmx[rank] = mx;
+            rsm[rank] = sm;
+        }
+        cluster.sync();
+        if (rank == 0 && threadIdx.x == 0) {
+            float m0 = cmx[0], s0 = csm[0];
+            for (unsigned c = 1; c < C; ++c) { m0 = fmaxf(m0, cmx[c]); s0 += csm[c]; }
+            out_max[r] = m0;
+            out_sum[r] = s0;
+        }
+        cluster.sync();                              // rank 0 has read the slots before anyone writes the next row's
+    }
+}
+
 template <class L>
 static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& l) {
     const int sms = sm_count();
+    const bool whole_vectors = (a.n * sizeof(L)) % 32 == 0 && (reinterpret_cast<size_t>(a.in) & 31) == 0;
+    if (a.n >= 2 && a.n <= size_t(kTinyMaxN) && a.row_stride == a.n && a.rows * a.n >= (size_t(1) << 22) &&
+        !tuning().no_tiny_rows && (!whole_vectors || tuning().tiny_rows_always)) {
+        const unsigned n = unsigned(a.n);
+        const unsigned rpt_vec = tiny_rows_per_tile_vec(n, unsigned(sizeof(L)), a.in);
+        const int vec16 = rpt_vec > 0;
+        const unsigned rows_per_tile = vec16 ? rpt_vec : kTinyTile / n;
+        const size_t ntiles = (a.rows + rows_per_tile - 1) / rows_per_tile;
+        unsigned width = 1;
+        if (rows_per_tile <= 64)
+            while (width < 32 && rows_per_tile * width * 2 <= unsigned(kRowThreads)) width <<= 1;
+#define DB200_MS_TINY(W)                                                                                              \
+        do {                                                                                                          \
+            const unsigned pad = tiny_row_pad(n, W, unsigned(sizeof(L)), rows_per_tile);                              \
+            if (pad == 0) {                                                                                           \
+                size_t grid = size_t(sms) * resident_ctas<rows_max_sum_tiny_kernel<L, W, false>>(kRowThreads);        \
+                if (grid > ntiles) grid = ntiles;                                                                     \
+                rows_max_sum_tiny_kernel<L, W, false><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(                  \
+                    (const L*)a.in, a.out_max, a.out_sum, a.rows, n, rows_per_tile, 0u, 0u, vec16);                          \
+            } else {                                                                                                  \
+                size_t grid = size_t(sms) * resident_ctas<rows_max_sum_tiny_kernel<L, W, true>>(kRowThreads);         \
+                if (grid > ntiles) grid = ntiles;                                                                     \
+                rows_max_sum_tiny_kernel<L, W, true><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(                   \
+                    (const L*)a.in, a.out_max, a.out_sum, a.rows, n, rows_per_tile, pad, tiny_magic(n), 0);              \
+            }                                                                                                         \
+        } while (0)
+        switch (width) {
+            case 1: DB200_MS_TINY(1); break;
+            case 2: DB200_MS_TINY(2); break;
+            case 4: DB200_MS_TINY(4); break;
+            case 8: DB200_MS_TINY(8); break;
+            case 16: DB200_MS_TINY(16); break;
+            default: DB200_MS_TINY(32); break;
+        }
+#undef DB200_MS_TINY
+        return cudaGetLastError();
+    }
+    const size_t slots = size_t(sms) * resident_ctas<rows_max_sum_cluster_kernel<L, 32, 4>>(kRowThreads);
+    if (a.n * sizeof(L) >= (size_t(64) << 10) && a.rows < slots * (kRowThreads / 32)) {
+        // fewer rows than warps in a wave: CTAs (clusters of up to 8 along the row) instead of warps
+        unsigned C = 1;
+        while (C < 8 && a.rows * C < slots && a.n * sizeof(L) / (2 * C) >= (size_t(32) << 10)) C <<= 1;
+        size_t gy = a.rows < 65535 ? a.rows : 65535;
+        if (gy * C > slots) gy = slots / C;
+        if (gy == 0) gy = 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(C, (unsigned)gy, 1);
+        cfg.blockDim = dim3(kRowThreads, 1, 1);
+        cfg.stream = l.stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = C;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        return cudaLaunchKernelEx(&cfg, rows_max_sum_cluster_kernel<L, 32, 4>, (const L*)a.in, a.out_max, a.out_sum, a.rows,
+                                  a.n, a.row_stride);
+    }
     const int G = pick_group(a.n * sizeof(L));
     const size_t rows_per_cta = size_t(kRowThreads / 32) * (32 / G);
     size_t grid = (a.rows + rows_per_cta - 1) / rows_per_cta;

@@ -327,7 +327,13 @@ def test_bf16_f16_fp32_accumulate(cuda):
 
 
 @pytest.mark.parametrize('rows,n,dtype', [(512, 8192, torch.bfloat16), (100, 1000, torch.float32),
-                                          (33, 77, torch.float16), (4096, 64, torch.bfloat16), (2, 100000, torch.float32)])
+                                          (33, 77, torch.float16), (4096, 64, torch.bfloat16), (2, 100000, torch.float32),
+                                          # tiny dense rows through the shared-memory tile (1 ... 32 lanes per row)
+                                          (500001, 10, torch.float32), (140000, 33, torch.bfloat16), (70001, 64, torch.float16),
+                                          (45000, 100, torch.float32), (40000, 128, torch.bfloat16), (2100000, 2, torch.float32),
+                                          # few long rows: clusters of 1 ... 8 CTAs per row
+                                          (1, 3000001, torch.float32), (8, 1 << 20, torch.bfloat16), (100, 70001, torch.float32),
+                                          (700, 33000, torch.float16), (3000, 16400, torch.float32)])
 def test_rows_max_sum_fused(rows, n, dtype, cuda):
     g = torch.Generator(device='cpu').manual_seed(0)
     x = torch.randn(rows, n, generator=g).to(dtype)
