@@ -237,14 +237,12 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
     // fold ([2.7M, 100]: 40 rows per tile, 4 lanes each, 0.54 -> 0.61)
     unsigned width = 1;
     if (rows_per_tile <= 64)
-        while (width < 32 && rows_per_tile * width * 2 <= unsigned(kRowThreads)) width <<= 1;
+        while (width < 8 && rows_per_tile * width * 2 <= unsigned(kRowThreads)) width <<= 1;   // (a tile holds >= 32 rows)
     switch (width) {
         case 1: DB200_TINY(1); break;
         case 2: DB200_TINY(2); break;
         case 4: DB200_TINY(4); break;
-        case 8: DB200_TINY(8); break;
-        case 16: DB200_TINY(16); break;
-        default: DB200_TINY(32); break;
+        default: DB200_TINY(8); break;
     }
 #undef DB200_TINY
     return cudaGetLastError();
@@ -479,7 +477,7 @@ static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& 
         const size_t ntiles = (a.rows + rows_per_tile - 1) / rows_per_tile;
         unsigned width = 1;
         if (rows_per_tile <= 64)
-            while (width < 32 && rows_per_tile * width * 2 <= unsigned(kRowThreads)) width <<= 1;
+            while (width < 8 && rows_per_tile * width * 2 <= unsigned(kRowThreads)) width <<= 1;   // (a tile holds >= 32 rows)
 #define DB200_MS_TINY(W)                                                                                              \
         do {                                                                                                          \
             const unsigned pad = tiny_row_pad(n, W, unsigned(sizeof(L)), rows_per_tile);                              \
@@ -499,9 +497,7 @@ static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& 
             case 1: DB200_MS_TINY(1); break;
             case 2: DB200_MS_TINY(2); break;
             case 4: DB200_MS_TINY(4); break;
-            case 8: DB200_MS_TINY(8); break;
-            case 16: DB200_MS_TINY(16); break;
-            default: DB200_MS_TINY(32); break;
+            default: DB200_MS_TINY(8); break;
         }
 #undef DB200_MS_TINY
         return cudaGetLastError();
