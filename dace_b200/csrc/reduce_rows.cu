@@ -68,6 +68,9 @@ static inline int pick_group(size_t row_bytes) {
     int G = 1;
     const size_t per_lane = tuning().rows_lane_bytes > 0 ? size_t(tuning().rows_lane_bytes) : 128;
     while (G < 32 && size_t(G) * per_lane < row_bytes) G <<= 1;
+    // never a whole multi-vector row per lane: 32 lanes reading 32 rows 128 bytes apart touch 32 lines per load
+    // (bf16 [8M, 64]: 2.4 TB/s with one lane per 128-byte row, 6.4 with two)
+    if (G == 1 && row_bytes >= 128 && tuning().rows_lane_bytes == 0) G = 2;
     return G;
 }
 
