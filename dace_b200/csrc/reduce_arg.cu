@@ -426,7 +426,6 @@ static cudaError_t launch_arg_t(const ArgArgs& a_in, const Launch& l) {
             int G = 1;
             const size_t per_lane = tuning().rows_lane_bytes > 0 ? size_t(tuning().rows_lane_bytes) : 128;   // as in reduce_rows.cu
             while (G < 32 && size_t(G) * per_lane < row_bytes) G <<= 1;
-            if (G == 1 && row_bytes >= 128 && tuning().rows_lane_bytes == 0) G = 2;     // as in reduce_rows.cu
             const size_t rows_per_cta = size_t(kArgThreads / 32) * (32 / G);
             size_t grid = (rows + rows_per_cta - 1) / rows_per_cta;
             const size_t cap = size_t(sms) * resident_ctas<arg_rows_group_kernel<L, A, IsMax>>(kArgThreads);
