@@ -102,7 +102,10 @@ __device__ __forceinline__ void arg_fold_vec(A& best, long long& bidx, const Wor
 
 // A group of nthr threads scans n contiguous elements starting at p (element index `base` of
 // the row); each thread visits its elements in increasing index order.
-template <class L, class A, bool IsMax, int VB, int U>
+// SHORT: the caller guarantees at most U vectors per thread (rows of a sub-warp group): they go out as ONE
+// predicated batch - the unrolled loop below only starts with U whole vectors per thread, and what it leaves is
+// walked one round trip at a time (rows of 128 bytes, two lanes per row: two dependent trips).
+template <class L, class A, bool IsMax, int VB, int U, bool SHORT = false>
 __device__ __forceinline__ void span_arg(const L* __restrict__ p, size_t n, long long base, unsigned tid, unsigned nthr,
                                          A& best, long long& bidx) {
     constexpr int N = VecInfo<L, VB>::N;
@@ -117,17 +120,28 @@ __device__ __forceinline__ void span_arg(const L* __restrict__ p, size_t n, long
     const size_t nvec = (n - h) / N;
     const long long vbase = base + (long long)h;
     size_t v = tid;
-    for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
+    if constexpr (SHORT) {
         Words<VB> w[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
+        for (int u = 0; u < U; ++u)
+            if (v + size_t(u) * nthr < nvec) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
 #pragma unroll
         for (int u = 0; u < U; ++u)
-            arg_fold_vec<L, A, IsMax, VB>(best, bidx, w[u], vbase + (long long)((v + size_t(u) * nthr) * N));
-    }
-    for (; v < nvec; v += nthr) {
-        Words<VB> w = ldg_stream<VB>(pv + v * VB);
-        arg_fold_vec<L, A, IsMax, VB>(best, bidx, w, vbase + (long long)(v * N));
+            if (v + size_t(u) * nthr < nvec)
+                arg_fold_vec<L, A, IsMax, VB>(best, bidx, w[u], vbase + (long long)((v + size_t(u) * nthr) * N));
+    } else {
+        for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
+            Words<VB> w[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                arg_fold_vec<L, A, IsMax, VB>(best, bidx, w[u], vbase + (long long)((v + size_t(u) * nthr) * N));
+        }
+        for (; v < nvec; v += nthr) {
+            Words<VB> w = ldg_stream<VB>(pv + v * VB);
+            arg_fold_vec<L, A, IsMax, VB>(best, bidx, w, vbase + (long long)(v * N));
+        }
     }
     for (size_t i = h + nvec * N + tid; i < n; i += nthr) {
         A x = to_acc<A, L>(ldg_scalar(p + i));
@@ -138,7 +152,7 @@ __device__ __forceinline__ void span_arg(const L* __restrict__ p, size_t n, long
 constexpr int kArgThreads = 256;
 
 // ---- contiguous reduced axis, short rows: G lanes per row -------------------------------------
-template <class L, class A, bool IsMax>
+template <class L, class A, bool IsMax, bool SHORT>
 __global__ void __launch_bounds__(kArgThreads)
 arg_rows_group_kernel(const L* __restrict__ in, size_t rows, size_t n, size_t inner, long long so, long long si,
                       ArgOut out, A init, int G) {
@@ -155,7 +169,7 @@ arg_rows_group_kernel(const L* __restrict__ in, size_t rows, size_t n, size_t in
         long long i = kNoIndex;
         if (active) {
             const L* p = in + (long long)(r / inner) * so + (long long)(r % inner) * si;
-            span_arg<L, A, IsMax, 32, 4>(p, n, 0, g, G, v, i);
+            span_arg<L, A, IsMax, 32, 4, SHORT>(p, n, 0, g, G, v, i);
         }
         for (int m = G >> 1; m >= 1; m >>= 1) {
             A ov = shfl_xor(v, m);
@@ -428,10 +442,18 @@ static cudaError_t launch_arg_t(const ArgArgs& a_in, const Launch& l) {
             while (G < 32 && size_t(G) * per_lane < row_bytes) G <<= 1;
             const size_t rows_per_cta = size_t(kArgThreads / 32) * (32 / G);
             size_t grid = (rows + rows_per_cta - 1) / rows_per_cta;
-            const size_t cap = size_t(sms) * resident_ctas<arg_rows_group_kernel<L, A, IsMax>>(kArgThreads);
+            if (row_bytes / 32 <= size_t(G) * 4) {            // at most four vectors per lane: one predicated batch
+                size_t cap = size_t(sms) * resident_ctas<arg_rows_group_kernel<L, A, IsMax, true>>(kArgThreads);
+                if (grid > cap) grid = cap;
+                if (grid == 0) grid = 1;
+                arg_rows_group_kernel<L, A, IsMax, true><<<(unsigned)grid, kArgThreads, 0, l.stream>>>(
+                    (const L*)a.in, rows, n, a.inner, a.in_stride_o, a.in_stride_i, out, init, G);
+                return cudaGetLastError();
+            }
+            const size_t cap = size_t(sms) * resident_ctas<arg_rows_group_kernel<L, A, IsMax, false>>(kArgThreads);
             if (grid > cap) grid = cap;
             if (grid == 0) grid = 1;
-            arg_rows_group_kernel<L, A, IsMax><<<(unsigned)grid, kArgThreads, 0, l.stream>>>(
+            arg_rows_group_kernel<L, A, IsMax, false><<<(unsigned)grid, kArgThreads, 0, l.stream>>>(
                 (const L*)a.in, rows, n, a.inner, a.in_stride_o, a.in_stride_i, out, init, G);
             return cudaGetLastError();
         }

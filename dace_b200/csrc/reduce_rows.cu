@@ -297,7 +297,7 @@ cudaError_t launch_rows(int red, int dtin, int dtout, const RowsArgs& a, const L
 // style pair, reference tests/softmax_test.py:8-31 runs them as two Reduce
 // nodes, i.e. two full passes).  fp32 accumulation for every input type.
 // ---------------------------------------------------------------------------
-template <class L, int VB, int U>
+template <class L, int VB, int U, bool SHORT = false>       // SHORT: at most U vectors per thread, one predicated batch
 __device__ __forceinline__ void span_max_sum(const L* __restrict__ p, size_t n, unsigned tid, unsigned nthr,
                                              float& mx, float& sm) {
     constexpr int N = VecInfo<L, VB>::N;
@@ -315,26 +315,43 @@ __device__ __forceinline__ void span_max_sum(const L* __restrict__ p, size_t n, 
     const char* pv = reinterpret_cast<const char*>(p + h);
     const size_t nvec = (n - h) / N;
     size_t v = tid;
-    for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
+    if constexpr (SHORT) {
         Words<VB> w[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
+        for (int u = 0; u < U; ++u)
+            if (v + size_t(u) * nthr < nvec) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
 #pragma unroll
         for (int u = 0; u < U; ++u)
+            if (v + size_t(u) * nthr < nvec) {
 #pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    float x = vec_elem<L, float, VB>(w[u], j);
+                    amax[j % NA] = fmaxf(amax[j % NA], x);
+                    asum[j % NA] += x;
+                }
+            }
+    } else {
+        for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
+            Words<VB> w[U];
+    #pragma unroll
+            for (int u = 0; u < U; ++u) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
+    #pragma unroll
+            for (int u = 0; u < U; ++u)
+    #pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    float x = vec_elem<L, float, VB>(w[u], j);
+                    amax[j % NA] = fmaxf(amax[j % NA], x);
+                    asum[j % NA] += x;
+                }
+        }
+        for (; v < nvec; v += nthr) {
+            Words<VB> w = ldg_stream<VB>(pv + v * VB);
+    #pragma unroll
             for (int j = 0; j < N; ++j) {
-                float x = vec_elem<L, float, VB>(w[u], j);
+                float x = vec_elem<L, float, VB>(w, j);
                 amax[j % NA] = fmaxf(amax[j % NA], x);
                 asum[j % NA] += x;
             }
-    }
-    for (; v < nvec; v += nthr) {
-        Words<VB> w = ldg_stream<VB>(pv + v * VB);
-#pragma unroll
-        for (int j = 0; j < N; ++j) {
-            float x = vec_elem<L, float, VB>(w, j);
-            amax[j % NA] = fmaxf(amax[j % NA], x);
-            asum[j % NA] += x;
         }
     }
     for (size_t i = h + nvec * N + tid; i < n; i += nthr) {
@@ -345,7 +362,7 @@ __device__ __forceinline__ void span_max_sum(const L* __restrict__ p, size_t n, 
     sm = (asum[0] + asum[1]) + (asum[2] + asum[3]);
 }
 
-template <class L, int VB, int U>
+template <class L, int VB, int U, bool SHORT>
 __global__ void __launch_bounds__(kRowThreads)
 rows_max_sum_kernel(const L* __restrict__ in, float* __restrict__ out_max, float* __restrict__ out_sum,
                     size_t rows, size_t n, size_t row_stride, int G) {
@@ -359,7 +376,7 @@ rows_max_sum_kernel(const L* __restrict__ in, float* __restrict__ out_max, float
         const size_t r = rb + sub;
         const bool active = r < rows;
         float mx = OpMax<float>::neutral(), sm = 0.f;
-        if (active) span_max_sum<L, VB, U>(in + r * row_stride, n, g, G, mx, sm);
+        if (active) span_max_sum<L, VB, U, SHORT>(in + r * row_stride, n, g, G, mx, sm);
         for (int m = G >> 1; m >= 1; m >>= 1) {
             mx = fmaxf(mx, __shfl_xor_sync(kFullMask, mx, m));
             sm += __shfl_xor_sync(kFullMask, sm, m);
@@ -530,10 +547,18 @@ static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& 
     const int G = pick_group(a.n * sizeof(L));
     const size_t rows_per_cta = size_t(kRowThreads / 32) * (32 / G);
     size_t grid = (a.rows + rows_per_cta - 1) / rows_per_cta;
-    const size_t cap = size_t(sms) * resident_ctas<rows_max_sum_kernel<L, 32, 4>>(kRowThreads);
+    if (a.n * sizeof(L) / 32 <= size_t(G) * 4) {             // at most four vectors per lane
+        const size_t cap = size_t(sms) * resident_ctas<rows_max_sum_kernel<L, 32, 4, true>>(kRowThreads);
+        if (grid > cap) grid = cap;
+        if (grid == 0) grid = 1;
+        rows_max_sum_kernel<L, 32, 4, true><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
+            (const L*)a.in, a.out_max, a.out_sum, a.rows, a.n, a.row_stride, G);
+        return cudaGetLastError();
+    }
+    const size_t cap = size_t(sms) * resident_ctas<rows_max_sum_kernel<L, 32, 4, false>>(kRowThreads);
     if (grid > cap) grid = cap;
     if (grid == 0) grid = 1;
-    rows_max_sum_kernel<L, 32, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
+    rows_max_sum_kernel<L, 32, 4, false><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
         (const L*)a.in, a.out_max, a.out_sum, a.rows, a.n, a.row_stride, G);
     return cudaGetLastError();
 }
