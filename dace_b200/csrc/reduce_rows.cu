@@ -22,7 +22,7 @@ namespace db200 {
 constexpr int kRowThreads = 256;
 
 // G lanes per row; 32/G rows per warp per step.  G is a run-time power of two.
-template <class L, class A, class S, class Op, int VB, int U>
+template <class L, class A, class S, class Op, int VB, int U, bool SHORT>
 __global__ void __launch_bounds__(kRowThreads)
 rows_group_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, size_t n, size_t row_stride,
                   ptrdiff_t out_stride, Finish<A> fin, int G) {
@@ -41,7 +41,7 @@ rows_group_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, si
         const size_t r = rb + sub;
         const bool active = r < rows;
         A v = Op::neutral();
-        if (active) v = span_accumulate<L, A, Op, VB, U>(in + r * row_stride, n, g, G);
+        if (active) v = span_accumulate<L, A, Op, VB, U, SHORT>(in + r * row_stride, n, g, G);
         for (int m = G >> 1; m >= 1; m >>= 1) v = Op::apply(v, shfl_xor(v, m));
         if (active && g == 0) write_result<Op, A, S>(out + ptrdiff_t(r) * out_stride, v, fin);
     }
@@ -272,12 +272,18 @@ static cudaError_t launch_rows_t(const RowsArgs& a, const Launch& l) {
     const int G = pick_group(row_bytes);
     const size_t rows_per_cta = size_t(kRowThreads / 32) * (32 / G);
     size_t grid = (a.rows + rows_per_cta - 1) / rows_per_cta;
-    const size_t cap = size_t(sms) * resident_ctas<rows_group_kernel<L, A, S, Op, VB, 4>>(kRowThreads);   // one full wave
+    const bool short_rows = row_bytes / 32 <= size_t(G) * 4;      // at most four vectors per lane: one batch, no loop
+    const size_t cap = size_t(sms) * (short_rows ? resident_ctas<rows_group_kernel<L, A, S, Op, VB, 4, true>>(kRowThreads)
+                                                 : resident_ctas<rows_group_kernel<L, A, S, Op, VB, 4, false>>(kRowThreads));   // one full wave
     if (grid > cap) grid = cap;
     else if (grid > size_t(sms)) grid = ((grid + sms - 1) / sms) * sms;   // whole CTAs per SM (see the kernel)
     if (grid == 0) grid = 1;
-    rows_group_kernel<L, A, S, Op, VB, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
-        (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G);
+    if (short_rows)
+        rows_group_kernel<L, A, S, Op, VB, 4, true><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
+            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G);
+    else
+        rows_group_kernel<L, A, S, Op, VB, 4, false><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
+            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G);
     return cudaGetLastError();
 }
 

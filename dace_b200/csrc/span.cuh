@@ -30,7 +30,9 @@ __device__ __forceinline__ A fold_acc(const A (&acc)[NA]) {
     return v;
 }
 
-template <class L, class A, class Op, int VB, int U>
+// SHORT: the caller guarantees at most U vectors per thread (rows shorter than U * 32 bytes * group width): they are
+// loaded as one predicated batch, no loop.
+template <class L, class A, class Op, int VB, int U, bool SHORT = false>
 __device__ __forceinline__ A span_accumulate(const L* __restrict__ p, size_t n, unsigned tid, unsigned nthr) {
     constexpr int N = VecInfo<L, VB>::N;
     constexpr int NA = VecInfo<L, VB>::NA;
@@ -46,6 +48,16 @@ __device__ __forceinline__ A span_accumulate(const L* __restrict__ p, size_t n, 
     const char* pv = reinterpret_cast<const char*>(p + h);
     const size_t nvec = (n - h) / N;
     size_t v = tid;
+    if constexpr (SHORT) {
+        Words<VB> w[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v + size_t(u) * nthr < nvec) w[u] = ldg_stream<VB>(pv + (v + size_t(u) * nthr) * VB);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v + size_t(u) * nthr < nvec) fold_vec<L, A, Op, VB>(acc, w[u]);
+        v = nvec;
+    }
     for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
         Words<VB> w[U];
 #pragma unroll
