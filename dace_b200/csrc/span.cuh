@@ -43,12 +43,17 @@ __device__ __forceinline__ A span_accumulate(const L* __restrict__ p, size_t n, 
     const size_t addr = reinterpret_cast<size_t>(p);
     size_t h = ((size_t(VB) - (addr & size_t(VB - 1))) & size_t(VB - 1)) / sizeof(L);
     if (h > n) h = n;
-    for (size_t i = tid; i < h; i += nthr) acc[0] = Op::apply(acc[0], to_acc<A, L>(ldg_scalar(p + i)));
-
     const char* pv = reinterpret_cast<const char*>(p + h);
     const size_t nvec = (n - h) / N;
     size_t v = tid;
     if constexpr (SHORT) {
+        // everything in one round trip: the first head and tail elements are requested before the vectors and
+        // folded after them (rows that are not whole vectors: head, vectors, tail were three dependent trips)
+        const size_t t0 = h + nvec * N;
+        const bool has_head = tid < h, has_tail = t0 + tid < n;
+        L he{}, te{};
+        if (has_head) he = ldg_scalar(p + tid);
+        if (has_tail) te = ldg_scalar(p + t0 + tid);
         Words<VB> w[U];
 #pragma unroll
         for (int u = 0; u < U; ++u)
@@ -56,8 +61,13 @@ __device__ __forceinline__ A span_accumulate(const L* __restrict__ p, size_t n, 
 #pragma unroll
         for (int u = 0; u < U; ++u)
             if (v + size_t(u) * nthr < nvec) fold_vec<L, A, Op, VB>(acc, w[u]);
-        v = nvec;
+        if (has_head) acc[0] = Op::apply(acc[0], to_acc<A, L>(he));
+        if (has_tail) acc[0] = Op::apply(acc[0], to_acc<A, L>(te));
+        for (size_t i = size_t(tid) + nthr; i < h; i += nthr) acc[0] = Op::apply(acc[0], to_acc<A, L>(ldg_scalar(p + i)));
+        for (size_t i = t0 + tid + nthr; i < n; i += nthr) acc[0] = Op::apply(acc[0], to_acc<A, L>(ldg_scalar(p + i)));
+        return fold_acc<A, Op, NA>(acc);
     }
+    for (size_t i = tid; i < h; i += nthr) acc[0] = Op::apply(acc[0], to_acc<A, L>(ldg_scalar(p + i)));
     for (; v + size_t(U - 1) * nthr < nvec; v += size_t(U) * nthr) {
         Words<VB> w[U];
 #pragma unroll
