@@ -214,6 +214,10 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
     if ((a.n * sizeof(L)) % 32 == 0 && (reinterpret_cast<size_t>(a.in) & 31) == 0 && !tuning().tiny_rows_always &&
         !(sizeof(L) >= 4 && a.n * sizeof(L) == 64))          // (64-byte rows of 4-byte elements: 4.4 vs 3.3 TB/s)
         return cudaErrorNotSupported;
+    // ... and so do longer odd rows since that kernel fetches head, vectors and tail in one round trip: the tile
+    // keeps rows under 192 bytes of 4- and 8-byte elements ([8M, 33] f32 5.1 vs 4.7 TB/s, [32M, 7] 4.1 vs 2.0; but
+    // [2.7M, 100] f32 5.6 vs 6.3 through the lanes, bf16 [5M, 100] 3.4 vs 5.2, f64 [4M, 33] 4.0 vs 5.5)
+    if ((sizeof(L) < 4 || a.n * sizeof(L) >= 192) && !tuning().tiny_rows_always) return cudaErrorNotSupported;
     const unsigned n = unsigned(a.n);
     const unsigned rpt_vec = tiny_rows_per_tile_vec(n, unsigned(sizeof(L)), a.in);
     const int vec16 = rpt_vec > 0;
@@ -499,7 +503,7 @@ static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& 
     const int sms = sm_count();
     const bool whole_vectors = (a.n * sizeof(L)) % 32 == 0 && (reinterpret_cast<size_t>(a.in) & 31) == 0;
     if (a.n >= 2 && a.n <= size_t(kTinyMaxN) && a.row_stride == a.n && a.rows * a.n >= (size_t(1) << 22) &&
-        !tuning().no_tiny_rows && (!whole_vectors || tuning().tiny_rows_always)) {
+        !tuning().no_tiny_rows && ((!whole_vectors && sizeof(L) >= 4 && a.n * sizeof(L) < 192) || tuning().tiny_rows_always)) {
         const unsigned n = unsigned(a.n);
         const unsigned rpt_vec = tiny_rows_per_tile_vec(n, unsigned(sizeof(L)), a.in);
         const int vec16 = rpt_vec > 0;
