@@ -43,7 +43,6 @@ static Tuning read_tuning() {
     t.no_tiled = flag("DACE_B200_NO_TILED");
     t.no_tiny_rows = flag("DACE_B200_NO_TINY_ROWS");
     t.no_outer_first = flag("DACE_B200_NO_OUTER_FIRST");
-    t.tiny_rows_always = flag("DACE_B200_TINY_ROWS_ALWAYS");
     t.wide_wc = num("DACE_B200_WIDE_WC", 0);
     t.part_chunk_log2 = num("DACE_B200_PART_CHUNK_LOG2", 0);
     t.rows_lane_bytes = num("DACE_B200_ROWS_LANE_BYTES", 0);

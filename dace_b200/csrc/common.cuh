@@ -397,7 +397,7 @@ struct Launch {
 // Experiment knobs (environment variables), read ONCE when the library is loaded - never on a call path.
 struct Tuning {
     bool no_two_pass, no_axis_sort, no_peel, no_wide_cols, no_few_rows, no_narrow_cols, no_partition, no_tiled, no_tiny_rows,
-         no_outer_first, tiny_rows_always;
+         no_outer_first;
     int wide_wc;            // DACE_B200_WIDE_WC (0 = default)
     int rows_lane_bytes;    // DACE_B200_ROWS_LANE_BYTES (0 = default)
     int part_chunk_log2;    // DACE_B200_PART_CHUNK_LOG2 (0 = default)

@@ -211,13 +211,13 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
         return cudaErrorNotSupported;
     // rows that are whole 32-byte vectors stream through the lanes-per-row kernel at full speed since its lanes
     // take 128 bytes each ([4M, 64] f32: 6.1 TB/s there, 4.3 through the tile)
-    if ((a.n * sizeof(L)) % 32 == 0 && (reinterpret_cast<size_t>(a.in) & 31) == 0 && !tuning().tiny_rows_always &&
+    if ((a.n * sizeof(L)) % 32 == 0 && (reinterpret_cast<size_t>(a.in) & 31) == 0 &&
         !(sizeof(L) >= 4 && a.n * sizeof(L) == 64))          // (64-byte rows of 4-byte elements: 4.4 vs 3.3 TB/s)
         return cudaErrorNotSupported;
     // ... and so do longer odd rows since that kernel fetches head, vectors and tail in one round trip: the tile
     // keeps rows under 192 bytes of 4- and 8-byte elements ([8M, 33] f32 5.1 vs 4.7 TB/s, [32M, 7] 4.1 vs 2.0; but
     // [2.7M, 100] f32 5.6 vs 6.3 through the lanes, bf16 [5M, 100] 3.4 vs 5.2, f64 [4M, 33] 4.0 vs 5.5)
-    if ((sizeof(L) < 4 || a.n * sizeof(L) >= 192) && !tuning().tiny_rows_always) return cudaErrorNotSupported;
+    if (sizeof(L) < 4 || a.n * sizeof(L) >= 192) return cudaErrorNotSupported;
     const unsigned n = unsigned(a.n);
     const unsigned rpt_vec = tiny_rows_per_tile_vec(n, unsigned(sizeof(L)), a.in);
     const int vec16 = rpt_vec > 0;
@@ -239,18 +239,8 @@ static cudaError_t launch_rows_tiny(const RowsArgs& a, const Launch& l) {
                 (const L*)a.in, (S*)a.out, a.rows, n, rows_per_tile, a.out_stride, fin, pad, tiny_magic(n), 0);            \
         }                                                                                                               \
     } while (0)
-    // lanes per row: a thread per row while a tile holds at least 64 rows (n <= 64: measured faster than two lanes
-    // per row, [8M, 33] 0.63 vs 0.57 of the peak); for longer rows as many lanes as keep the 256 threads busy in the
-    // fold ([2.7M, 100]: 40 rows per tile, 4 lanes each, 0.54 -> 0.61)
-    unsigned width = 1;
-    if (rows_per_tile <= 64)
-        while (width < 8 && rows_per_tile * width * 2 <= unsigned(kRowThreads)) width <<= 1;   // (a tile holds >= 32 rows)
-    switch (width) {
-        case 1: DB200_TINY(1); break;
-        case 2: DB200_TINY(2); break;
-        case 4: DB200_TINY(4); break;
-        default: DB200_TINY(8); break;
-    }
+    // rows under 192 bytes: a tile holds at least 80 of them, a thread folds a whole row
+    DB200_TINY(1);
 #undef DB200_TINY
     return cudaGetLastError();
 }
@@ -503,15 +493,12 @@ static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& 
     const int sms = sm_count();
     const bool whole_vectors = (a.n * sizeof(L)) % 32 == 0 && (reinterpret_cast<size_t>(a.in) & 31) == 0;
     if (a.n >= 2 && a.n <= size_t(kTinyMaxN) && a.row_stride == a.n && a.rows * a.n >= (size_t(1) << 22) &&
-        !tuning().no_tiny_rows && ((!whole_vectors && sizeof(L) >= 4 && a.n * sizeof(L) < 192) || tuning().tiny_rows_always)) {
+        !tuning().no_tiny_rows && !whole_vectors && sizeof(L) >= 4 && a.n * sizeof(L) < 192) {
         const unsigned n = unsigned(a.n);
         const unsigned rpt_vec = tiny_rows_per_tile_vec(n, unsigned(sizeof(L)), a.in);
         const int vec16 = rpt_vec > 0;
         const unsigned rows_per_tile = vec16 ? rpt_vec : kTinyTile / n;
         const size_t ntiles = (a.rows + rows_per_tile - 1) / rows_per_tile;
-        unsigned width = 1;
-        if (rows_per_tile <= 64)
-            while (width < 8 && rows_per_tile * width * 2 <= unsigned(kRowThreads)) width <<= 1;   // (a tile holds >= 32 rows)
 #define DB200_MS_TINY(W)                                                                                              \
         do {                                                                                                          \
             const unsigned pad = tiny_row_pad(n, W, unsigned(sizeof(L)), rows_per_tile);                              \
@@ -527,12 +514,7 @@ static cudaError_t launch_rows_max_sum_t(const RowsMaxSumArgs& a, const Launch& 
                     (const L*)a.in, a.out_max, a.out_sum, a.rows, n, rows_per_tile, pad, tiny_magic(n), 0);              \
             }                                                                                                         \
         } while (0)
-        switch (width) {
-            case 1: DB200_MS_TINY(1); break;
-            case 2: DB200_MS_TINY(2); break;
-            case 4: DB200_MS_TINY(4); break;
-            default: DB200_MS_TINY(8); break;
-        }
+        DB200_MS_TINY(1);
 #undef DB200_MS_TINY
         return cudaGetLastError();
     }

@@ -16,7 +16,6 @@ dump $B/reduce_cols.o 'cols_narrow_kernel<float, float, db200::OpSum<float> >' r
 dump $B/reduce_cols.o 'cols_small_kernel<float, float, float, db200::OpSum<float> >' r2_cols_small_f32_sum.sass
 dump $B/reduce_cols.o 'cols_few_rows_kernel<float, float, float, db200::OpSum<float> >' r2_cols_few_rows_f32_sum.sass
 dump $B/reduce_rows.o 'rows_tiny_kernel<float, float, float, db200::OpSum<float>, 1, false>' r2_rows_tiny_f32_sum_w1.sass
-dump $B/reduce_rows.o 'rows_tiny_kernel<float, float, float, db200::OpSum<float>, 4, false>' r2_rows_tiny_f32_sum_w4.sass
 dump $B/reduce_generic.o 'generic.*<float, float, float, db200::OpSum<float>' r2_generic_f32_sum.sass
 dump $B/wcr_scatter.o 'scatter_smem_kernel<3, int, int, false, 4>' r2_scatter_smem_i32.sass
 dump $B/wcr_scatter.o 'scatter_global_kernel<3, int, int, false, 4>' r2_scatter_global_i32_sum.sass
