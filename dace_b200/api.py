@@ -202,8 +202,8 @@ def reduce(op, in_array: torch.Tensor, out_array: Optional[torch.Tensor] = None,
         ident_buf = ctypes.create_string_buffer(scalar_bytes(identity, dt_out), 8)
     sptr = _stream_ptr(stream)
     if workspace is None:
-        # shapes with >= 3 axes may have a two-pass plan that wants scratch behind the base workspace
-        need = int(lib.dace_b200_reduce_nd_workspace_bytes(dt_in, dt_out, nd, shape, istr, mask)) if nd >= 3 else 0
+        # multi-pass plans (interleaved axes, padded views) want scratch behind the base workspace
+        need = int(lib.dace_b200_reduce_nd_workspace_bytes(dt_in, dt_out, nd, shape, istr, mask)) if nd >= 2 else 0
         workspace = _default_workspace(_WORKSPACES, in_array.device, sptr, need, True)
     with _on_device(in_array.device):
         status = lib.dace_b200_reduce_nd(int(rt), dt_in, dt_out, in_array.data_ptr(), out_array.data_ptr(), nd,

@@ -439,7 +439,10 @@ static cudaError_t plan_dims(int red, int dtin, int dtout, const void* in, void*
         cudaError_t ef = plan_fast(red, dtin, dtout, in, out, c, nc, nr, identity, l);
         if (ef != cudaErrorNotSupported) return ef;
     }
-    if (nr > 0 && nk > 0 && nc >= 3) {
+    // (also with nothing kept: all elements of a padded view, [R1, R2] with a pitch - the rows go into an
+    // intermediate, the intermediate is one contiguous run; the strided kernel folded such a view with ONE warp:
+    // 0.96 s for a [16384, 16000] window of a [16384, 16384] array)
+    if (nr > 0 && nc >= 2 && (nk > 0 ? nc >= 3 : true)) {
         cudaError_t ei = plan_inner_first(red, dtin, dtout, in, out, c, nc, identity, l, depth);
         if (ei != cudaErrorNotSupported) return ei;
     }

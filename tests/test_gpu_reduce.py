@@ -747,3 +747,26 @@ def test_signed_zero_max_is_a_zero(cuda):
     neg = torch.full((4097, ), -0.0, device=cuda)
     got = db.reduce('lambda a, b: max(a, b)', neg, axis=None, identity=-1.0)
     assert got.item() == 0.0 and torch.signbit(got).item()      # all inputs -0.0: no choice to make
+
+
+@pytest.mark.parametrize('dtype', [np.float32, np.int32, np.float64, np.int16])
+def test_all_elements_of_padded_and_strided_views(dtype, cuda):
+    """Every element of a window of a larger array (a pitch between the rows): rows into an intermediate, then one
+    contiguous run (api.cu plan_inner_first with nothing kept) - not one warp of the strided kernel; also a 3-D
+    window padded on two levels, sum and max, identity None."""
+    rng = np.random.default_rng(21)
+    base = _data(rng, [3000, 2500], dtype)
+    tb = torch.from_numpy(base).to(cuda)
+    for view, host in ((tb[:, :2400], base[:, :2400]), (tb[5:2000, 17:999], base[5:2000, 17:999]), (tb[::2, :2400], base[::2, :2400])):
+        for op, lam, red in (('sum', 'lambda a, b: a + b', O.SUM), ('max', 'lambda a, b: max(a, b)', O.MAX)):
+            out = torch.zeros((), dtype=tb.dtype, device=cuda)
+            ident = 0 if op == 'sum' else _identity('max', dtype)
+            db.reduce(lam, view, out, axis=None, identity=ident)
+            ref = O.reduce(red, np.ascontiguousarray(host), None, identity=ident, wide=True)
+            _check(out.cpu().numpy().reshape(ref.shape), ref, dtype, np.ascontiguousarray(host), None, op)
+    cube = _data(rng, [40, 300, 500], dtype)
+    tc = torch.from_numpy(cube).to(cuda)
+    v, h = tc[:, :250, :450], np.ascontiguousarray(cube[:, :250, :450])
+    out = torch.zeros((), dtype=tc.dtype, device=cuda)
+    db.reduce('lambda a, b: a + b', v, out, axis=None, identity=0)
+    _check(out.cpu().numpy().reshape(()), O.reduce(O.SUM, h, None, identity=0, wide=True), dtype, h, None, 'sum')
