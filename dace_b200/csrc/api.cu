@@ -113,12 +113,15 @@ static cudaError_t plan_split(int red, int dtin, int dtout, const void* in, void
 
 // [K, R] with contiguous R: few long rows -> split kernel, else the rows kernel.
 static cudaError_t plan_rows(int red, int dtin, int dtout, const void* in, void* out, size_t rows, size_t n,
-                             size_t row_stride, ptrdiff_t out_stride, const void* identity, const Launch& l) {
+                             size_t row_stride, ptrdiff_t out_stride, const void* identity, const Launch& l,
+                             size_t hi_count = 1, size_t hi_in_stride = 0, ptrdiff_t hi_out_stride = 0) {
+    if (hi_count > 65535) return cudaErrorNotSupported;
     if (l.dry_need) return cudaSuccess;
     const size_t row_bytes = n * dtype_size(dtin);
-    if (rows < 2 * (size_t)sm_count() && row_bytes >= (size_t(128) << 10) && rows <= kCounters)
+    if (hi_count == 1 && rows < 2 * (size_t)sm_count() && row_bytes >= (size_t(128) << 10) && rows <= kCounters)
         return plan_split(red, dtin, dtout, in, out, rows, n, row_stride, out_stride, identity, l);
     RowsArgs a{in, out, rows, n, row_stride, out_stride, identity};
+    a.hi_count = hi_count; a.hi_in_stride = hi_in_stride; a.hi_out_stride = hi_out_stride;
     return launch_rows(red, dtin, dtout, a, l);
 }
 
@@ -252,6 +255,14 @@ static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void*
             return plan_rows(red, dtin, dtout, in, out, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[0].in_stride,
                              (ptrdiff_t)c[0].out_stride, identity, l);
         }
+        // [K1, K2, R]: rows of a window of a larger array (a pitch after every K2 rows) -> rows on two levels.
+        if (nc == 3 && !c[0].reduced && !c[1].reduced && c[2].reduced && c[2].in_stride == 1 && c[0].in_stride >= 0 &&
+            c[1].in_stride >= 0 && c[0].shape <= 65535) {
+            cudaError_t e = plan_rows(red, dtin, dtout, in, out, (size_t)c[1].shape, (size_t)c[2].shape, (size_t)c[1].in_stride,
+                                      (ptrdiff_t)c[1].out_stride, identity, l, (size_t)c[0].shape, (size_t)c[0].in_stride,
+                                      (ptrdiff_t)c[0].out_stride);
+            if (e != cudaErrorNotSupported) return e;
+        }
         // [R, K] / [K1, R, K2] with contiguous trailing K -> cols.
         if (nc == 2 && c[0].reduced && !c[1].reduced && c[1].in_stride == 1 && c[0].in_stride >= 0) {
             ColsArgs a{in, out, 1, (size_t)c[0].shape, (size_t)c[1].shape, 0, (size_t)c[0].in_stride,
@@ -372,8 +383,14 @@ static cudaError_t plan_inner_first(int red, int dtin, int dtout, const void* in
     if (j < 1 || nc - 1 - j > 1) return cudaErrorNotSupported;          // needs outer axes; at most one kept axis inside
     const bool has_inner = j == nc - 2;
     if (c[nc - 1].in_stride != 1 || c[j].in_stride < 1 || c[j].shape < 2) return cudaErrorNotSupported;
-    for (int i = 0; i + 1 < j; ++i)                                        // the outer axes form one dense index
-        if (c[i].in_stride != c[i + 1].in_stride * c[i + 1].shape) return cudaErrorNotSupported;
+    bool dense = true;
+    for (int i = 0; i + 1 < j; ++i)                                        // the outer axes form one dense index ...
+        if (c[i].in_stride != c[i + 1].in_stride * c[i + 1].shape) dense = false;
+    // ... or there are exactly two of them and the innermost axis is the folded one: rows on two levels (windows of a
+    // larger 3-D array: every axis combination that folds the innermost axis ended in the strided kernel - all
+    // elements of a [1024, 500, 500] window of a [1024, 512, 512] array with one warp, 1.35 s)
+    const bool two_level = !dense && j == 2 && nc == 3 && c[0].in_stride >= 0 && c[0].shape <= 65535;
+    if (!dense && !two_level) return cudaErrorNotSupported;
     if (c[j - 1].in_stride < 0) return cudaErrorNotSupported;
     const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
     unsigned char neutral[8];
@@ -392,6 +409,9 @@ static cudaError_t plan_inner_first(int red, int dtin, int dtout, const void* in
     if (has_inner) {
         ColsArgs a{in, mid, O, R, K, (size_t)c[j - 1].in_stride, (size_t)c[j].in_stride, (ptrdiff_t)K, 1, neutral};
         e = plan_cols(red, dtin, dtmid, a, l);
+    } else if (two_level) {
+        e = plan_rows(red, dtin, dtmid, in, mid, (size_t)c[1].shape, R, (size_t)c[1].in_stride, 1, neutral, l,
+                      (size_t)c[0].shape, (size_t)c[0].in_stride, (ptrdiff_t)c[1].shape);
     } else {
         e = plan_rows(red, dtin, dtmid, in, mid, O, R, (size_t)c[j - 1].in_stride, 1, neutral, l);
     }

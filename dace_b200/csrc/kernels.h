@@ -24,6 +24,10 @@ struct RowsArgs {
     const void* in; void* out;
     size_t rows; size_t n; size_t row_stride; ptrdiff_t out_stride;
     const void* identity;
+    // A second, outer level of rows (windows of a larger array: [A, B, n] with a pitch after every B rows): the
+    // kernels run `hi_count` slices of `rows` rows along gridDim.y, slice h starting at in + h * hi_in_stride and
+    // writing from out + h * hi_out_stride (element strides).  1 / 0 / 0 = one level.
+    size_t hi_count = 1; size_t hi_in_stride = 0; ptrdiff_t hi_out_stride = 0;
 };
 cudaError_t launch_rows(int red, int dtin, int dtout, const RowsArgs& a, const Launch& l);
 

@@ -25,7 +25,9 @@ constexpr int kRowThreads = 256;
 template <class L, class A, class S, class Op, int VB, int U, bool SHORT>
 __global__ void __launch_bounds__(kRowThreads)
 rows_group_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, size_t n, size_t row_stride,
-                  ptrdiff_t out_stride, Finish<A> fin, int G) {
+                  ptrdiff_t out_stride, Finish<A> fin, int G, size_t hi_in_stride, ptrdiff_t hi_out_stride) {
+    in += size_t(blockIdx.y) * hi_in_stride;          // outer level of rows (RowsArgs::hi_*), one slice per blockIdx.y
+    out += ptrdiff_t(blockIdx.y) * hi_out_stride;
     const unsigned lane = threadIdx.x & 31;
     const unsigned g = lane & (G - 1);            // lane within the row group
     const unsigned sub = lane / G;                // row slot within the warp
@@ -51,8 +53,10 @@ rows_group_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, si
 template <class L, class A, class S, class Op, int VB, int U>
 __global__ void __launch_bounds__(kRowThreads)
 rows_block_kernel(const L* __restrict__ in, S* __restrict__ out, size_t rows, size_t n, size_t row_stride,
-                  ptrdiff_t out_stride, Finish<A> fin) {
+                  ptrdiff_t out_stride, Finish<A> fin, size_t hi_in_stride, ptrdiff_t hi_out_stride) {
     __shared__ A scratch[32];
+    in += size_t(blockIdx.y) * hi_in_stride;
+    out += ptrdiff_t(blockIdx.y) * hi_out_stride;
     for (size_t r = blockIdx.x; r < rows; r += gridDim.x) {
         A v = span_accumulate<L, A, Op, VB, U>(in + r * row_stride, n, threadIdx.x, kRowThreads);
         v = block_reduce<Op, A>(v, scratch);
@@ -249,18 +253,21 @@ template <class T, class Op>
 static cudaError_t launch_rows_t(const RowsArgs& a, const Launch& l) {
     using L = typename T::L; using A = typename T::A; using S = typename T::S;
     constexpr int VB = 32;
-    {
+    if (a.hi_count > 65535 || a.hi_count == 0) return cudaErrorNotSupported;
+    if (a.hi_count == 1) {
         cudaError_t e = launch_rows_tiny<T, Op>(a, l);
         if (e != cudaErrorNotSupported) return e;
     }
     Finish<A> fin = make_finish<A, S>(a.identity);
     const size_t row_bytes = a.n * sizeof(L);
     const int sms = sm_count();
+    const unsigned gy = unsigned(a.hi_count);
     if (row_bytes >= (size_t(32) << 10)) {
         const size_t slots = size_t(sms) * resident_ctas<rows_block_kernel<L, A, S, Op, VB, 4>>(kRowThreads);
         size_t grid = a.rows < slots ? a.rows : slots;
-        rows_block_kernel<L, A, S, Op, VB, 4><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
-            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin);
+        if (gy > 1) grid = std::max<size_t>(1, std::min(grid, slots / gy));
+        rows_block_kernel<L, A, S, Op, VB, 4><<<dim3((unsigned)grid, gy), kRowThreads, 0, l.stream>>>(
+            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, a.hi_in_stride, a.hi_out_stride);
         return cudaGetLastError();
     }
     const int G = pick_group(row_bytes);
@@ -269,19 +276,23 @@ static cudaError_t launch_rows_t(const RowsArgs& a, const Launch& l) {
     // At most four vectors per lane: one batch with the row's head and tail in the same round trip, no loop.  That
     // instantiation needs 72 registers (3 CTAs per SM instead of 4), so rows that are whole aligned vectors stay with
     // the loop kernel, which is better there ([262144, 1000] f32: 6.4 vs 5.9 TB/s, bf16 [8M, 64]: 6.5 vs 5.8).
-    const bool whole = row_bytes % 32 == 0 && (a.row_stride * sizeof(L)) % 32 == 0 && (reinterpret_cast<size_t>(a.in) & 31) == 0;
+    const bool whole = row_bytes % 32 == 0 && (a.row_stride * sizeof(L)) % 32 == 0 && (a.hi_in_stride * sizeof(L)) % 32 == 0 &&
+                       (reinterpret_cast<size_t>(a.in) & 31) == 0;
     const bool short_rows = row_bytes / 32 <= size_t(G) * 4 && !whole;
     const size_t cap = size_t(sms) * (short_rows ? resident_ctas<rows_group_kernel<L, A, S, Op, VB, 4, true>>(kRowThreads)
                                                  : resident_ctas<rows_group_kernel<L, A, S, Op, VB, 4, false>>(kRowThreads));   // one full wave
-    if (grid > cap) grid = cap;
+    if (gy > 1) {
+        const size_t per_slice = std::max<size_t>(1, cap / gy);          // (slices x CTAs) is about one wave
+        if (grid > per_slice) grid = per_slice;
+    } else if (grid > cap) grid = cap;
     else if (grid > size_t(sms)) grid = ((grid + sms - 1) / sms) * sms;   // whole CTAs per SM (see the kernel)
     if (grid == 0) grid = 1;
     if (short_rows)
-        rows_group_kernel<L, A, S, Op, VB, 4, true><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
-            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G);
+        rows_group_kernel<L, A, S, Op, VB, 4, true><<<dim3((unsigned)grid, gy), kRowThreads, 0, l.stream>>>(
+            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G, a.hi_in_stride, a.hi_out_stride);
     else
-        rows_group_kernel<L, A, S, Op, VB, 4, false><<<(unsigned)grid, kRowThreads, 0, l.stream>>>(
-            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G);
+        rows_group_kernel<L, A, S, Op, VB, 4, false><<<dim3((unsigned)grid, gy), kRowThreads, 0, l.stream>>>(
+            (const L*)a.in, (S*)a.out, a.rows, a.n, a.row_stride, a.out_stride, fin, G, a.hi_in_stride, a.hi_out_stride);
     return cudaGetLastError();
 }
 

@@ -770,3 +770,36 @@ def test_all_elements_of_padded_and_strided_views(dtype, cuda):
     out = torch.zeros((), dtype=tc.dtype, device=cuda)
     db.reduce('lambda a, b: a + b', v, out, axis=None, identity=0)
     _check(out.cpu().numpy().reshape(()), O.reduce(O.SUM, h, None, identity=0, wide=True), dtype, h, None, 'sum')
+
+
+@pytest.mark.parametrize('axes', [(0, ), (1, ), (2, ), (0, 1), (0, 2), (1, 2), (0, 1, 2)])
+@pytest.mark.parametrize('dtype', [np.float32, np.int64, np.int16])
+def test_windows_of_a_larger_3d_array(axes, dtype, cuda):
+    """[A, B, C] windows with a pitch on two levels (stencil interiors, sub-blocks): every axis combination; the ones
+    that fold the innermost axis run the row kernels on two levels of rows (RowsArgs::hi_*), directly or as the
+    first pass of the inner-first plan.  Sum and max, identity None, long and short innermost axes."""
+    rng = np.random.default_rng(sum(axes) + 7)
+    for full, win in (((60, 70, 900), (slice(2, 58), slice(3, 66), slice(5, 880))),
+                      ((300, 40, 64), (slice(0, 300), slice(0, 37), slice(0, 60))),
+                      ((5, 600, 4100), (slice(1, 5), slice(0, 590), slice(4, 4100)))):
+        base = _data(rng, list(full), dtype)
+        host = np.ascontiguousarray(base[win])
+        view = torch.from_numpy(base).to(cuda)[win]
+        for op in ('sum', 'max'):
+            got, ref = _run(host, axes, op, cuda)                 # the oracle on the contiguous copy
+            red, lam, _ = _OPS[op]
+            ident = _identity(op, dtype)
+            out = db.reduce(lam, view, axis=axes, identity=ident)
+            _check(out.cpu().numpy().reshape(ref.shape), ref, dtype, host, axes, op)
+        kept = [s for i, s in enumerate(host.shape) if i not in axes] or [1]
+        init = _data(rng, kept, dtype)
+        out = torch.from_numpy(init.copy()).to(cuda).reshape(kept if len(axes) < 3 else ())
+        db.reduce('lambda a, b: a + b', view, out, axis=axes, identity=None)
+        ref = O.reduce(O.SUM, host, axes, identity=None, out_init=init.reshape(out.shape if out.dim() else ()).copy(), wide=True) \
+            if False else None
+        want = host.astype(np.float64).sum(axes) + init.reshape(np.shape(host.astype(np.float64).sum(axes))).astype(np.float64)
+        if np.issubdtype(dtype, np.floating):
+            scale = np.abs(host.astype(np.float64)).sum(axes) + np.abs(init.astype(np.float64)).reshape(want.shape)
+            assert np.all(np.abs(out.cpu().numpy().astype(np.float64).reshape(want.shape) - want) <= RTOL_F32 * np.maximum(scale, 1e-30))
+        else:
+            np.testing.assert_array_equal(out.cpu().numpy().reshape(want.shape), want.astype(dtype))

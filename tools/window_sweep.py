@@ -1,0 +1,29 @@
+"""Reductions over WINDOWS of a larger 3-D array (padding on two levels: [1024, 512, 512] f32, window
+[:, :500, :500] = 0.95 of the bytes): every axis combination, GB/s of the useful bytes."""
+import os, sys, itertools, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import dace_b200 as db
+dev = torch.device('cuda:0')
+ADD = 'lambda a, b: a + b'
+base = torch.rand(1024, 512, 512, device=dev)
+views = {'window [:, :500, :500]': base[:, :500, :500], 'window [3:1000, 7:, :500]': base[3:1000, 7:, :500],
+         'window [:, :500, :] (one padded level)': base[:, :500, :]}
+print('%-42s %-10s %9s %9s' % ('view', 'axes', 'ms', 'GB/s'))
+for vname, x in views.items():
+    for r in (1, 2, 3):
+        for axes in itertools.combinations(range(3), r):
+            try:
+                out = db.reduce(ADD, x, axis=axes, identity=0)
+                ref = x.double().sum(axes)
+                ok = torch.allclose(out.double().reshape(ref.shape), ref, rtol=1e-4)
+                db.reduce(ADD, x, out, axis=axes, identity=0)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(3): db.reduce(ADD, x, out, axis=axes, identity=0)
+                e1.record(); torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / 3
+                gbs = x.numel() * 4 / ms / 1e6
+                print('%-42s %-10s %9.3f %9.0f %s%s' % (vname, axes, ms, gbs, '' if ok else 'MISMATCH', '   <--' if gbs < 3000 else ''), flush=True)
+            except Exception as ex:
+                print('%-42s %-10s %s' % (vname, axes, str(ex)[:80]), flush=True)
