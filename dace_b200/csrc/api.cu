@@ -389,7 +389,14 @@ static cudaError_t plan_inner_first(int red, int dtin, int dtout, const void* in
     // ... or there are exactly two of them and the innermost axis is the folded one: rows on two levels (windows of a
     // larger 3-D array: every axis combination that folds the innermost axis ended in the strided kernel - all
     // elements of a [1024, 500, 500] window of a [1024, 512, 512] array with one warp, 1.35 s)
-    const bool two_level = !dense && j == 2 && nc == 3 && c[0].in_stride >= 0 && c[0].shape <= 65535;
+    // (more outer axes are fine as long as they fall into two dense groups: [N, C, H, W] interiors folded over
+    // (0, 2, 3) have N and C dense and a pitch after H)
+    int brk = -1, nbrk = 0;
+    for (int i = 0; i + 1 < j; ++i)
+        if (c[i].in_stride != c[i + 1].in_stride * c[i + 1].shape) { brk = i; ++nbrk; }
+    size_t hi_count = 1, lo_count = 1;
+    for (int i = 0; i < j; ++i) (i <= brk ? hi_count : lo_count) *= (size_t)c[i].shape;
+    const bool two_level = !dense && nbrk == 1 && j == nc - 1 && c[brk].in_stride >= 0 && hi_count <= 65535;
     if (!dense && !two_level) return cudaErrorNotSupported;
     if (c[j - 1].in_stride < 0) return cudaErrorNotSupported;
     const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
@@ -410,8 +417,8 @@ static cudaError_t plan_inner_first(int red, int dtin, int dtout, const void* in
         ColsArgs a{in, mid, O, R, K, (size_t)c[j - 1].in_stride, (size_t)c[j].in_stride, (ptrdiff_t)K, 1, neutral};
         e = plan_cols(red, dtin, dtmid, a, l);
     } else if (two_level) {
-        e = plan_rows(red, dtin, dtmid, in, mid, (size_t)c[1].shape, R, (size_t)c[1].in_stride, 1, neutral, l,
-                      (size_t)c[0].shape, (size_t)c[0].in_stride, (ptrdiff_t)c[1].shape);
+        e = plan_rows(red, dtin, dtmid, in, mid, lo_count, R, (size_t)c[j - 1].in_stride, 1, neutral, l,
+                      hi_count, (size_t)c[brk].in_stride, (ptrdiff_t)lo_count);
     } else {
         e = plan_rows(red, dtin, dtmid, in, mid, O, R, (size_t)c[j - 1].in_stride, 1, neutral, l);
     }

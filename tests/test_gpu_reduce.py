@@ -803,3 +803,20 @@ def test_windows_of_a_larger_3d_array(axes, dtype, cuda):
             assert np.all(np.abs(out.cpu().numpy().astype(np.float64).reshape(want.shape) - want) <= RTOL_F32 * np.maximum(scale, 1e-30))
         else:
             np.testing.assert_array_equal(out.cpu().numpy().reshape(want.shape), want.astype(dtype))
+
+
+@pytest.mark.parametrize('axes', [(2, 3), (0, 2, 3), (3, ), (1, 2, 3), (0, 1, 2, 3), (0, 1), (1, ), (0, 3)])
+@pytest.mark.parametrize('dtype', [np.float32, np.int32])
+def test_interior_of_a_4d_array(axes, dtype, cuda):
+    """[N, C, H, W] interiors `A[:, :, 1:-1, 1:-1]` (per-image, per-channel and global statistics of a stencil
+    domain): N and C stay dense, a pitch after every row and after every image plane."""
+    rng = np.random.default_rng(len(axes) * 3 + axes[0])
+    base = _data(rng, [6, 10, 70, 300], dtype)
+    host = np.ascontiguousarray(base[:, :, 1:-1, 1:-1])
+    view = torch.from_numpy(base).to(cuda)[:, :, 1:-1, 1:-1]
+    for op in ('sum', 'min'):
+        red, lam, _ = _OPS[op]
+        ident = _identity(op, dtype)
+        out = db.reduce(lam, view, axis=axes, identity=ident)
+        ref = O.reduce(red, host, axes, identity=ident, wide=True)
+        _check(out.cpu().numpy().reshape(ref.shape), ref, dtype, host, axes, op)

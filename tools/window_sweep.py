@@ -8,10 +8,14 @@ ADD = 'lambda a, b: a + b'
 base = torch.rand(1024, 512, 512, device=dev)
 views = {'window [:, :500, :500]': base[:, :500, :500], 'window [3:1000, 7:, :500]': base[3:1000, 7:, :500],
          'window [:, :500, :] (one padded level)': base[:, :500, :]}
+base4 = base.view(32, 32, 512, 512)
+views4 = {'4-D interior [:, :, 1:-1, 1:-1]': base4[:, :, 1:-1, 1:-1]}
 print('%-42s %-10s %9s %9s' % ('view', 'axes', 'ms', 'GB/s'))
-for vname, x in views.items():
-    for r in (1, 2, 3):
-        for axes in itertools.combinations(range(3), r):
+ALL = [(vn, x, axes) for vn, x in views.items() for r in (1, 2, 3) for axes in itertools.combinations(range(3), r)]
+ALL += [(vn, x, axes) for vn, x in views4.items() for axes in ((2, 3), (0, 2, 3), (3, ), (1, 2, 3), (0, 1, 2, 3), (0, 1), (1, ))]
+for vname, x, axes in ALL:
+    if True:
+        if True:
             try:
                 out = db.reduce(ADD, x, axis=axes, identity=0)
                 ref = x.double().sum(axes)
