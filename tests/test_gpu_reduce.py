@@ -820,3 +820,19 @@ def test_interior_of_a_4d_array(axes, dtype, cuda):
         out = db.reduce(lam, view, axis=axes, identity=ident)
         ref = O.reduce(red, host, axes, identity=ident, wide=True)
         _check(out.cpu().numpy().reshape(ref.shape), ref, dtype, host, axes, op)
+
+
+@pytest.mark.parametrize('axes', [(0, ), (1, ), None])
+def test_broadcast_views_stride_zero(axes, cuda):
+    """Inputs with a zero stride (a row or a column broadcast over the other axis, `expand`): every element is
+    counted as often as the view shows it."""
+    g = torch.Generator(device='cuda').manual_seed(4)
+    row = torch.randint(-20, 20, (1, 3000), device=cuda, dtype=torch.int32, generator=g)
+    col = torch.randint(-20, 20, (2500, 1), device=cuda, dtype=torch.int32, generator=g)
+    for x in (row.expand(2500, 3000), col.expand(2500, 3000), row.expand(2500, 3000)[::2, 5:2999]):
+        ref = x.contiguous().sum(axes, dtype=torch.int32) if axes is not None else x.contiguous().sum(dtype=torch.int32)
+        out = db.reduce('lambda a, b: a + b', x, axis=axes, identity=0)
+        assert torch.equal(out.reshape(ref.shape), ref)
+        mref = x.contiguous().amax(axes) if axes is not None else x.contiguous().max()
+        out = db.reduce('lambda a, b: max(a, b)', x, axis=axes, identity=-1000)
+        assert torch.equal(out.reshape(mref.shape), mref)
