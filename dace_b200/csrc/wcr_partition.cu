@@ -100,7 +100,9 @@ __device__ __forceinline__ void group_sync(unsigned g) {
     asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kGroupThreads) : "memory");
 }
 
-template <class V, class W>
+// KW: 32-bit words per key (1: int32 / uint32 keys, 2: int64 keys - DaCe's default index type; the high word must
+// be zero for a key to be in range, the partition itself moves 32-bit keys either way).
+template <class V, class W, int KW>
 __global__ void __launch_bounds__(kPartThreads, 1)
 scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restrict__ bins, unsigned nbins, V cval, W scale,
                          unsigned* buf, unsigned* gcur, size_t chunk, unsigned cap, int B, int S, int aligned,
@@ -142,24 +144,28 @@ scatter_partition_kernel(const unsigned* __restrict__ keys, size_t n, W* __restr
         const unsigned ntiles = unsigned((chunk_n + kTileKeys - 1) / kTileKeys);
         unsigned* bufc = buf + size_t(c & 1) * size_t(B) * cap;
         unsigned* cur = gcur + c * size_t(B);
-        const unsigned* ck = keys + chunk_lo;
+        const unsigned* ck = keys + chunk_lo * KW;
 
         unsigned knext[kKeysPerThread];
         auto load_tile = [&](unsigned t, unsigned (&k)[kKeysPerThread]) {
             const size_t base = size_t(t) * kTileKeys;
             if (aligned && base + kTileKeys <= chunk_n) {
+                constexpr int kPerLoad = 4 / KW;                        // keys per 16-byte load
 #pragma unroll
-                for (int u = 0; u < kKeysPerThread / 4; ++u) {
-                    const unsigned* src = ck + base + (size_t(gtid) + size_t(u) * kGroupThreads) * 4;
+                for (int u = 0; u < kKeysPerThread / kPerLoad; ++u) {
+                    const unsigned* src = ck + (base + (size_t(gtid) + size_t(u) * kGroupThreads) * kPerLoad) * KW;
                     Words<16> w = keys_first ? ldg_policy16(src, pol_first) : ldg_stream16(src);
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) k[u * 4 + j] = w.w[j];
+                    for (int j = 0; j < kPerLoad; ++j)
+                        k[u * kPerLoad + j] = (KW == 1 || w.w[j * KW + KW - 1] == 0u) ? w.w[j * KW] : 0xffffffffu;
                 }
             } else {
 #pragma unroll
                 for (int j = 0; j < kKeysPerThread; ++j) {
                     const size_t i = base + gtid + size_t(j) * kGroupThreads;
-                    k[j] = i < chunk_n ? __ldg(ck + i) : 0xffffffffu;   // 0xffffffff is never a valid bin
+                    unsigned key = 0xffffffffu;                         // 0xffffffff is never a valid bin
+                    if (i < chunk_n && (KW == 1 || __ldg(ck + i * KW + KW - 1) == 0u)) key = __ldg(ck + i * KW);
+                    k[j] = key;
                 }
             }
         };
@@ -328,7 +334,7 @@ constexpr int kSampleKeys = 4096;
 constexpr int kSampleSlots = 8192;
 
 __global__ void __launch_bounds__(1024) scatter_sample_kernel(const unsigned* __restrict__ keys, size_t n, unsigned nbins,
-                                                              int* flag) {
+                                                              int* flag, int kw) {
     __shared__ unsigned table[kSampleSlots];
     __shared__ unsigned dups;
     for (int i = threadIdx.x; i < kSampleSlots; i += 1024) table[i] = 0xffffffffu;
@@ -340,9 +346,10 @@ __global__ void __launch_bounds__(1024) scatter_sample_kernel(const unsigned* __
 #pragma unroll
     for (int j = 0; j < kSampleKeys / 1024; ++j) {
         const size_t p = (size_t(j) * 1024 + threadIdx.x) * stride;
-        const unsigned k = __ldg(keys + p);
-        if (j == 0) equal = k == __ldg(keys + p + 1);
-        if (k >= nbins) continue;
+        const unsigned k = __ldg(keys + p * kw);
+        const unsigned hi = kw == 2 ? __ldg(keys + p * kw + 1) : 0u;
+        if (j == 0) equal = k == __ldg(keys + (p + 1) * kw) && (kw == 1 || hi == __ldg(keys + (p + 1) * kw + 1));
+        if (k >= nbins || hi != 0u) continue;
         unsigned slot = (k * 2654435761u) >> 19;          // top 13 bits
         for (int probe = 0; probe < 16; ++probe) {
             const unsigned old = atomicCAS(&table[slot], 0xffffffffu, k);
@@ -378,7 +385,7 @@ struct PartPlan {
 
 static bool part_plan(int dtidx, int dtval, bool has_values, size_t n, size_t nbins, PartPlan& p) {
     if (has_values) return false;
-    if (dtidx != DT_I32 && dtidx != DT_U32) return false;
+    if (dtidx != DT_I32 && dtidx != DT_U32 && dtidx != DT_I64) return false;
     if (dtval != DT_I32 && dtval != DT_U32 && dtval != DT_F32 && dtval != DT_I64 && dtval != DT_U64 && dtval != DT_F64)
         return false;
     if (n < (size_t(1) << 22)) return false;
@@ -426,7 +433,8 @@ cudaError_t launch_scatter_sample(int dtidx, int dtval, const ScatterArgs& a, co
     if (a.values == nullptr || !valued_selection_applies(dtidx, dtval, a.n, a.nbins)) return cudaErrorNotSupported;
     if (l.extra == nullptr || l.extra_bytes < 256 || (reinterpret_cast<size_t>(l.extra) & 15) != 0) return cudaErrorNotSupported;
     int* flag = reinterpret_cast<int*>(l.extra);
-    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(reinterpret_cast<const unsigned*>(a.idx), a.n, unsigned(a.nbins), flag);
+    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(reinterpret_cast<const unsigned*>(a.idx), a.n, unsigned(a.nbins), flag,
+                                                    dtidx == DT_I64 ? 2 : 1);
     *gate = flag;
     return cudaGetLastError();
 }
@@ -444,14 +452,15 @@ static bool partition_supported(size_t smem) {
         if (coop) {
             const int sm = (int)smem;
             const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
-            if (cudaFuncSetAttribute(scatter_partition_kernel<int, int>, at, sm) != cudaSuccess ||
-                cudaFuncSetAttribute(scatter_partition_kernel<unsigned, unsigned>, at, sm) != cudaSuccess ||
-                cudaFuncSetAttribute(scatter_partition_kernel<float, float>, at, sm) != cudaSuccess ||
-                cudaFuncSetAttribute(scatter_partition_kernel<unsigned, long long>, at, sm) != cudaSuccess ||
-                cudaFuncSetAttribute(scatter_partition_kernel<unsigned, unsigned long long>, at, sm) != cudaSuccess ||
-                cudaFuncSetAttribute(scatter_partition_kernel<unsigned, double>, at, sm) != cudaSuccess)
+            auto set = [&](auto kernel) { return cudaFuncSetAttribute(kernel, at, sm) == cudaSuccess; };
+            if (!set(scatter_partition_kernel<int, int, 1>) || !set(scatter_partition_kernel<unsigned, unsigned, 1>) ||
+                !set(scatter_partition_kernel<float, float, 1>) || !set(scatter_partition_kernel<unsigned, long long, 1>) ||
+                !set(scatter_partition_kernel<unsigned, unsigned long long, 1>) || !set(scatter_partition_kernel<unsigned, double, 1>) ||
+                !set(scatter_partition_kernel<int, int, 2>) || !set(scatter_partition_kernel<unsigned, unsigned, 2>) ||
+                !set(scatter_partition_kernel<float, float, 2>) || !set(scatter_partition_kernel<unsigned, long long, 2>) ||
+                !set(scatter_partition_kernel<unsigned, unsigned long long, 2>) || !set(scatter_partition_kernel<unsigned, double, 2>))
                 coop = 0;
-            else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scatter_partition_kernel<int, int>, kPartThreads, smem) != cudaSuccess || occ < 1)
+            else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scatter_partition_kernel<int, int, 2>, kPartThreads, smem) != cudaSuccess || occ < 1)
                 coop = 0;
         }
         cudaGetLastError();
@@ -460,9 +469,9 @@ static bool partition_supported(size_t smem) {
     return g_part_coop[dev] == 1;
 }
 
-template <class V, class W>
-static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, W scale, const PartPlan& p, const Launch& l,
-                                        const int** gate_out) {
+template <class V, class W, int KW>
+static cudaError_t launch_partitioned_kw(const ScatterArgs& a, V cval, W scale, const PartPlan& p, const Launch& l,
+                                         const int** gate_out) {
     unsigned char* base = static_cast<unsigned char*>(l.extra);
     int* flag = reinterpret_cast<int*>(base);
     unsigned* gcur = reinterpret_cast<unsigned*>(base + p.gcur_off);
@@ -471,7 +480,7 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, W scale, c
     if (e != cudaSuccess) return e;
     const unsigned* keys = reinterpret_cast<const unsigned*>(a.idx);
     size_t n = a.n;
-    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(keys, n, unsigned(a.nbins), flag);
+    scatter_sample_kernel<<<1, 1024, 0, l.stream>>>(keys, n, unsigned(a.nbins), flag, KW);
     const int* gate = flag;
     *gate_out = gate;
     W* bins = reinterpret_cast<W*>(a.bins);
@@ -484,10 +493,17 @@ static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, W scale, c
     int hint = tuning().part_hint >= 0 ? tuning().part_hint : kHintDefault;
     int bits_arg = p.bits;
     void* args[] = {&keys, &n, &bins, &nbins, &cval, &scale, &buf, &gcur, &chunk_arg, &cap_arg, &B_arg, &S_arg, &aligned, &gate, &divert, &hint, &bits_arg};
-    e = cudaLaunchCooperativeKernel((void*)scatter_partition_kernel<V, W>, dim3(sm_count()), dim3(kPartThreads), args,
+    e = cudaLaunchCooperativeKernel((void*)scatter_partition_kernel<V, W, KW>, dim3(sm_count()), dim3(kPartThreads), args,
                                     p.smem, l.stream);
     if (e != cudaSuccess) { cudaGetLastError(); return cudaErrorNotSupported; }
     return cudaSuccess;
+}
+
+template <class V, class W>
+static cudaError_t launch_partitioned_t(const ScatterArgs& a, V cval, W scale, const PartPlan& p, const Launch& l,
+                                        const int** gate_out, bool keys64) {
+    return keys64 ? launch_partitioned_kw<V, W, 2>(a, cval, scale, p, l, gate_out)
+                  : launch_partitioned_kw<V, W, 1>(a, cval, scale, p, l, gate_out);
 }
 
 // Returns cudaErrorNotSupported when the partitioned path does not apply or the caller's scratch is too
@@ -498,14 +514,15 @@ cudaError_t launch_scatter_partitioned(int dtidx, int dtval, const ScatterArgs& 
     if (l.extra == nullptr || l.extra_bytes < p.total || (reinterpret_cast<size_t>(l.extra) & 15) != 0)
         return cudaErrorNotSupported;
     if (!partition_supported(p.smem)) return cudaErrorNotSupported;
+    const bool k64 = dtidx == DT_I64;
     switch (dtval) {
-        case DT_I32: { int c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<int, int>(a, c, 1, p, l, gate); }
-        case DT_U32: { unsigned c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<unsigned, unsigned>(a, c, 1u, p, l, gate); }
-        case DT_F32: { float c = 1.f; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<float, float>(a, c, 1.f, p, l, gate); }
+        case DT_I32: { int c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<int, int>(a, c, 1, p, l, gate, k64); }
+        case DT_U32: { unsigned c = 1; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<unsigned, unsigned>(a, c, 1u, p, l, gate, k64); }
+        case DT_F32: { float c = 1.f; if (a.const_value) memcpy(&c, a.const_value, 4); return launch_partitioned_t<float, float>(a, c, 1.f, p, l, gate, k64); }
         // 64-bit bins: occurrences are counted in 32-bit tables, the counts scaled by the increment at the flush
-        case DT_I64: { long long c = 1; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, long long>(a, 1u, c, p, l, gate); }
-        case DT_U64: { unsigned long long c = 1; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, unsigned long long>(a, 1u, c, p, l, gate); }
-        case DT_F64: { double c = 1.0; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, double>(a, 1u, c, p, l, gate); }
+        case DT_I64: { long long c = 1; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, long long>(a, 1u, c, p, l, gate, k64); }
+        case DT_U64: { unsigned long long c = 1; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, unsigned long long>(a, 1u, c, p, l, gate, k64); }
+        case DT_F64: { double c = 1.0; if (a.const_value) memcpy(&c, a.const_value, 8); return launch_partitioned_t<unsigned, double>(a, 1u, c, p, l, gate, k64); }
         default: return cudaErrorNotSupported;
     }
 }

@@ -506,6 +506,14 @@ cudaError_t launch_scatter(int red, int dtidx, int dtval, const ScatterArgs& a, 
             ScatterArgs g = a;
             g.gate = gate;
             g.gate_run_if = 1;
+            if (dtidx == DT_I64) {
+                // 64-bit keys: the hot-key cache takes 32-bit keys, so skewed keys (flag 2) go to the warp-merging
+                // global kernel as well
+                e = launch_scatter_val<long long>(red, dtval, g, l);
+                if (e != cudaSuccess) return e;
+                g.gate_run_if = 2;
+                return launch_scatter_val<long long>(red, dtval, g, l);
+            }
             e = (dtidx == DT_I32) ? launch_scatter_val<int>(red, dtval, g, l) : launch_scatter_val<unsigned>(red, dtval, g, l);
             if (e != cudaSuccess) return e;
             g.gate_run_if = 2;

@@ -336,3 +336,34 @@ def test_privatised_min_max_small_bins(nbins, op, npop, cuda):
         touched[keys[ok]] = True
         want[touched] = npop(want[touched], const[0])
         np.testing.assert_array_equal(bins.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize('nbins', [65536, 300001, 1 << 20])
+@pytest.mark.parametrize('dist', ['uniform', 'zipf', 'equal', 'sorted'])
+def test_partitioned_histogram_int64_keys(nbins, dist, cuda):
+    """int64 keys (DaCe's default index type) through the radix partition: a key is in range only if its high word
+    is zero - negative keys and keys >= 2^32 whose LOW word happens to be a valid bin are dropped."""
+    rng = np.random.default_rng(nbins % 89)
+    n = (1 << 23) + 4321
+    if dist == 'uniform':
+        keys = rng.integers(-3, nbins + 3, n)
+        keys[::1001] += 1 << 32                          # low word in range, high word not
+        keys[5::2003] = -keys[5::2003] - 1
+    elif dist == 'zipf':
+        keys = np.minimum(rng.zipf(1.2, n) - 1, nbins - 1)
+    elif dist == 'equal':
+        keys = np.full(n, nbins - 1)
+    else:
+        keys = np.sort(rng.integers(0, nbins, n))
+    keys = keys.astype(np.int64)
+    ok = keys[(keys >= 0) & (keys < nbins)]
+    for dt, tdt in ((np.int32, torch.int32), (np.int64, torch.int64)):
+        start = rng.integers(0, 5, nbins).astype(dt)
+        bins = torch.from_numpy(start.copy()).to(cuda)
+        db.wcr_scatter('lambda a, b: a + b', bins, torch.from_numpy(keys).to(cuda))
+        np.testing.assert_array_equal(bins.cpu().numpy(), start + np.bincount(ok, minlength=nbins).astype(dt))
+    # a key pointer 8 bytes off a 16-byte boundary: the scalar loads
+    tk = torch.from_numpy(np.concatenate([keys[:1], keys])).to(cuda)[1:]
+    bins = torch.zeros(nbins, dtype=torch.int32, device=cuda)
+    db.wcr_scatter('lambda a, b: a + b', bins, tk)
+    np.testing.assert_array_equal(bins.cpu().numpy(), np.bincount(ok, minlength=nbins).astype(np.int32))
