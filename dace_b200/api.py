@@ -244,19 +244,30 @@ def _arg_reduce(red: int, in_array: torch.Tensor, axis, out_idx, out_val, init, 
         a = a.reshape(-1)      # a view when possible, like the frontend's flat() (reduction.py:281-283)
         axis = 0
     axis = _normalize_axes(axis, a.dim())[0]
-    if not a.is_contiguous():
-        # any [outer, reduced, inner] factorisation needs mergeable leading / trailing dims
-        lead, trail = a.shape[:axis], a.shape[axis + 1:]
-        ok = all(a.stride(i) == a.stride(i + 1) * a.shape[i + 1] for i in range(axis - 1)) and \
-            all(a.stride(i) == a.stride(i + 1) * a.shape[i + 1] for i in range(axis + 1, a.dim() - 1))
-        if not ok:
-            raise NotImplementedError('argmin/argmax: leading and trailing dimensions must each be mergeable')
-    outer = int(np.prod(a.shape[:axis], dtype=np.int64))
-    inner = int(np.prod(a.shape[axis + 1:], dtype=np.int64))
+    # [outer, reduced, inner] with one stride each: the kept axes, in order, must merge into at most two dense groups
+    # (contiguous arrays: leading and trailing axes; windows of larger arrays: e.g. [A, B, C] with a pitch after
+    # every row and every slice, reduced over C -> outer = A, inner = B)
+    groups = []
+    for i in [d for d in range(a.dim()) if d != axis]:
+        if a.shape[i] == 1:
+            continue
+        if groups and groups[-1][2] == i - 1 and i - 1 != axis and groups[-1][1] == a.stride(i) * a.shape[i]:
+            groups[-1] = (groups[-1][0] * a.shape[i], a.stride(i), i)
+        else:
+            groups.append((a.shape[i], a.stride(i), i))
+    if len(groups) > 2:
+        raise NotImplementedError('argmin/argmax: the kept dimensions must merge into at most two dense groups')
     reduced = a.shape[axis]
-    so = a.stride(axis - 1) if axis > 0 else 0
-    si = a.stride(a.dim() - 1) if axis < a.dim() - 1 else 1
     sr = a.stride(axis)
+    if len(groups) == 2:
+        (outer, so, _), (inner, si, _) = groups
+    elif len(groups) == 1 and groups[0][2] > axis:
+        outer, so, (inner, si, _) = 1, 0, groups[0]
+    elif len(groups) == 1:
+        (outer, so, _), inner, si = groups[0], 1, 1
+    else:
+        outer, so, inner, si = 1, 0, 1, 1
+    outer, inner = int(outer), int(inner)
     kept = tuple(a.shape[:axis]) + tuple(a.shape[axis + 1:])
     created = out_idx is None
     if created:

@@ -165,3 +165,19 @@ def test_arg_full_size_properties():
     assert int(i1) == pos[0] and int(i2) == pos[0] and float(val) == 2.0
     t[5] = -1.0
     assert int(db.argmin(t)) == 5
+
+
+def test_arg_over_windows_of_larger_arrays():
+    """Kept axes that merge into two dense groups: 3-D windows folded over their last / first / middle axis, the
+    interior of a 4-D array over its last axis; three groups are refused."""
+    g = torch.Generator(device='cuda').manual_seed(11)
+    base = torch.rand(60, 70, 900, device='cuda', generator=g)
+    w = base[2:58, 3:66, 5:880]
+    for axis in (0, 1, 2):
+        assert torch.equal(db.argmax(w, axis=axis).long(), w.argmax(dim=axis))
+        assert torch.equal(db.argmin(w, axis=axis).long(), w.argmin(dim=axis))
+    b4 = torch.rand(6, 10, 70, 300, device='cuda', generator=g)[:, :, 1:-1, 1:-1]
+    assert torch.equal(db.argmax(b4, axis=3).long(), b4.argmax(dim=3))
+    assert torch.equal(db.argmax(b4, axis=2).long(), b4.argmax(dim=2))
+    with pytest.raises(NotImplementedError):
+        db.argmax(b4, axis=0)
