@@ -19,7 +19,7 @@ import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '_built')
-VERSION = 22
+VERSION = 23
 
 
 def up_to_date() -> bool:
@@ -46,6 +46,7 @@ def _programs(dace):
     add, mx = 'lambda a, b: a + b', 'lambda a, b: max(a, b)'
     progs = []
     N, M = dace.symbol('N', dace.int64), dace.symbol('M', dace.int64)
+    K = dace.symbol('K', dace.int64)
 
     # (1) Unmodified @dace.program; the backend is chosen only through the registry default.
     E.Reduce.default_implementation = 'B200'
@@ -99,6 +100,24 @@ def _programs(dace):
     sdfg.apply_gpu_transformations()
     E.use_b200_reductions(sdfg)
     progs.append(sdfg)
+
+    # (3b) Interiors of larger arrays (stencil domains): every element of A[1:N-1, 1:M-1] and per-plane sums of
+    #      V[:, 1:H-1, 1:W-1] - all-reduced / innermost-reduced windows with a pitch on one and two levels, which take
+    #      the inner-first plan and the row kernels on two levels of rows.
+    @dace.program
+    def b200_interior_sum(A: dace.float64[N, M], s: dace.float64[1]):
+        s[0] = np.sum(A[1:N - 1, 1:M - 1])
+
+    @dace.program
+    def b200_interior_plane_sums(V: dace.float32[K, N, M], s: dace.float32[K], t: dace.float32[K, N - 2]):
+        s[:] = np.sum(V[:, 1:N - 1, 1:M - 1], axis=(1, 2))
+        t[:] = np.max(V[:, 1:N - 1, 1:M - 1], axis=2)
+
+    for p in (b200_interior_sum, b200_interior_plane_sums):
+        sdfg = _to_sdfg(p, simplify=True)
+        sdfg.apply_gpu_transformations()
+        E.use_b200_reductions(sdfg)
+        progs.append(sdfg)
 
     # (4) Device-resident arrays (GPU_Global): no copies in the generated program.
     sdfg = dace.SDFG('b200_full_sum_f32_resident')

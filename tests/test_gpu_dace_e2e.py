@@ -322,6 +322,24 @@ def test_np_argmax_argmin_dace_programs(cuda):
     np.testing.assert_array_equal(outb, np.argmax(big, axis=1))
 
 
+def test_interiors_of_larger_arrays(cuda):
+    """np.sum over A[1:-1, 1:-1] and per-plane sum / row max over V[:, 1:-1, 1:-1]: Reduce nodes whose input memlets
+    are windows (a pitch on one and on two levels); large enough that the one-warp strided kernel these shapes used
+    to end in would take seconds."""
+    rng = np.random.default_rng(5)
+    a = rng.standard_normal((3000, 4100))
+    s = np.zeros(1)
+    prog('b200_interior_sum')(A=a, s=s, N=3000, M=4100)
+    np.testing.assert_allclose(s[0], a[1:-1, 1:-1].sum(), rtol=1e-11)
+    v = rng.standard_normal((40, 300, 500)).astype(np.float32)
+    ps = np.zeros(40, np.float32)
+    rm = np.zeros((40, 298), np.float32)
+    prog('b200_interior_plane_sums')(V=v, s=ps, t=rm, K=40, N=300, M=500)
+    w = v[:, 1:-1, 1:-1].astype(np.float64)
+    assert np.all(np.abs(ps - w.sum((1, 2))) <= 1e-5 * np.abs(w).sum((1, 2)))
+    np.testing.assert_array_equal(rm, v[:, 1:-1, 1:-1].max(2))
+
+
 def test_np_argmax_over_all_elements(cuda):
     """np.argmax(A) / np.argmin(A) without an axis: flat index of the first extreme element (NumPy's rule and the
     reference frontend's sequential order); the reference itself cannot put these programs on a GPU."""
