@@ -655,6 +655,113 @@ static cudaError_t launch_cols_small(const ColsArgs& a, const Launch& l) {
     return cudaGetLastError();
 }
 
+// A short reduced axis between MANY outer slices ([N, 3, M] channel folds, [1M, 4, 64]): a thread owns one output
+// (o, c) - adjacent threads adjacent columns - and folds its R <= 64 values itself, two outputs and four rows at a
+// time in flight.  The general kernel launches a CTA per (slice, 256 columns) for R rows each ([1M, 4, 64] f32:
+// 0.48 TB/s, [4096, 4, 16384]: 1.9), the few-rows kernel above wants one huge inner axis.
+template <class L, class A, class S, class Op>
+__global__ void __launch_bounds__(kFewThreads)
+cols_short_axis_kernel(const L* __restrict__ in, S* __restrict__ out, size_t outer, size_t reduced, size_t inner,
+                       size_t in_stride_o, size_t in_stride_r, ptrdiff_t out_stride_o, ptrdiff_t out_stride_i, Finish<A> fin) {
+    const size_t total = outer * inner;
+    const size_t nthr = size_t(gridDim.x) * kFewThreads;
+    for (size_t t0 = size_t(blockIdx.x) * kFewThreads + threadIdx.x; t0 < total; t0 += 2 * nthr) {
+        const size_t t1 = t0 + nthr;
+        const bool two = t1 < total;
+        const size_t o0 = t0 / inner, c0 = t0 - o0 * inner;
+        const size_t o1 = two ? t1 / inner : o0, c1 = two ? t1 - o1 * inner : c0;
+        const L* p0 = in + o0 * in_stride_o + c0;
+        const L* p1 = in + o1 * in_stride_o + c1;
+        A a0 = Op::neutral(), a1 = Op::neutral();
+        size_t r = 0;
+        for (; r + 4 <= reduced; r += 4, p0 += 4 * in_stride_r, p1 += 4 * in_stride_r) {
+            A v0[4], v1[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { v0[q] = to_acc<A, L>(ldg_scalar(p0 + q * in_stride_r)); v1[q] = to_acc<A, L>(ldg_scalar(p1 + q * in_stride_r)); }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { a0 = Op::apply(a0, v0[q]); a1 = Op::apply(a1, v1[q]); }
+        }
+        for (; r < reduced; ++r, p0 += in_stride_r, p1 += in_stride_r) {
+            a0 = Op::apply(a0, to_acc<A, L>(ldg_scalar(p0)));
+            a1 = Op::apply(a1, to_acc<A, L>(ldg_scalar(p1)));
+        }
+        write_result<Op, A, S>(out + ptrdiff_t(o0) * out_stride_o + ptrdiff_t(c0) * out_stride_i, a0, fin);
+        if (two) write_result<Op, A, S>(out + ptrdiff_t(o1) * out_stride_o + ptrdiff_t(c1) * out_stride_i, a1, fin);
+    }
+}
+
+// The same with NV adjacent outputs per thread (one 16-byte load per row): R = 3 or 4 rows of scalar loads left a
+// thread with 32 bytes in flight ([4096, 4, 16384] f32: 3.6 TB/s).
+template <class L, class A, class S, class Op, int NV>
+__global__ void __launch_bounds__(kFewThreads)
+cols_short_axis_vec_kernel(const L* __restrict__ in, S* __restrict__ out, size_t outer, size_t reduced, size_t inner,
+                           size_t in_stride_o, size_t in_stride_r, ptrdiff_t out_stride_o, ptrdiff_t out_stride_i, Finish<A> fin) {
+    const size_t innerv = inner / NV, total = outer * innerv;
+    const size_t nthr = size_t(gridDim.x) * kFewThreads;
+    for (size_t t0 = size_t(blockIdx.x) * kFewThreads + threadIdx.x; t0 < total; t0 += 2 * nthr) {
+        const size_t t1 = t0 + nthr;
+        const bool two = t1 < total;
+        const size_t o0 = t0 / innerv, c0 = (t0 - o0 * innerv) * NV;
+        const size_t o1 = two ? t1 / innerv : o0, c1 = two ? (t1 - o1 * innerv) * NV : c0;
+        const L* p0 = in + o0 * in_stride_o + c0;
+        const L* p1 = in + o1 * in_stride_o + c1;
+        A a0[NV], a1[NV];
+#pragma unroll
+        for (int j = 0; j < NV; ++j) { a0[j] = Op::neutral(); a1[j] = Op::neutral(); }
+        size_t r = 0;
+        for (; r + 4 <= reduced; r += 4, p0 += 4 * in_stride_r, p1 += 4 * in_stride_r) {
+            A v0[4][NV], v1[4][NV];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { load_cols<L, A, NV>(p0 + q * in_stride_r, v0[q]); load_cols<L, A, NV>(p1 + q * in_stride_r, v1[q]); }
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int j = 0; j < NV; ++j) { a0[j] = Op::apply(a0[j], v0[q][j]); a1[j] = Op::apply(a1[j], v1[q][j]); }
+        }
+        for (; r < reduced; ++r, p0 += in_stride_r, p1 += in_stride_r) {
+            A v0[NV], v1[NV];
+            load_cols<L, A, NV>(p0, v0);
+            load_cols<L, A, NV>(p1, v1);
+#pragma unroll
+            for (int j = 0; j < NV; ++j) { a0[j] = Op::apply(a0[j], v0[j]); a1[j] = Op::apply(a1[j], v1[j]); }
+        }
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            write_result<Op, A, S>(out + ptrdiff_t(o0) * out_stride_o + ptrdiff_t(c0 + j) * out_stride_i, a0[j], fin);
+            if (two) write_result<Op, A, S>(out + ptrdiff_t(o1) * out_stride_o + ptrdiff_t(c1 + j) * out_stride_i, a1[j], fin);
+        }
+    }
+}
+
+template <class T, class Op>
+static cudaError_t launch_cols_short_axis(const ColsArgs& a, const Launch& l) {
+    using L = typename T::L; using A = typename T::A; using S = typename T::S;
+    // many slices of few rows; an inner run of at least 32 bytes so that the scalar loads of a warp stay in sectors
+    if (a.reduced > 16 || a.outer < 64 || a.inner * sizeof(L) < 32 || a.outer * a.inner < size_t(sm_count()) * kFewThreads * 4 ||
+        tuning().no_few_rows)
+        return cudaErrorNotSupported;
+    if constexpr (sizeof(L) == 4 || sizeof(L) == 8) {
+        constexpr int NV = 16 / int(sizeof(L));
+        if (a.inner % NV == 0 && a.in_stride_o % NV == 0 && a.in_stride_r % NV == 0 && (reinterpret_cast<size_t>(a.in) & 15) == 0 &&
+            a.outer * (a.inner / NV) >= size_t(sm_count()) * kFewThreads * 2) {
+            size_t grid = ceil_div(a.outer * (a.inner / NV), size_t(kFewThreads) * 2);
+            const size_t cap = size_t(sm_count()) * resident_ctas<cols_short_axis_vec_kernel<L, A, S, Op, NV>>(kFewThreads);
+            if (grid > cap) grid = cap;
+            cols_short_axis_vec_kernel<L, A, S, Op, NV><<<(unsigned)grid, kFewThreads, 0, l.stream>>>(
+                (const L*)a.in, (S*)a.out, a.outer, a.reduced, a.inner, a.in_stride_o, a.in_stride_r, a.out_stride_o,
+                a.out_stride_i, make_finish<A, S>(a.identity));
+            return cudaGetLastError();
+        }
+    }
+    size_t grid = ceil_div(a.outer * a.inner, size_t(kFewThreads) * 2);
+    const size_t cap = size_t(sm_count()) * resident_ctas<cols_short_axis_kernel<L, A, S, Op>>(kFewThreads);
+    if (grid > cap) grid = cap;
+    cols_short_axis_kernel<L, A, S, Op><<<(unsigned)grid, kFewThreads, 0, l.stream>>>(
+        (const L*)a.in, (S*)a.out, a.outer, a.reduced, a.inner, a.in_stride_o, a.in_stride_r, a.out_stride_o, a.out_stride_i,
+        make_finish<A, S>(a.identity));
+    return cudaGetLastError();
+}
+
 template <class T, class Op>
 static cudaError_t launch_cols_t(const ColsArgs& a, const Launch& l) {
     using L = typename T::L;
@@ -668,6 +775,10 @@ static cudaError_t launch_cols_t(const ColsArgs& a, const Launch& l) {
     }
     {
         cudaError_t e = launch_cols_few_rows<T, Op>(a, l);
+        if (e != cudaErrorNotSupported) return e;
+    }
+    {
+        cudaError_t e = launch_cols_short_axis<T, Op>(a, l);
         if (e != cudaErrorNotSupported) return e;
     }
     constexpr int NV = 32 / int(sizeof(L));

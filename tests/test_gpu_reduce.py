@@ -836,3 +836,27 @@ def test_broadcast_views_stride_zero(axes, cuda):
         mref = x.contiguous().amax(axes) if axes is not None else x.contiguous().max()
         out = db.reduce('lambda a, b: max(a, b)', x, axis=axes, identity=-1000)
         assert torch.equal(out.reshape(mref.shape), mref)
+
+
+@pytest.mark.parametrize('shape', [(3000, 3, 700), (200000, 4, 64), (70000, 2, 33), (5000, 16, 300), (64, 5, 9000), (100000, 1, 40)])
+@pytest.mark.parametrize('dtype', [np.float32, np.int64, np.int16])
+def test_short_axis_between_many_slices(shape, dtype, cuda):
+    """[N, R <= 16, M] over the middle axis (channel folds): the thread-per-output kernel; sum / max, identity None,
+    a strided output, a window of a larger array."""
+    rng = np.random.default_rng(shape[0] % 97)
+    a = _data(rng, list(shape), dtype)
+    for op in ('sum', 'max'):
+        got, ref = _run(a, (1, ), op, cuda)
+        _check(got, ref, dtype, a, (1, ), op)
+    init = _data(rng, [shape[0], shape[2]], dtype)
+    got, ref = _run(a, (1, ), 'sum', cuda, identity=None, out_init=init)
+    _check(got, ref, dtype, a, (1, ), 'sum')
+    ta = torch.from_numpy(a).to(cuda)
+    out = torch.zeros(shape[2], shape[0], dtype=ta.dtype, device=cuda).t()          # transposed destination
+    db.reduce('lambda a, b: a + b', ta, out, axis=(1, ), identity=0)
+    _check(out.cpu().numpy(), O.reduce(O.SUM, a, (1, ), identity=0, wide=True), dtype, a, (1, ), 'sum')
+    if shape[2] > 40:
+        w = ta[:, :, 3:shape[2] - 5]
+        out = db.reduce('lambda a, b: a + b', w, axis=(1, ), identity=0)
+        h = np.ascontiguousarray(a[:, :, 3:shape[2] - 5])
+        _check(out.cpu().numpy(), O.reduce(O.SUM, h, (1, ), identity=0, wide=True), dtype, h, (1, ), 'sum')
