@@ -117,3 +117,29 @@ def test_single_process_communicator_needs_neither_nccl_nor_a_gpu():
         for k, v in saved.items():
             if v is not None:
                 os.environ[k] = v
+
+
+def test_planner_has_multi_pass_plans_for_views_without_a_gpu():
+    """The dry run behind dace_b200_reduce_nd_workspace_bytes walks the same planner as a real call and needs no GPU:
+    layouts that once fell to one warp of the strided kernel (padded windows folded completely or over interleaved
+    axes) must report scratch beyond the base workspace, i.e. a multi-pass streaming plan exists for them; layouts
+    with a direct kernel must not."""
+    import ctypes
+    lib = _lib.load()
+    base = lib.dace_b200_workspace_bytes()
+
+    def need(shape, istr, mask, dt=0):
+        n = len(shape)
+        return lib.dace_b200_reduce_nd_workspace_bytes(dt, dt, n, (ctypes.c_int64 * n)(*shape), (ctypes.c_int64 * n)(*istr), mask)
+
+    pitch2, pitch3 = [16384, 1], [512 * 512, 512, 1]
+    assert need([16384, 16000], pitch2, 0b11) == base + 16384 * 4                       # rows -> mid[R1] -> full
+    assert need([1024, 500, 500], pitch3, 0b111) > base + 1024 * 500 * 4 - 1            # rows on two levels -> mid[A, B]
+    assert need([1024, 500, 500], pitch3, 0b101) > base + 1024 * 500 * 4 - 1            # axes (0, 2)
+    assert need([1024, 500, 500], pitch3, 0b110) > base                                 # axes (1, 2)
+    assert need([32, 32, 510, 510], [32 * 512 * 512, 512 * 512, 512, 1], 0b1101) > base   # [N, C, H, W] interior, (0, 2, 3)
+    assert need([4096, 512, 8], [4096, 8, 1], 0b101) == base + 256 * ((512 * 8 * 4 + 255) // 256)   # outer axis first
+    # direct kernels: nothing beyond the base
+    assert need([4096, 4096], [4096, 1], 0b11) == base
+    assert need([1024, 500, 500], pitch3, 0b100) == base                                # rows on two levels, no scratch
+    assert need([1024, 500, 500], pitch3, 0b001) == base                                # column fold with an outer axis
