@@ -24,6 +24,9 @@ _PROTOTYPES = {
     'dace_b200_reduce_nd_workspace_bytes': (_c.c_size_t, [
         _c.c_int, _c.c_int, _c.c_int, _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64), _c.c_uint32
     ]),
+    'dace_b200_reduce_nd_plan': (_c.c_size_t, [
+        _c.c_int, _c.c_int, _c.c_int, _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64), _c.c_uint32, _c.c_char_p, _c.c_size_t
+    ]),
     'dace_b200_reduce_nd': (_c.c_int, [
         _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_int,
         _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64), _c.c_uint32, _c.c_void_p,

@@ -77,6 +77,7 @@ static bool supported_pair(int dtin, int dtout) {
 // Full reduction / few long rows through the split kernel.
 static cudaError_t plan_split(int red, int dtin, int dtout, const void* in, void* out, size_t rows, size_t n,
                               size_t row_stride, ptrdiff_t out_stride, const void* identity, const Launch& l) {
+    l.note("split");
     if (l.dry_need) return cudaSuccess;
     const size_t row_bytes = n * dtype_size(dtin);
     const size_t sms = sm_count();
@@ -116,16 +117,18 @@ static cudaError_t plan_rows(int red, int dtin, int dtout, const void* in, void*
                              size_t row_stride, ptrdiff_t out_stride, const void* identity, const Launch& l,
                              size_t hi_count = 1, size_t hi_in_stride = 0, ptrdiff_t hi_out_stride = 0) {
     if (hi_count > 65535) return cudaErrorNotSupported;
-    if (l.dry_need) return cudaSuccess;
     const size_t row_bytes = n * dtype_size(dtin);
     if (hi_count == 1 && rows < 2 * (size_t)sm_count() && row_bytes >= (size_t(128) << 10) && rows <= kCounters)
         return plan_split(red, dtin, dtout, in, out, rows, n, row_stride, out_stride, identity, l);
+    l.note(hi_count > 1 ? "rows2" : "rows");
+    if (l.dry_need) return cudaSuccess;
     RowsArgs a{in, out, rows, n, row_stride, out_stride, identity};
     a.hi_count = hi_count; a.hi_in_stride = hi_in_stride; a.hi_out_stride = hi_out_stride;
     return launch_rows(red, dtin, dtout, a, l);
 }
 
 static cudaError_t plan_cols(int red, int dtin, int dtout, const ColsArgs& a, const Launch& l) {
+    l.note("cols");
     if (l.dry_need) return cudaSuccess;
     return launch_cols(red, dtin, dtout, a, l);
 }
@@ -198,7 +201,7 @@ static cudaError_t plan_two_pass(int red, int dtin, int dtout, const void* in, v
     const size_t need = two_pass_bytes(dtin, dtout, O, R1, K);
     if (half_out && O != 1) return cudaErrorNotSupported;
     if (need > kMidMaxBytes) return cudaErrorNotSupported;
-    if (l.dry_need) { l.take(need); return cudaSuccess; }
+    if (l.dry_need) { l.take(need); l.note("two-pass(rows,cols)"); return cudaSuccess; }
     if (need > l.extra_bytes) return cudaErrorNotSupported;
     void* mid = l.extra;
     cudaError_t e;
@@ -234,7 +237,7 @@ static cudaError_t plan_outer_first(int red, int dtin, int dtout, const void* in
         return cudaErrorNotSupported;
     const size_t need = outer_first_bytes(dtin, K, R2);
     if (need > kMidMaxBytes) return cudaErrorNotSupported;
-    if (l.dry_need) { l.take(need); return cudaSuccess; }
+    if (l.dry_need) { l.take(need); l.note("outer-first(cols,rows)"); return cudaSuccess; }
     if (need > l.extra_bytes) return cudaErrorNotSupported;
     void* mid = l.extra;
     ColsArgs a{in, mid, 1, R1, K * R2, 0, K * R2, 0, 1, neutral};
@@ -274,6 +277,17 @@ static cudaError_t plan_fast(int red, int dtin, int dtout, const void* in, void*
             ColsArgs a{in, out, (size_t)c[0].shape, (size_t)c[1].shape, (size_t)c[2].shape,
                        (size_t)c[0].in_stride, (size_t)c[1].in_stride,
                        (ptrdiff_t)c[0].out_stride, (ptrdiff_t)c[2].out_stride, identity};
+            return plan_cols(red, dtin, dtout, a, l);
+        }
+        // [R, K1, K2] where K1 and K2 do not merge (a window: a pitch after every K2 run; or an output laid out
+        // differently) -> the same kernel, K1 as its outer axis: the strides are all it needs.  Only for the slices of a
+        // peeled reduced axis ([R0, R, K1, K2] with a pitch on every level: 0.55 -> 3.3 TB/s); on its own the
+        // thread-per-output strided kernel serves this form better (5.5 against 4.1 TB/s on [1024, 500, 500]).
+        if (l.slice_of_fold && nc == 3 && c[0].reduced && !c[1].reduced && !c[2].reduced && c[2].in_stride == 1 && c[0].in_stride >= 0 &&
+            c[1].in_stride >= 0 && c[1].shape <= 65535) {
+            ColsArgs a{in, out, (size_t)c[1].shape, (size_t)c[0].shape, (size_t)c[2].shape,
+                       (size_t)c[1].in_stride, (size_t)c[0].in_stride,
+                       (ptrdiff_t)c[1].out_stride, (ptrdiff_t)c[2].out_stride, identity};
             return plan_cols(red, dtin, dtout, a, l);
         }
     }
@@ -411,6 +425,7 @@ static cudaError_t plan_inner_first(int red, int dtin, int dtout, const void* in
     if (mid_bytes > kMidMaxBytes) return cudaErrorNotSupported;
     if (!l.dry_need && mid_bytes > l.extra_bytes) return cudaErrorNotSupported;
     l.take(mid_bytes);
+    l.note("inner-first:");
     void* mid = l.extra;
     cudaError_t e;
     if (has_inner) {
@@ -484,20 +499,40 @@ static cudaError_t plan_dims(int red, int dtin, int dtout, const void* in, void*
         for (int i = 1; i < nc; ++i) slice_elems *= (size_t)c[i].shape;
         // a reduced outer axis is where the strided kernel is weakest (one thread folds everything for its output);
         // with a kept outer axis it keeps its warp-per-output mapping, so small slices are not worth their launches
-        bool ok = sub_nr > 0 && slice_elems * isz >= (c[0].reduced ? (size_t(1) << 20) : (size_t(32) << 20));
+        // (unless it folds the innermost axis into few outputs: a warp per output, 16 outputs = 16 warps, 14 GB/s)
+        const bool few_outputs = c[nc - 1].reduced && c[nc - 1].in_stride == 1 && nout < size_t(16384);
+        bool ok = sub_nr > 0 && slice_elems * isz >= (c[0].reduced || few_outputs ? (size_t(1) << 20) : (size_t(32) << 20));
+        Launch ls = l;
+        ls.slice_of_fold = c[0].reduced;
+        // What would serve one slice?  A dry run of the whole planner on it (multi-pass plans included: a window padded
+        // on three levels folded over all its axes is 16 slices of an inner-first plan, not one warp of the strided
+        // kernel); slices that would themselves end in the strided kernel are not worth peeling.
+        char sub[160] = {0};
+        size_t sub_need = 0;
+        if (ok) {
+            Launch ld = ls;
+            ld.dry_need = &sub_need; ld.dry_base = 0; ld.dry_plan = sub; ld.dry_plan_bytes = sizeof(sub);
+            const cudaError_t ed = plan_dims(red, dtin, dtout, nullptr, nullptr, c + 1, nc - 1, nullptr, ld, false, depth + 1);
+            ok = ed == cudaSuccess && strstr(sub, "generic") == nullptr && (l.dry_need != nullptr || sub_need <= l.extra_bytes);
+        }
+        if (ok) {
+            l.note("peel:");
+            l.note(sub);
+            l.take(sub_need);
+            if (l.dry_need) return cudaSuccess;
+        }
         for (long long i = 0; ok && i < c[0].shape; ++i) {
             const char* sin = static_cast<const char*>(in) + size_t(i) * size_t(c[0].in_stride) * isz;
             char* sout = static_cast<char*>(out) + (c[0].reduced ? 0 : ptrdiff_t(i) * c[0].out_stride * ptrdiff_t(osz));
             const void* sid = (c[0].reduced && i > 0) ? nullptr : identity;
-            cudaError_t ep = plan_fast(red, dtin, dtout, sin, sout, c + 1, nc - 1, sub_nr, sid, l);
-            if (ep == cudaErrorNotSupported && i == 0) { ok = false; break; }   // nothing launched yet: generic kernel
+            const cudaError_t ep = plan_dims(red, dtin, dtout, sin, sout, c + 1, nc - 1, sid, ls, false, depth + 1);
             if (ep != cudaSuccess) return ep;
-            if (l.dry_need) break;     // every slice has the same plan
         }
         if (ok) return cudaSuccess;
     }
     // Everything else: generic strided kernel.
     if (nk > kMaxDims || nr > kMaxDims) return cudaErrorNotSupported;
+    l.note("generic");
     if (l.dry_need) return cudaSuccess;
     GenericArgs g;
     memset(&g, 0, sizeof(g));
@@ -513,7 +548,9 @@ static cudaError_t plan_dims(int red, int dtin, int dtout, const void* in, void*
 }
 
 static size_t reduce_nd_workspace_bytes_impl(int dtin, int dtout, int ndim, const int64_t* shape,
-                                             const int64_t* in_strides, uint32_t mask) {
+                                             const int64_t* in_strides, uint32_t mask, char* plan = nullptr,
+                                             size_t plan_bytes = 0) {
+    if (plan && plan_bytes) plan[0] = 0;
     Dim c[DACE_B200_MAX_DIMS];
     int nc = 0;
     size_t nout = 0, nred = 0;
@@ -525,6 +562,7 @@ static size_t reduce_nd_workspace_bytes_impl(int dtin, int dtout, int ndim, cons
     l.stream = nullptr;
     l.ws.counters = nullptr; l.ws.partials = nullptr;
     l.dry_need = &need;
+    l.dry_plan = plan; l.dry_plan_bytes = plan_bytes;
     plan_dims(RT_Sum, dtin, dtout, nullptr, nullptr, c, nc, nullptr, l, false, 0);   // the plan does not depend on the operator
     return kWorkspaceBytes + need;
 }
@@ -556,7 +594,7 @@ using namespace db200;
 
 extern "C" {
 
-int dace_b200_version(void) { return 2000; }
+int dace_b200_version(void) { return 2001; }
 
 const char* dace_b200_status_string(int status) { return cudaGetErrorString((cudaError_t)status); }
 
@@ -570,6 +608,11 @@ int dace_b200_workspace_init(void* workspace, size_t workspace_bytes, dace_b200_
 size_t dace_b200_reduce_nd_workspace_bytes(int dtype_in, int dtype_out, int ndim, const int64_t* shape,
                                            const int64_t* in_strides, uint32_t reduce_mask) {
     return reduce_nd_workspace_bytes_impl(dtype_in, dtype_out, ndim, shape, in_strides, reduce_mask);
+}
+
+size_t dace_b200_reduce_nd_plan(int dtype_in, int dtype_out, int ndim, const int64_t* shape, const int64_t* in_strides,
+                                uint32_t reduce_mask, char* plan, size_t plan_bytes) {
+    return reduce_nd_workspace_bytes_impl(dtype_in, dtype_out, ndim, shape, in_strides, reduce_mask, plan, plan_bytes);
 }
 
 int dace_b200_reduce_nd(int redtype, int dtype_in, int dtype_out, const void* in, void* out, int ndim,

@@ -392,6 +392,18 @@ struct Launch {
     size_t* dry_need = nullptr;
     size_t dry_base = 0;
     void take(size_t bytes) const { if (dry_need && dry_base + bytes > *dry_need) *dry_need = dry_base + bytes; }
+    // Dry runs may also record WHICH plan the planner picked (dace_b200_reduce_nd_plan): a space-separated trace.
+    char* dry_plan = nullptr;
+    size_t dry_plan_bytes = 0;
+    bool slice_of_fold = false;  // this call plans one slice of a host-peeled REDUCED axis (api.cu, plan_dims)
+    void note(const char* what) const {
+        if (!dry_plan || dry_plan_bytes == 0) return;
+        size_t used = 0;
+        while (used < dry_plan_bytes && dry_plan[used]) ++used;
+        if (used && used + 1 < dry_plan_bytes) dry_plan[used++] = ' ';
+        while (*what && used + 1 < dry_plan_bytes) dry_plan[used++] = *what++;
+        if (used < dry_plan_bytes) dry_plan[used] = 0;
+    }
 };
 
 // Experiment knobs (environment variables), read ONCE when the library is loaded - never on a call path.

@@ -109,6 +109,14 @@ DACE_B200_API size_t dace_b200_workspace_bytes(void);
 DACE_B200_API int dace_b200_workspace_init(void* workspace, size_t workspace_bytes, dace_b200_stream_t stream);
 DACE_B200_API size_t dace_b200_reduce_nd_workspace_bytes(int dtype_in, int dtype_out, int ndim, const int64_t* shape,
                                                          const int64_t* in_strides, uint32_t reduce_mask);
+/* Diagnostics (no reference counterpart): the same dry run, which also writes WHICH plan the planner picks for the
+ * layout into `plan` as a NUL-terminated, space-separated trace ("rows", "cols", "split", "rows2" = rows on two
+ * levels, "two-pass(rows,cols)", "outer-first(cols,rows)", "inner-first: <first pass> <rest>", "peel: <slice plan>",
+ * "generic" = the strided fallback kernel).  Needs no GPU; returns what dace_b200_reduce_nd_workspace_bytes returns.
+ * tests/test_cabi_library.py uses it to keep layouts off the fallback kernel. */
+DACE_B200_API size_t dace_b200_reduce_nd_plan(int dtype_in, int dtype_out, int ndim, const int64_t* shape,
+                                              const int64_t* in_strides, uint32_t reduce_mask, char* plan,
+                                              size_t plan_bytes);
 
 /* ---- Reduce library node -------------------------------------------------
  * General N-D entry, the call the `B200` expansion of

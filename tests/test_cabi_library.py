@@ -26,7 +26,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     for name in _declared():
         assert hasattr(lib, name), name
     lib = dace_b200.load()
-    assert lib.dace_b200_version() == 2000
+    assert lib.dace_b200_version() == 2001
     assert lib.dace_b200_workspace_bytes() == 8 << 20
     assert lib.dace_b200_status_string(801).decode() == 'operation not supported'
 
@@ -143,3 +143,56 @@ def test_planner_has_multi_pass_plans_for_views_without_a_gpu():
     assert need([4096, 4096], [4096, 1], 0b11) == base
     assert need([1024, 500, 500], pitch3, 0b100) == base                                # rows on two levels, no scratch
     assert need([1024, 500, 500], pitch3, 0b001) == base                                # column fold with an outer axis
+
+
+def test_planner_trace_keeps_views_off_the_strided_kernel():
+    """dace_b200_reduce_nd_plan names the kernels a call would launch (no GPU needed).  Over contiguous arrays,
+    windows padded on one to three levels and transposed views, every axis mask: the strided thread-per-output
+    kernel ('generic') may only serve the layouts listed here -- folds over outer axes of a window (thread per
+    output is a streaming plan there: measured 5.5-5.8 TB/s, profiles/r2_window_sweep.txt) and three transposed
+    views whose output order differs from their input order."""
+    import ctypes
+    lib = _lib.load()
+
+    def plan(shape, istr, mask, dt=0):
+        n = len(shape)
+        buf = ctypes.create_string_buffer(256)
+        need = lib.dace_b200_reduce_nd_plan(dt, dt, n, (ctypes.c_int64 * n)(*shape), (ctypes.c_int64 * n)(*istr), mask, buf, 256)
+        assert need == lib.dace_b200_reduce_nd_workspace_bytes(dt, dt, n, (ctypes.c_int64 * n)(*shape), (ctypes.c_int64 * n)(*istr), mask)
+        return buf.value.decode()
+
+    def dense(full):
+        st = [1] * len(full)
+        for i in range(len(full) - 2, -1, -1):
+            st[i] = st[i + 1] * full[i + 1]
+        return st
+
+    cases = []
+    for shape in ([4096, 4096], [512, 512, 1024], [64, 64, 64, 1024], [1 << 20, 8], [8, 1 << 20], [100000, 33], [64, 256, 16, 512]):
+        cases += [('contig', shape, dense(shape), m) for m in range(1, 1 << len(shape))]
+    for full, win in (([1024, 512, 512], [1024, 500, 500]), ([32, 32, 512, 512], [32, 32, 510, 510]),
+                      ([4096, 4096], [4000, 4000]), ([16, 64, 64, 4096], [16, 60, 60, 4000])):
+        cases += [('window', win, dense(full), m) for m in range(1, 1 << len(win))]
+    for shape, perm in (([512, 512, 1024], (2, 0, 1)), ([512, 512, 1024], (1, 0, 2)), ([4096, 4096], (1, 0)), ([64, 64, 64, 1024], (0, 2, 1, 3))):
+        st = dense(shape)
+        cases += [('permuted', [shape[q] for q in perm], [st[q] for q in perm], m) for m in range(1, 1 << len(shape))]
+
+    allowed = {
+        ('window', (1024, 500, 500), 0b1), ('window', (32, 32, 510, 510), 0b1), ('window', (32, 32, 510, 510), 0b10),
+        ('window', (32, 32, 510, 510), 0b11), ('window', (16, 60, 60, 4000), 0b1), ('window', (16, 60, 60, 4000), 0b10),
+        ('permuted', (1024, 512, 512), 0b10), ('permuted', (64, 64, 64, 1024), 0b1), ('permuted', (64, 64, 64, 1024), 0b1000),
+        ('permuted', (64, 64, 64, 1024), 0b1001),
+    }
+    generic = {(k, tuple(sh), m) for k, sh, st, m in cases if 'generic' in plan(sh, st, m)}
+    assert generic <= allowed, sorted(generic - allowed)
+
+    # spot checks of the trace itself
+    assert plan([4096, 4096], [4096, 1], 0b10) == 'rows'
+    assert plan([4096, 4096], [4096, 1], 0b01) == 'cols'
+    assert plan([4096, 4096], [4096, 1], 0b11) == 'split'
+    assert plan([1024, 500, 500], [262144, 512, 1], 0b100) == 'rows2'
+    assert plan([16, 60, 60, 4000], [16777216, 262144, 4096, 1], 0b1111).startswith('peel: inner-first:')
+    assert plan([16, 60, 60, 4000], [16777216, 262144, 4096, 1], 0b1000) == 'peel: rows2'
+    assert plan([16, 60, 60, 4000], [16777216, 262144, 4096, 1], 0b0011) == 'peel: cols'       # slices [R, K1, K2] of a folded axis
+    assert plan([16, 60, 60, 1000], [16777216, 262144, 4096, 1], 0b1110).startswith('peel:')   # 16 outputs: never a warp each
+

@@ -822,6 +822,36 @@ def test_interior_of_a_4d_array(axes, dtype, cuda):
         _check(out.cpu().numpy().reshape(ref.shape), ref, dtype, host, axes, op)
 
 
+@pytest.mark.parametrize('dtype', [np.float32, np.int32])
+def test_window_padded_on_three_levels(dtype, cuda):
+    """[A, B, C, D] windows with a pitch after every row, plane and cube: the planner peels the outermost axis and
+    plans each slice with everything it has (rows on two levels, inner-first), instead of giving the whole view to
+    the strided kernel.  Slices above the peel thresholds (1 MiB folded, 32 MiB kept)."""
+    rng = np.random.default_rng(11)
+    base = _data(rng, [4, 54, 64, 3072], dtype)
+    win = (slice(0, 4), slice(2, 52), slice(1, 61), slice(8, 3008))
+    host = np.ascontiguousarray(base[win])
+    view = torch.from_numpy(base).to(cuda)[win]
+    for axes in ((0, 1, 2, 3), (1, 2, 3), (1, 3), (2, 3), (0, 1, 3), (0, 2, 3), (1, ), (0, 1), (3, )):
+        for op in ('sum', 'max'):
+            red, lam, _ = _OPS[op]
+            ident = _identity(op, dtype)
+            out = db.reduce(lam, view, axis=axes, identity=ident)
+            ref = O.reduce(red, host, axes, identity=ident, wide=True)
+            _check(out.cpu().numpy().reshape(ref.shape), ref, dtype, host, axes, op)
+    # identity None: folded into what the output holds, once, also when the folded outermost axis is peeled
+    want = host.astype(np.float64).sum((0, 1, 3))
+    init = _data(rng, [60], dtype)
+    out = torch.from_numpy(init.copy()).to(cuda)
+    db.reduce('lambda a, b: a + b', view, out, axis=(0, 1, 3), identity=None)
+    want = want + init.astype(np.float64)
+    if np.issubdtype(dtype, np.floating):
+        scale = np.abs(host.astype(np.float64)).sum((0, 1, 3)) + np.abs(init.astype(np.float64))
+        assert np.all(np.abs(out.cpu().numpy().astype(np.float64) - want) <= RTOL_F32 * np.maximum(scale, 1e-30))
+    else:
+        np.testing.assert_array_equal(out.cpu().numpy(), want.astype(np.int64).astype(dtype))
+
+
 @pytest.mark.parametrize('axes', [(0, ), (1, ), None])
 def test_broadcast_views_stride_zero(axes, cuda):
     """Inputs with a zero stride (a row or a column broadcast over the other axis, `expand`): every element is

@@ -11,7 +11,11 @@ views = {'window [:, :500, :500]': base[:, :500, :500], 'window [3:1000, 7:, :50
 base4 = base.view(32, 32, 512, 512)
 views4 = {'4-D interior [:, :, 1:-1, 1:-1]': base4[:, :, 1:-1, 1:-1]}
 print('%-42s %-10s %9s %9s' % ('view', 'axes', 'ms', 'GB/s'))
-ONLY4 = '--4d' in sys.argv
+ONLY4 = '--4d' in sys.argv or '--3level' in sys.argv
+if '--3level' in sys.argv:   # a pitch after every row, plane and cube: the outermost axis is peeled
+    b4 = base.view(16, 64, 64, 4096)
+    views4 = {'3 padded levels [:, :60, :60, :4000]': b4[:, :60, :60, :4000],      # 57.6 MB slices
+              '3 padded levels [:, :60, :60, :1000]': b4[:, :60, :60, :1000]}      # 14.4 MB slices
 ALL = [(vn, x, axes) for vn, x in ({} if ONLY4 else views).items() for r in (1, 2, 3) for axes in itertools.combinations(range(3), r)]
 ALL += [(vn, x, axes) for vn, x in views4.items() for axes in ((2, 3), (0, 2, 3), (3, ), (1, 2, 3), (0, 1, 2, 3), (0, 1), (1, ), (0, ), (2, ), (0, 2), (1, 3), (0, 3), (1, 2), (0, 1, 3), (0, 1, 2))]
 for vname, x, axes in ALL:
