@@ -414,14 +414,24 @@ static cudaError_t plan_inner_first(int red, int dtin, int dtout, const void* in
     if (!dense && !two_level) return cudaErrorNotSupported;
     if (c[j - 1].in_stride < 0) return cudaErrorNotSupported;
     const int dtmid = (dtin == DT_BF16 || dtin == DT_F16) ? DT_F32 : dtin;
+    // 16-bit output behind an fp32 intermediate (bf16 -> bf16, f16 -> f16: no fp32 -> 16-bit kernel pair exists): the
+    // rest of the fold stays in fp32 into a small buffer behind the intermediate, one tiny launch folds the
+    // caller's identity and rounds once (as in plan_two_pass).  At most one kept axis group may remain.
+    const bool half_out = dtmid == DT_F32 && (dtout == DT_BF16 || dtout == DT_F16);
     unsigned char neutral[8];
-    if (!supported_pair(dtin, dtmid) || !supported_pair(dtmid, dtout) || !neutral_bytes(red, dtmid, neutral))
+    if (!supported_pair(dtin, dtmid) || !(half_out || supported_pair(dtmid, dtout)) || !neutral_bytes(red, dtmid, neutral))
         return cudaErrorNotSupported;
     size_t O = 1;
     for (int i = 0; i < j; ++i) O *= (size_t)c[i].shape;
     const size_t K = has_inner ? (size_t)c[nc - 1].shape : 1;
     const size_t R = (size_t)c[j].shape;
-    const size_t mid_bytes = (O * K * dtype_size(dtmid) + 255) & ~size_t(255);
+    size_t kept_out = 1;
+    int kept_groups = 0, kept_at = -1;
+    for (int i = 0; i < nc; ++i)
+        if (!c[i].reduced) { kept_out *= (size_t)c[i].shape; ++kept_groups; kept_at = i; }
+    if (half_out && kept_groups > 1) return cudaErrorNotSupported;
+    const size_t fin_bytes = half_out ? ((kept_out * sizeof(float) + 255) & ~size_t(255)) : 0;
+    const size_t mid_bytes = ((O * K * dtype_size(dtmid) + 255) & ~size_t(255)) + fin_bytes;
     if (mid_bytes > kMidMaxBytes) return cudaErrorNotSupported;
     if (!l.dry_need && mid_bytes > l.extra_bytes) return cudaErrorNotSupported;
     l.take(mid_bytes);
@@ -456,6 +466,17 @@ static cudaError_t plan_inner_first(int red, int dtin, int dtout, const void* in
         l2.extra_bytes = l.extra_bytes - mid_bytes;
     }
     l2.dry_base = l.dry_base + mid_bytes;
+    if (half_out) {
+        float* fin = l.dry_need ? nullptr : reinterpret_cast<float*>(static_cast<char*>(l.extra) + (mid_bytes - fin_bytes));
+        for (int i = 0; i < nmerged; ++i)
+            if (!merged[i].reduced) merged[i].out_stride = 1;            // the one kept group, dense in `fin`
+        e = plan_dims(red, DT_F32, DT_F32, mid, fin, merged, nmerged, neutral, l2, false, depth + 1);
+        if (e != cudaSuccess) return e;
+        l.note("finish");
+        if (l.dry_need) return cudaSuccess;
+        return launch_finish_convert(red, dtout, fin, out, kept_out, kept_at >= 0 ? (ptrdiff_t)c[kept_at].out_stride : 1,
+                                     identity, l);
+    }
     return plan_dims(red, dtmid, dtout, mid, out, merged, nmerged, identity, l2, false, depth + 1);
 }
 

@@ -195,4 +195,12 @@ def test_planner_trace_keeps_views_off_the_strided_kernel():
     assert plan([16, 60, 60, 4000], [16777216, 262144, 4096, 1], 0b1000) == 'peel: rows2'
     assert plan([16, 60, 60, 4000], [16777216, 262144, 4096, 1], 0b0011) == 'peel: cols'       # slices [R, K1, K2] of a folded axis
     assert plan([16, 60, 60, 1000], [16777216, 262144, 4096, 1], 0b1110).startswith('peel:')   # 16 outputs: never a warp each
-
+    # 16-bit in and out (dtype codes of include/dace_b200_reduce.h): fp32 between the passes, one small launch rounds
+    import torch
+    from dace_b200 import api
+    BF16, F16 = api.dtype_code(torch.bfloat16), api.dtype_code(torch.float16)
+    for dt in (BF16, F16):
+        assert plan([1024, 500, 500], [262144, 512, 1], 0b111, dt) == 'inner-first: rows2 split finish'
+        assert plan([1024, 500, 500], [262144, 512, 1], 0b101, dt) == 'inner-first: rows2 cols finish'
+        assert plan([16384, 16000], [16384, 1], 0b11, dt) == 'inner-first: rows split finish'
+        assert plan([512, 512, 1024], [524288, 1024, 1], 0b101, dt) == 'two-pass(rows,cols)'

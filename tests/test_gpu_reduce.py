@@ -852,6 +852,35 @@ def test_window_padded_on_three_levels(dtype, cuda):
         np.testing.assert_array_equal(out.cpu().numpy(), want.astype(np.int64).astype(dtype))
 
 
+@pytest.mark.parametrize('tdtype', ['bfloat16', 'float16'])
+def test_windows_with_16_bit_output(tdtype, cuda):
+    """bf16 -> bf16 / f16 -> f16 over windows: the multi-pass plans keep fp32 between their passes and there is no
+    fp32 -> 16-bit kernel pair, so the last pass writes fp32 behind the intermediate and one small launch folds the
+    identity and rounds once.  (Before: these layouts fell to one warp of the strided kernel.)  Exact small integers
+    whose sums stay exactly representable in fp32; the result is the correctly rounded 16-bit value."""
+    dt = getattr(torch, tdtype)
+    g = torch.Generator(device='cuda').manual_seed(5)
+    base = torch.randint(-3, 4, (60, 70, 900), device=cuda, generator=g).to(dt)
+    view = base[2:58, 3:66, 5:880]
+    for axes in ((0, 1, 2), (0, 2), (1, 2), (0, 1), (2, ), (1, ), (0, )):
+        ref64 = view.double().sum(axes)
+        out = db.reduce('lambda a, b: a + b', view, axis=axes, identity=0)
+        assert out.dtype == dt
+        assert torch.equal(out.reshape(ref64.shape), ref64.to(dt)), axes
+        mref = view.float().amax(axes).to(dt)
+        out = db.reduce('lambda a, b: max(a, b)', view, axis=axes, identity=-100)
+        assert torch.equal(out.reshape(mref.shape), mref), axes
+    # identity None: folded into what the output holds
+    init = torch.randint(-5, 6, (63, ), device=cuda, generator=g).to(dt)
+    out = init.clone()
+    db.reduce('lambda a, b: a + b', view, out, axis=(0, 2), identity=None)
+    assert torch.equal(out, (view.double().sum((0, 2)) + init.double()).to(dt))
+    # every element of a padded 2-D window
+    base2 = torch.randint(-3, 4, (3000, 4096), device=cuda, generator=g).to(dt)
+    out = db.reduce('lambda a, b: a + b', base2[:, :4000], axis=None, identity=0)
+    assert torch.equal(out.reshape(()), base2[:, :4000].double().sum().to(dt))
+
+
 @pytest.mark.parametrize('axes', [(0, ), (1, ), None])
 def test_broadcast_views_stride_zero(axes, cuda):
     """Inputs with a zero stride (a row or a column broadcast over the other axis, `expand`): every element is
